@@ -1,0 +1,194 @@
+"""Entry point and role split.
+
+Parity: reference ``main_manager.py:46-73`` — every endpoint runs the same
+program; the master wipes/creates ``savedata``, builds the ``PBTCluster``, dumps
+the initial hyper-parameters, trains ``train_round`` rounds, appends the timing
+line to ``test_results.txt``, writes reports and the best model, prints the
+profiling summary and sends EXIT; every other endpoint runs
+``TrainingWorker.main_loop()``.
+
+Launch modes (no ``mpirun`` on the target image):
+
+* ``transport="local"``  master + workers as threads of this process (tests, 1 GPU);
+* ``transport="tcp"``    ``spawn_tcp`` starts one process per worker (one per GPU)
+  and runs the master in the parent; also used under ``torchrun`` where local
+  rank 0 hosts the master thread next to its worker;
+* ``transport="gloo"`` / ``"mpi"``  the process is already one rank of a job.
+"""
+from __future__ import annotations
+
+import json
+import multiprocessing as mp
+import os
+import random
+import shutil
+import threading
+from typing import Any, Callable, Dict, List, Optional
+
+from . import report
+from .config import RunConfig, parse_args
+from .master import PBTCluster
+from .models import get_model_class
+from .parallel.local import LocalFabric
+from .worker import TrainingWorker
+
+
+def _fault_hook(cfg: RunConfig) -> Optional[Callable[[Any, int], None]]:
+    plan = {}
+    for item in cfg.inject_nan:
+        mid, rnd = item.split("@")
+        plan.setdefault(int(rnd), set()).add(int(mid))
+    if not plan:
+        return None
+
+    def hook(member, rnd):
+        if member.cluster_id in plan.get(rnd, ()):
+            raise FloatingPointError(f"injected NaN for member {member.cluster_id} at round {rnd}")
+    return hook
+
+
+def model_kwargs(cfg: RunConfig) -> Dict[str, Any]:
+    if cfg.target_model == "toy":
+        return {}
+    kw = dict(engine=cfg.engine, dtype=cfg.dtype, synthetic=cfg.synthetic, data_dir=cfg.data_dir,
+              max_train_steps=cfg.max_train_steps, eval_batches=cfg.eval_batches,
+              resume=cfg.resume)
+    if cfg.target_model == "cifar10":
+        kw.update(resnet_size=cfg.resnet_size, resnet_version=cfg.resnet_version)
+    return kw
+
+
+def run_master(cfg: RunConfig, comm) -> Dict[str, Any]:
+    if cfg.clean:
+        shutil.rmtree(cfg.save_root, ignore_errors=True)
+    os.makedirs(cfg.save_root, exist_ok=True)
+    initial = None
+    if cfg.initial_hp:
+        with open(cfg.initial_hp) as f:
+            initial = [rec["hparams"] for rec in json.load(f)]
+    rng = random.Random(cfg.seed) if cfg.seed is not None else None
+    cluster = PBTCluster(cfg.population_size, comm, cfg.master_rank,
+                         epochs_per_round=cfg.epochs_per_round,
+                         do_exploit=cfg.do_exploit, do_explore=cfg.do_explore,
+                         save_root=cfg.save_root, exploit_path=cfg.exploit_path, rng=rng,
+                         recv_timeout=cfg.recv_timeout, initial_hparams=initial,
+                         verbose=cfg.verbose)
+    cluster.dump_all_models_to_json(os.path.join(cfg.save_root, "initial_hp.json"))
+    elapsed = cluster.train(cfg.train_round)
+    if cfg.results_file:
+        report.append_timing(cfg.results_file, comm.Get_size(), cfg.population_size, elapsed)
+    if cfg.target_model == "toy":
+        cluster.report_plot_for_toy_model()
+    else:
+        cluster._reports()
+    best = cluster.report_best_model()
+    prof = cluster.print_profiling_info()
+    cluster.kill_all_workers()
+    return {"elapsed": elapsed, "best": best, "profiling": prof, "history": cluster.history,
+            "pop_size": cluster.pop_size}
+
+
+def run_worker(cfg: RunConfig, comm) -> TrainingWorker:
+    worker = TrainingWorker(comm, cfg.master_rank, get_model_class(cfg.target_model),
+                            save_base_dir=os.path.join(cfg.save_root, "model_"),
+                            verbose=cfg.verbose, model_kwargs=model_kwargs(cfg),
+                            fault_hook=_fault_hook(cfg))
+    if cfg.seed is not None:
+        random.seed(cfg.seed * 1000003 + comm.Get_rank())
+    worker.main_loop()
+    return worker
+
+
+def run_local(cfg: RunConfig) -> Dict[str, Any]:
+    """Master + workers as threads over the in-process fabric."""
+    fabric = LocalFabric(cfg.workers + 1)
+    errors: List[BaseException] = []
+
+    def guard(fn, *a):
+        try:
+            fn(*a)
+        except BaseException as e:  # surfaced after join
+            errors.append(e)
+
+    threads = [threading.Thread(target=guard, args=(run_worker, cfg, fabric.endpoint(r)),
+                                name=f"dtf-worker{r}", daemon=True)
+               for r in range(1, cfg.workers + 1)]
+    for t in threads:
+        t.start()
+    result = run_master(cfg, fabric.endpoint(0))
+    for t in threads:
+        t.join(timeout=60)
+    if errors:
+        raise errors[0]
+    return result
+
+
+def _tcp_worker_entry(cfg: RunConfig, rank: int, gpu: Optional[int]) -> None:
+    from .parallel.tcp import TcpWorkerComm
+    if gpu is not None:
+        os.environ.setdefault("DTF_LOCAL_GPU", str(gpu))
+    comm = TcpWorkerComm(cfg.master_addr, cfg.master_port, rank, cfg.workers + 1)
+    try:
+        run_worker(cfg, comm)
+    finally:
+        comm.close()
+
+
+def spawn_tcp(cfg: RunConfig, gpus: Optional[List[int]] = None) -> Dict[str, Any]:
+    """One OS process per worker (one per GPU when ``gpus`` is given), master here."""
+    from .parallel.tcp import TcpMasterComm
+    ctx = mp.get_context("spawn")
+    master = TcpMasterComm(cfg.master_addr, cfg.master_port, cfg.workers + 1)
+    cfg = cfg.replace(master_port=master.port)
+    procs = []
+    for r in range(1, cfg.workers + 1):
+        gpu = gpus[(r - 1) % len(gpus)] if gpus else None
+        p = ctx.Process(target=_tcp_worker_entry, args=(cfg, r, gpu), daemon=True)
+        p.start()
+        procs.append(p)
+    try:
+        master.wait_for_workers()
+        result = run_master(cfg, master)
+    finally:
+        for p in procs:
+            p.join(timeout=60)
+            if p.is_alive():
+                p.terminate()
+        master.close()
+    return result
+
+
+def run(cfg: RunConfig) -> Optional[Dict[str, Any]]:
+    cfg.validate()
+    if cfg.transport == "local":
+        return run_local(cfg)
+    if cfg.transport == "tcp":
+        return spawn_tcp(cfg)
+    if cfg.transport == "gloo":
+        import torch.distributed as dist
+        from .parallel.gloo import GlooComm
+        if not dist.is_initialized():
+            dist.init_process_group("gloo")
+        comm = GlooComm()
+    elif cfg.transport == "mpi":
+        from .parallel.mpi import MpiComm
+        comm = MpiComm()
+    else:
+        raise ValueError(cfg.transport)
+    if comm.Get_rank() == cfg.master_rank:
+        return run_master(cfg, comm)
+    run_worker(cfg, comm)
+    return None
+
+
+def main(argv=None) -> int:
+    os.environ.setdefault("TF_CPP_MIN_LOG_LEVEL", "3")  # harmless; mirrors main_manager.py:19
+    cfg = parse_args(argv)
+    # Under mpirun without mpi4py, or plain invocation: fall back to the built-in launcher.
+    if cfg.transport == "mpi":
+        from .parallel import mpi
+        if not mpi.available():
+            print("mpi4py not importable: degrading to the built-in local launcher")
+            cfg = cfg.replace(transport="local")
+    run(cfg)
+    return 0

@@ -1,0 +1,151 @@
+"""The worker runtime: a blocking instruction loop that owns a slice of the population.
+
+Parity: reference ``training_worker.py:12-105``.  Same handlers
+(``add_graphs, train, get_all_values, set_values, explore_necessary_graphs``) and
+the same member-drop rule: a member whose ``train`` raises, or whose accuracy is
+NaN, is removed from the worker and its directory deleted; the master learns of
+it through a shorter GET reply (``training_worker.py:63-80``).
+
+B200-first differences: members are persistent GPU-resident objects (built once
+in ``add_graphs``), SET records may carry ``extras`` describing a device-side
+exploit (``[id, acc, hparams, extras]``), donor records (``extras["role"] ==
+"src"``) ask a winner to take part in a two-sided transfer, and the profiling
+reply may append a dict of device-timed phases.
+"""
+from __future__ import annotations
+
+import math
+import time
+import traceback
+from typing import Any, Callable, Dict, List, Optional
+
+from .protocol import WorkerInstruction, validate
+
+
+class TrainingWorker:
+    def __init__(self, comm, master_rank: int, target_model_class: Callable[..., Any], *,
+                 save_base_dir: str = "./savedata/model_", verbose: bool = True,
+                 model_kwargs: Optional[Dict[str, Any]] = None,
+                 fault_hook: Optional[Callable[[Any, int], None]] = None):
+        self.worker_graphs: List[Any] = []
+        self.is_expolore_only = False          # (sic) reference attribute name
+        self.rank = comm.Get_rank()
+        self.comm = comm
+        self.master_rank = master_rank
+        self.target_model_class = target_model_class
+        self.save_base_dir = save_base_dir
+        self.verbose = verbose
+        self.model_kwargs = dict(model_kwargs or {})
+        self.fault_hook = fault_hook           # test hook: f(member, round) may raise / poison
+        self.train_time = 0.0
+        self.explore_time = 0.0
+        self.exploit_time = 0.0
+        self.rounds_seen = 0
+        self.dropped: List[int] = []
+
+    @property
+    def is_explore_only(self) -> bool:
+        return self.is_expolore_only
+
+    def _say(self, *a) -> None:
+        if self.verbose:
+            print(*a, flush=True)
+
+    # ------------------------------------------------------------------ loop
+    def main_loop(self) -> None:
+        while True:
+            data = self.comm.recv(source=self.master_rank)
+            inst = validate(data)
+            if inst == WorkerInstruction.ADD_GRAPHS:
+                self.is_expolore_only = data[3]
+                self.add_graphs(data[1], data[2])
+            elif inst == WorkerInstruction.TRAIN:
+                self.train(data[1], data[2])
+            elif inst == WorkerInstruction.GET:
+                self.comm.send(self.get_all_values(), dest=self.master_rank)
+            elif inst == WorkerInstruction.SET:
+                self.set_values(data[1])
+            elif inst == WorkerInstruction.EXPLORE:
+                self.explore_necessary_graphs()
+            elif inst == WorkerInstruction.GET_PROFILING_INFO:
+                self.comm.send(self.profiling_info(), dest=self.master_rank)
+            elif inst == WorkerInstruction.EXIT:
+                self.shutdown()
+                break
+
+    # ------------------------------------------------------------------ handlers
+    def add_graphs(self, hparam_list: List[dict], id_begin: int) -> None:
+        self._say("[{}]Got {} hparams".format(self.rank, len(hparam_list)))
+        for offset, hparam in enumerate(hparam_list):
+            member = self.target_model_class(id_begin + offset, hparam, self.save_base_dir,
+                                             **self.model_kwargs)
+            self.worker_graphs.append(member)
+
+    def train(self, num_epoches: int, total_epochs: int) -> None:
+        t0 = time.time()
+        failed = []
+        for g in self.worker_graphs:
+            try:
+                if self.fault_hook is not None:
+                    self.fault_hook(g, self.rounds_seen)
+                g.train(num_epoches, total_epochs)
+                self._say("Model {} epoch = {},  acc = {}".format(
+                    g.cluster_id, g.epoches_trained, g.get_accuracy()))
+                acc = g.get_accuracy()
+                if isinstance(acc, float) and math.isnan(acc):
+                    failed.append(g)
+            except Exception:  # member-level failure: drop it, keep the worker alive
+                if self.verbose:
+                    traceback.print_exc()
+                failed.append(g)
+        for g in failed:
+            self._say("Error occured , graph {} removed".format(g.cluster_id))
+            self.dropped.append(g.cluster_id)
+            try:
+                g.drop()
+            finally:
+                self.worker_graphs.remove(g)
+        self.rounds_seen += 1
+        self.train_time += time.time() - t0
+
+    def get_all_values(self) -> List[List[Any]]:
+        return [g.get_values() for g in self.worker_graphs]
+
+    def set_values(self, values_to_set: List[List[Any]]) -> None:
+        t0 = time.time()
+        for v in values_to_set:
+            extras = v[3] if len(v) > 3 else None
+            for g in self.worker_graphs:
+                if g.cluster_id != v[0]:
+                    continue
+                if extras and extras.get("role") == "src":
+                    donate = getattr(g, "donate_state", None)
+                    if donate is not None:
+                        donate(extras)
+                else:
+                    g.set_values(v)
+                    g.need_explore = True
+        self.exploit_time += time.time() - t0
+
+    def explore_necessary_graphs(self) -> None:
+        t0 = time.time()
+        for g in self.worker_graphs:
+            if g.need_explore or self.is_expolore_only:
+                self._say("[{}]Exploring graph {}".format(self.rank, g.cluster_id))
+                g.perturb_hparams()
+                g.need_explore = False
+        self.explore_time += time.time() - t0
+
+    def profiling_info(self) -> List[Any]:
+        device: Dict[str, float] = {}
+        for g in self.worker_graphs:
+            for k, val in getattr(g, "device_times", {}).items():
+                device[k] = device.get(k, 0.0) + float(val)
+        device["exploit_worker"] = self.exploit_time
+        return [self.train_time, self.explore_time, device]
+
+    def shutdown(self) -> None:
+        for g in self.worker_graphs:
+            close = getattr(g, "close", None)
+            if close is not None:
+                close()

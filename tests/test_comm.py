@@ -1,0 +1,116 @@
+"""Control-plane transports: ordering, isolation by source, multi-process TCP and gloo."""
+import multiprocessing as mp
+import os
+import socket
+import threading
+
+import pytest
+
+from distributedtf_b200.parallel.comm_base import CommTimeout
+from distributedtf_b200.parallel.local import LocalFabric
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def test_local_fifo_per_pair_and_copy_semantics():
+    f = LocalFabric(3)
+    m, w1, w2 = f.endpoint(0), f.endpoint(1), f.endpoint(2)
+    payload = {"k": [1, 2]}
+    for i in range(5):
+        m.isend((i, payload), dest=1).wait()
+    w2.send("from2", dest=0)
+    w1.send("from1", dest=0)
+    got = [w1.recv(source=0) for _ in range(5)]
+    assert [g[0] for g in got] == list(range(5))
+    got[0][1]["k"].append(3)
+    assert payload == {"k": [1, 2]}
+    assert m.recv(source=1) == "from1" and m.recv(source=2) == "from2"
+    with pytest.raises(CommTimeout):
+        m.recv(source=1, timeout=0.05)
+    assert (m.Get_rank(), m.Get_size(), w2.rank, w2.size) == (0, 3, 2, 3)
+
+
+def _tcp_worker(port, rank, size):
+    from distributedtf_b200.parallel.tcp import TcpWorkerComm
+    c = TcpWorkerComm("127.0.0.1", port, rank, size)
+    while True:
+        msg = c.recv(source=0)
+        if msg == "stop":
+            break
+        c.send((rank, msg), dest=0)
+    c.close()
+
+
+def test_tcp_star_multi_process():
+    from distributedtf_b200.parallel.tcp import TcpMasterComm
+    size = 4
+    master = TcpMasterComm("127.0.0.1", 0, size)
+    ctx = mp.get_context("spawn")
+    procs = [ctx.Process(target=_tcp_worker, args=(master.port, r, size)) for r in range(1, size)]
+    for p in procs:
+        p.start()
+    master.wait_for_workers()
+    for i in range(20):
+        reqs = [master.isend({"i": i, "blob": b"x" * (1000 * i)}, dest=r) for r in range(1, size)]
+        for r in reqs:
+            r.wait()
+    for r in range(size - 1, 0, -1):        # receive in reverse rank order on purpose
+        for i in range(20):
+            src, msg = master.recv(source=r, timeout=30)
+            assert src == r and msg["i"] == i and len(msg["blob"]) == 1000 * i
+    for r in range(1, size):
+        master.send("stop", dest=r)
+    for p in procs:
+        p.join(20)
+        assert p.exitcode == 0
+    master.close()
+
+
+def _gloo_rank(rank, size, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(size))
+    import torch.distributed as dist
+    from distributedtf_b200.parallel.gloo import GlooComm
+    dist.init_process_group("gloo", rank=rank, world_size=size)
+    c = GlooComm()
+    if rank == 0:
+        for r in range(1, size):
+            c.isend(("hello", r, list(range(100))), dest=r).wait()
+        q.put([c.recv(source=r) for r in range(1, size)])
+    else:
+        msg = c.recv(source=0)
+        c.send((rank, msg[1], sum(msg[2])), dest=0)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_gloo_comm_world_size_3():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_gloo_rank, args=(r, 3, port, q)) for r in range(3)]
+    for p in procs:
+        p.start()
+    out = q.get(timeout=120)
+    for p in procs:
+        p.join(60)
+        assert p.exitcode == 0
+    assert out == [(1, 1, 4950), (2, 2, 4950)]
+
+
+def test_toy_pbt_over_tcp_processes(tmp_path):
+    """BASELINE config 1: toy PBT, 1 master + 1 worker as separate processes."""
+    from distributedtf_b200.config import RunConfig
+    from distributedtf_b200.launch import spawn_tcp
+    cfg = RunConfig(target_model="toy", population_size=2, train_round=3, epochs_per_round=4,
+                    workers=1, transport="tcp", master_port=0, save_root=str(tmp_path / "sd"),
+                    results_file=str(tmp_path / "res.txt"), verbose=False, seed=1).validate()
+    out = spawn_tcp(cfg)
+    assert out["pop_size"] == 2
+    assert (tmp_path / "sd" / "best_model.json").exists()
+    assert "n = 2, pop_size = 2, time = " in (tmp_path / "res.txt").read_text()
