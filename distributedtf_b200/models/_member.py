@@ -1,0 +1,205 @@
+"""Shared machinery of the GPU-resident members (MNIST CNN, CIFAR-10 ResNet).
+
+A member is *persistent*: it is built once (engine + resident dataset), keeps its
+weights / optimizer slots / BN statistics on the device between rounds, and
+writes its checkpoint at the end of every ``train`` call (for resume and for the
+file-copy exploit baseline).  The reference instead rebuilds graph + session and
+re-reads the checkpoint every round for every member
+(``cifar10_main.py:321-330``; ``resnet_run_loop.py:397-398,452,463``).
+"""
+from __future__ import annotations
+
+import math
+import os
+import time
+from typing import Any, Dict, List, Optional
+
+import torch
+
+from .. import ckpt, report
+from ..model_base import ModelBase
+from ..utils.data import BatchIterator, Dataset
+
+
+def pick_device() -> torch.device:
+    if not torch.cuda.is_available():
+        return torch.device("cpu")
+    idx = os.environ.get("DTF_LOCAL_GPU", os.environ.get("LOCAL_RANK", "0"))
+    idx = int(idx) % torch.cuda.device_count()
+    torch.cuda.set_device(idx)
+    return torch.device("cuda", idx)
+
+
+def resolve_engine(engine: str, device: torch.device) -> str:
+    if engine != "auto":
+        return engine
+    if device.type == "cuda":
+        from ..ops import native
+        if native.available():
+            return "native"
+    return "eager"
+
+
+class GpuMember(ModelBase):
+    #: subclasses fill these in
+    train_examples = 0
+    eval_examples = 0
+    csv_fields: List[str] = []
+
+    def __init__(self, cluster_id: int, hparams: Dict[str, Any], save_base_dir: str, *,
+                 engine: str = "auto", dtype: str = "bf16", synthetic: bool = True,
+                 data_dir: str = "./datasets", max_train_steps: Optional[int] = None,
+                 eval_batches: Optional[int] = None, resume: bool = False,
+                 synthetic_mode: str = "random", device: Optional[torch.device] = None, **_):
+        super().__init__(cluster_id, hparams, save_base_dir)
+        self.device = device or pick_device()
+        self.engine_kind = resolve_engine(engine, self.device)
+        self.dtype = dtype
+        self.synthetic = synthetic
+        self.synthetic_mode = synthetic_mode
+        self.data_dir = data_dir
+        self.max_train_steps = max_train_steps
+        self.eval_batches = eval_batches
+        self.device_times: Dict[str, float] = {"train": 0.0, "eval": 0.0, "exploit": 0.0}
+        self.train_set, self.eval_set = self.build_datasets()
+        self.engine = self.build_engine()
+        self._train_iter = BatchIterator(len(self.train_set), int(self.hparams["batch_size"]), True,
+                                         seed=1000 + cluster_id, device=self.device)
+        self.last_images_per_sec = 0.0
+        if resume:
+            self.restore()
+
+    # ------------------------------------------------------------------ to implement
+    def build_datasets(self):
+        raise NotImplementedError
+
+    def build_engine(self):
+        raise NotImplementedError
+
+    def preprocess(self, images_u8: torch.Tensor, training: bool) -> torch.Tensor:
+        raise NotImplementedError
+
+    def csv_row(self, epoch_index: int, accuracy: float) -> Dict[str, Any]:
+        raise NotImplementedError
+
+    def steps_per_epoch(self) -> int:
+        return max(1, self.train_examples // int(self.hparams["batch_size"]))
+
+    # ------------------------------------------------------------------ train / eval
+    def _timed(self, key: str):
+        member = self
+
+        class _T:
+            def __enter__(s):
+                if member.device.type == "cuda":
+                    s.e0 = torch.cuda.Event(enable_timing=True)
+                    s.e1 = torch.cuda.Event(enable_timing=True)
+                    s.e0.record()
+                else:
+                    s.t0 = time.time()
+                return s
+
+            def __exit__(s, *a):
+                if member.device.type == "cuda":
+                    s.e1.record()
+                    s.e1.synchronize()
+                    member.device_times[key] += s.e0.elapsed_time(s.e1) / 1e3
+                else:
+                    member.device_times[key] += time.time() - s.t0
+        return _T()
+
+    def train_one_epoch(self) -> int:
+        bs = int(self.hparams["batch_size"])
+        self._train_iter.set_batch_size(bs)
+        steps = self.steps_per_epoch()
+        if self.max_train_steps is not None:
+            steps = min(steps, self.max_train_steps)
+        with self._timed("train"):
+            t0 = time.time()
+            for _ in range(steps):
+                idx = self._train_iter.next_indices()
+                x = self.preprocess(self.train_set.images[idx], True)
+                self.engine.train_step(x, self.train_set.labels[idx])
+        dt = max(self.device_times["train"], 1e-9)
+        self.last_images_per_sec = steps * bs / max(time.time() - t0, 1e-9)
+        return steps
+
+    def evaluate(self) -> float:
+        bs = int(self.hparams["batch_size"])
+        it = BatchIterator(len(self.eval_set), bs, False, device=self.device)
+        correct = torch.zeros((), dtype=torch.int64, device=self.device)
+        seen = 0
+        with self._timed("eval"):
+            for b, idx in enumerate(it.epoch_batches()):
+                if self.eval_batches is not None and b >= self.eval_batches:
+                    break
+                x = self.preprocess(self.eval_set.images[idx], False)
+                correct += self.engine.eval_batch(x, self.eval_set.labels[idx]).to(torch.int64)
+                seen += int(idx.numel())
+        loss = self.engine.last_loss
+        if loss is not None and not bool(torch.isfinite(loss)):
+            return float("nan")
+        return float(correct.item()) / max(seen, 1)
+
+    def train(self, num_epoch: int, total_epochs: int) -> None:
+        rows = []
+        for e in range(num_epoch):
+            self.train_one_epoch()
+            self.accuracy = self.evaluate()
+            rows.append(self.csv_row(self.epoch_index_for_csv(e), self.accuracy))
+        self.bump_epochs(num_epoch)
+        if math.isnan(self.accuracy):
+            return                      # the worker drops the member; nothing to persist
+        self.save()
+        report.append_csv(os.path.join(self.ensure_dir(), "learning_curve.csv"), self.csv_fields_now(), rows)
+
+    def epoch_index_for_csv(self, e: int) -> int:
+        return self.epoches_trained + e
+
+    def bump_epochs(self, num_epoch: int) -> None:
+        self.epoches_trained += num_epoch
+
+    def csv_fields_now(self) -> List[str]:
+        return list(self.csv_fields)
+
+    # ------------------------------------------------------------------ state
+    def on_hparams_changed(self) -> None:
+        self.engine.set_hparams(self.hparams)
+
+    def save(self) -> None:
+        self.engine.synchronize()
+        ckpt.save_checkpoint(self.ensure_dir(), self.engine.state_tensors(), step=self.engine.step,
+                             optimizer=self.hparams["opt_case"]["optimizer"],
+                             meta={"model": type(self).__name__, "engine": self.engine_kind,
+                                   "epoches_trained": self.epoches_trained})
+
+    def restore(self) -> bool:
+        loaded = ckpt.load_checkpoint(self.save_dir)
+        if loaded is None:
+            return False
+        tensors, index = loaded
+        self.engine.load_state(tensors, index["step"])
+        self.epoches_trained = int(index.get("meta", {}).get("epoches_trained", self.epoches_trained))
+        return True
+
+    def adopt_state(self, extras: Dict[str, Any]) -> None:
+        """Exploit: take over the winner's weights, slots, statistics and step."""
+        if extras.get("src_id") == self.cluster_id:
+            return
+        path = extras.get("path", "file")
+        with self._timed("exploit"):
+            if path == "file":
+                self.restore()          # the master already copied the winner's files here
+            else:
+                from ..parallel import exploit
+                exploit.receive(self, extras)
+
+    def donate_state(self, extras: Dict[str, Any]) -> None:
+        from ..parallel import exploit
+        with self._timed("exploit"):
+            exploit.donate(self, extras)
+
+    def close(self) -> None:
+        closer = getattr(self.engine, "close", None)
+        if closer:
+            closer()
