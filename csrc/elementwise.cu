@@ -1,0 +1,435 @@
+// Non-GEMM kernels of the training step: BN-backward apply (+ residual gradient), the
+// classifier head (final BN + ReLU + global average pool + dense + softmax cross-entropy,
+// forward and backward in one launch), weight packing, the multi-tensor optimizer with the six
+// TF-1.x update rules, step bookkeeping, and input preprocessing.
+//
+// Reference call sites replaced: K3/K4 BN backward, K7 reduce_mean, K8 dense,
+// K9 softmax/argmax/CE/accuracy (resnet_model.py:537-552, resnet_run_loop.py:230-246,303),
+// K10 regularisers (resnet_model.py:111-121), K11 optimizers (resnet_run_loop.py:552-586),
+// K12 loss scaling, K13 LR schedule (resnet_run_loop.py:135-173), K14 preprocessing
+// (cifar10_main.py:71-109).
+#include "common.cuh"
+#include "dtf_b200.h"
+
+namespace dtf {
+
+DTF_DEVINL void bn_consts(const DtfBnRef& bn, int c, float& scale, float& shift, float& mean, float& invstd) {
+    float var;
+    if (bn.use_running) {
+        mean = bn.run_mean[c];
+        var = bn.run_var[c];
+    } else {
+        mean = bn.stats[c] * bn.inv_count;
+        var = fmaxf(bn.stats[bn.channels + c] * bn.inv_count - mean * mean, 0.f);
+    }
+    invstd = rsqrtf(var + bn.eps);
+    scale = bn.gamma[c] * invstd;
+    shift = bn.beta[c] - mean * scale;
+}
+
+// ---------------------------------------------------------------------------------------
+// g[p][c] = p0[c]*t + p1[c]*x + p2[c] (+ res)      BN backward, given (sum t, sum t*xhat)
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+bn_bwd_apply_kernel(const dtf_bf16* __restrict__ t, const dtf_bf16* __restrict__ x,
+                    const dtf_bf16* __restrict__ res, dtf_bf16* __restrict__ out,
+                    DtfBnRef bn, const float* __restrict__ bwd_stats, long long total_vec, int C) {
+    __shared__ float p0[256], p1[256], p2[256];
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+        float scale, shift, mean, invstd;
+        bn_consts(bn, c, scale, shift, mean, invstd);
+        const float mt = bwd_stats[c] * bn.inv_count;
+        const float mtx = bwd_stats[C + c] * bn.inv_count;
+        p0[c] = scale;
+        p1[c] = -scale * invstd * mtx;
+        p2[c] = scale * (mean * invstd * mtx - mt);
+    }
+    __syncthreads();
+    const int cvec = C / 8;
+    for (long long v = blockIdx.x * (long long)blockDim.x + threadIdx.x; v < total_vec;
+         v += (long long)gridDim.x * blockDim.x) {
+        const int cb = static_cast<int>(v % cvec) * 8;
+        float ft[8], fx[8];
+        unpack8(ldg16(t + v * 8), ft);
+        unpack8(ldg16(x + v * 8), fx);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) ft[i] = fmaf(ft[i], p0[cb + i], fmaf(fx[i], p1[cb + i], p2[cb + i]));
+        if (res != nullptr) {
+            float fr[8];
+            unpack8(ldg16(res + v * 8), fr);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) ft[i] += fr[i];
+        }
+        *reinterpret_cast<uint4*>(out + v * 8) = pack8(ft);
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// classifier head: one CTA per image
+// ---------------------------------------------------------------------------------------
+constexpr int kHeadThreads = 256;
+constexpr int kMaxClasses = 16;
+
+__global__ void __launch_bounds__(kHeadThreads)
+head_kernel(const __grid_constant__ DtfHead P) {
+    __shared__ float s_scale[256], s_shift[256], s_mean[256], s_invstd[256];
+    __shared__ float pooled[256], gpool[256], st1[256], st2[256];
+    __shared__ float logits[kMaxClasses], dlog[kMaxClasses];
+    const int n = blockIdx.x;
+    const int C = P.C, HW = P.HW, K = P.classes;
+    const int tid = threadIdx.x;
+    for (int c = tid; c < C; c += kHeadThreads) {
+        if (P.has_bn) bn_consts(P.bn, c, s_scale[c], s_shift[c], s_mean[c], s_invstd[c]);
+        else { s_scale[c] = 1.f; s_shift[c] = 0.f; s_mean[c] = 0.f; s_invstd[c] = 1.f; }
+        pooled[c] = 0.f; st1[c] = 0.f; st2[c] = 0.f;
+    }
+    if (n == 0 && P.has_bn && P.update_running && !P.bn.use_running) {
+        const float m = 1.f / P.bn.inv_count;
+        const float unbias = m > 1.f ? m / (m - 1.f) : 1.f;
+        for (int c = tid; c < C; c += kHeadThreads) {
+            const float mean = P.bn.stats[c] * P.bn.inv_count;
+            const float var = fmaxf(P.bn.stats[C + c] * P.bn.inv_count - mean * mean, 0.f);
+            P.bn.run_mean[c] = P.bn.decay * P.bn.run_mean[c] + (1.f - P.bn.decay) * mean;
+            P.bn.run_var[c] = P.bn.decay * P.bn.run_var[c] + (1.f - P.bn.decay) * var * unbias;
+        }
+    }
+    __syncthreads();
+    const dtf_bf16* xn = P.x + static_cast<size_t>(n) * HW * C;
+    // forward: activation + average pool (thread owns channel c = idx % C for all its elements
+    // when C divides the thread count, which holds for C in {64, 128, 256})
+    {
+        const int c = tid % C;
+        float acc = 0.f;
+        for (int idx = tid; idx < HW * C; idx += kHeadThreads) {
+            const float v = __bfloat162float(xn[idx]);
+            float a = fmaf(v, s_scale[c], s_shift[c]);
+            if (P.has_bn) a = fmaxf(a, 0.f);
+            acc += a;
+        }
+        atomicAdd(&pooled[c], acc);
+    }
+    __syncthreads();
+    const float inv_hw = 1.f / HW;
+    if (tid < K) {
+        float z = P.bias[tid];
+        for (int c = 0; c < C; ++c) z = fmaf(P.w[tid * C + c], pooled[c] * inv_hw, z);
+        logits[tid] = z;
+    }
+    __syncthreads();
+    if (tid == 0) {
+        const int label = P.labels[n];
+        float mx = logits[0];
+        int arg = 0;
+        for (int k = 1; k < K; ++k) if (logits[k] > mx) { mx = logits[k]; arg = k; }
+        float se = 0.f;
+        for (int k = 0; k < K; ++k) se += __expf(logits[k] - mx);
+        const float lse = mx + __logf(se);
+        const float inv_n = 1.f / P.batch;
+        for (int k = 0; k < K; ++k)
+            dlog[k] = (__expf(logits[k] - lse) - (k == label ? 1.f : 0.f)) * inv_n * P.loss_scale;
+        atomicAdd(P.loss_out, (lse - logits[label]) * inv_n);
+        if (arg == label) atomicAdd(P.correct_out, 1);
+    }
+    if (P.logits_out != nullptr && tid < K) P.logits_out[n * K + tid] = logits[tid];
+    if (!P.training) return;
+    __syncthreads();
+    // dense gradients
+    for (int i = tid; i < K * C; i += kHeadThreads) {
+        const int k = i / C, c = i - k * C;
+        atomicAdd(P.dw + i, dlog[k] * pooled[c] * inv_hw);
+    }
+    if (tid < K) atomicAdd(P.db + tid, dlog[tid]);
+    for (int c = tid; c < C; c += kHeadThreads) {
+        float g = 0.f;
+        for (int k = 0; k < K; ++k) g = fmaf(dlog[k], P.w[k * C + c], g);
+        gpool[c] = g * inv_hw;
+    }
+    __syncthreads();
+    {
+        const int c = tid % C;
+        float a1 = 0.f, a2 = 0.f;
+        dtf_bf16* tn = P.t_out + static_cast<size_t>(n) * HW * C;
+        for (int idx = tid; idx < HW * C; idx += kHeadThreads) {
+            const float v = __bfloat162float(xn[idx]);
+            const bool on = !P.has_bn || fmaf(v, s_scale[c], s_shift[c]) > 0.f;
+            const float t = on ? gpool[c] : 0.f;
+            tn[idx] = __float2bfloat16(t);
+            a1 += t;
+            a2 += t * (v - s_mean[c]) * s_invstd[c];
+        }
+        atomicAdd(&st1[c], a1);
+        atomicAdd(&st2[c], a2);
+    }
+    __syncthreads();
+    if (P.bwd_stats_out != nullptr)
+        for (int c = tid; c < C; c += kHeadThreads) {
+            atomicAdd(P.bwd_stats_out + c, st1[c]);
+            atomicAdd(P.bwd_stats_out + C + c, st2[c]);
+        }
+}
+
+// ---------------------------------------------------------------------------------------
+// weight packing: fp32 OHWI master -> bf16 [K/8][N][8] for the forward and dgrad GEMMs
+// ---------------------------------------------------------------------------------------
+DTF_DEVINL void pack_store(const DtfOptSegment& s, dtf_bf16* pack, int local, float w) {
+    // local index inside the OHWI tensor: ((co*taps + tap)*Cin + ci)
+    const int ci = local % s.Cin;
+    const int rest = local / s.Cin;
+    const int tap = rest % s.taps;
+    const int co = rest / s.taps;
+    const dtf_bf16 h = __float2bfloat16(w);
+    if (s.fwd_pack_off >= 0) {
+        const int k = tap * s.Cin + ci;
+        pack[s.fwd_pack_off + ((k >> 3) * s.Cout + co) * 8 + (k & 7)] = h;
+    }
+    if (s.dgrad_pack_off >= 0) {
+        const int k = tap * s.Cout + co;
+        pack[s.dgrad_pack_off + ((k >> 3) * s.Cin + ci) * 8 + (k & 7)] = h;
+    }
+}
+
+__global__ void __launch_bounds__(256)
+pack_weights_kernel(const float* __restrict__ params, dtf_bf16* __restrict__ pack,
+                    const DtfOptSegment* __restrict__ segs, const int2* __restrict__ chunks) {
+    const int2 ch = chunks[blockIdx.x];
+    const DtfOptSegment s = segs[ch.x];
+    if (!s.pack) return;
+    for (int i = threadIdx.x; i < DTF_OPT_CHUNK; i += blockDim.x) {
+        const int local = ch.y + i;
+        if (local < s.count) pack_store(s, pack, local, params[s.offset + local]);
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// multi-tensor optimizer: TF-1.x Apply{GradientDescent,Momentum,Adagrad,Adadelta,Adam,RMSProp}
+// over the flat arena; device-resident hyper-parameters and LR schedule; regulariser gradient
+// folded in; optional gradient scale (1/loss_scale, 1/world); emits the bf16 packed weights.
+// ---------------------------------------------------------------------------------------
+DTF_DEVINL float schedule_lr(const DtfHparams& hp, long long step) {
+    // tf.train.piecewise_constant: values[0] for step <= b0, values[i] for b(i-1) < step <= b(i)
+    int i = 0;
+    while (i < hp.n_boundaries && step > hp.boundaries[i]) ++i;
+    return hp.lr_values[i];
+}
+
+DTF_DEVINL float apply_rule(const DtfHparams& hp, float lr, float lr_adam, float w, float g, float& s0, float& s1) {
+    switch (hp.optimizer) {
+        case DTF_OPT_GD:
+            return w - lr * g;
+        case DTF_OPT_MOMENTUM:
+            s0 = hp.momentum * s0 + g;
+            return w - lr * s0;
+        case DTF_OPT_ADAGRAD:
+            s0 += g * g;
+            return w - lr * g * rsqrtf(s0);
+        case DTF_OPT_ADADELTA: {
+            s0 = 0.95f * s0 + 0.05f * g * g;
+            const float upd = sqrtf(s1 + 1e-8f) * rsqrtf(s0 + 1e-8f) * g;
+            s1 = 0.95f * s1 + 0.05f * upd * upd;
+            return w - lr * upd;
+        }
+        case DTF_OPT_ADAM:
+            s0 = 0.9f * s0 + 0.1f * g;
+            s1 = 0.999f * s1 + 0.001f * g * g;
+            return w - lr_adam * s0 / (sqrtf(s1) + 1e-8f);
+        default: {  // DTF_OPT_RMSPROP
+            s0 = hp.grad_decay * s0 + (1.f - hp.grad_decay) * g * g;
+            s1 = hp.momentum * s1 + lr * g * rsqrtf(s0 + 1e-10f);
+            return w - s1;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256)
+optimizer_kernel(float* __restrict__ params, const float* __restrict__ grads,
+                 float* __restrict__ slot0, float* __restrict__ slot1, dtf_bf16* __restrict__ pack,
+                 const DtfOptSegment* __restrict__ segs, const int2* __restrict__ chunks,
+                 const DtfHparams* __restrict__ hp_ptr, const long long* __restrict__ step_ptr,
+                 float grad_scale) {
+    __shared__ DtfHparams hp;
+    if (threadIdx.x == 0) hp = *hp_ptr;
+    __syncthreads();
+    const long long step = *step_ptr;             // 1-based count of THIS update (dtf_step_begin bumped it)
+    const float lr = schedule_lr(hp, step - 1);   // TF evaluates the schedule at the pre-increment global_step
+    float lr_adam = lr;
+    if (hp.optimizer == DTF_OPT_ADAM) {
+        const float t = static_cast<float>(step);
+        lr_adam = lr * sqrtf(1.f - powf(0.999f, t)) / (1.f - powf(0.9f, t));
+    }
+    const int2 ch = chunks[blockIdx.x];
+    const DtfOptSegment s = segs[ch.x];
+    const float gs = grad_scale * hp.inv_loss_scale;
+    for (int i = threadIdx.x; i < DTF_OPT_CHUNK; i += blockDim.x) {
+        const int local = ch.y + i;
+        if (local >= s.count) break;
+        const int idx = s.offset + local;
+        const float w = params[idx];
+        float g = grads[idx] * gs;
+        if (s.regularized) {
+            if (hp.regularizer == DTF_REG_L1 || hp.regularizer == DTF_REG_L1_L2)
+                g += hp.weight_decay * (w > 0.f ? 1.f : (w < 0.f ? -1.f : 0.f));
+            if (hp.regularizer == DTF_REG_L2 || hp.regularizer == DTF_REG_L1_L2) g += hp.weight_decay * w;
+        }
+        float s0 = slot0[idx], s1 = slot1[idx];
+        const float nw = apply_rule(hp, lr, lr_adam, w, g, s0, s1);
+        params[idx] = nw;
+        slot0[idx] = s0;
+        slot1[idx] = s1;
+        if (s.pack) pack_store(s, pack, local, nw);
+    }
+}
+
+// zero the per-step accumulators (gradient arena, BN statistics, loss/metric cells) and bump
+// the device-resident step counter — one launch at the start of every step
+__global__ void __launch_bounds__(256)
+step_begin_kernel(float4* __restrict__ zero, long long n_vec, long long* __restrict__ step_ptr, int bump) {
+    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n_vec;
+         i += (long long)gridDim.x * blockDim.x)
+        zero[i] = z;
+    if (bump && blockIdx.x == 0 && threadIdx.x == 0) *step_ptr += 1;
+}
+
+__global__ void fill_kernel(float* __restrict__ p, long long n, float v) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+        p[i] = v;
+}
+
+// ---------------------------------------------------------------------------------------
+// input preprocessing: uint8 NHWC -> bf16 NHWC with channels padded to 8
+//   mode 0: plain cast (MNIST: pixels stay 0..255)
+//   mode 1: per-image standardisation (CIFAR eval)
+//   mode 2: pad 4 + random crop + random flip + standardisation (CIFAR train)
+// one CTA per image
+// ---------------------------------------------------------------------------------------
+DTF_DEVINL uint64_t splitmix64(uint64_t x) {
+    x += 0x9E3779B97F4A7C15ull;
+    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+    x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+    return x ^ (x >> 31);
+}
+
+__global__ void __launch_bounds__(256)
+preprocess_kernel(const uint8_t* __restrict__ images, const int* __restrict__ indices,
+                  dtf_bf16* __restrict__ out, const int* __restrict__ crop_flip,
+                  int H, int W, int C, int mode, unsigned long long seed, unsigned long long counter) {
+    __shared__ float red[2][8];
+    __shared__ float s_mean, s_inv;
+    const int n = blockIdx.x;
+    const int src_idx = indices ? indices[n] : n;
+    const uint8_t* img = images + static_cast<size_t>(src_idx) * H * W * C;
+    int oy = 4, ox = 4, flip = 0;
+    if (mode == 2) {
+        if (crop_flip) { oy = crop_flip[3 * n]; ox = crop_flip[3 * n + 1]; flip = crop_flip[3 * n + 2]; }
+        else {
+            const uint64_t r = splitmix64(seed ^ splitmix64(counter + n));
+            oy = static_cast<int>(r % 9); ox = static_cast<int>((r >> 16) % 9); flip = static_cast<int>((r >> 32) & 1);
+        }
+    }
+    const int total = H * W * C;
+    float s = 0.f, ss = 0.f;
+    if (mode != 0) {
+        for (int i = threadIdx.x; i < total; i += blockDim.x) {
+            const int c = i % C, p = i / C, x = p % W, y = p / W;
+            const int sx = (flip ? (W - 1 - x) : x) + ox - 4, sy = y + oy - 4;
+            const float v = (mode == 2 && (sx < 0 || sx >= W || sy < 0 || sy >= H)) ? 0.f
+                            : static_cast<float>(img[(sy * W + sx) * C + c]);
+            s += v; ss += v * v;
+        }
+        for (int o = 16; o; o >>= 1) { s += __shfl_xor_sync(0xffffffffu, s, o); ss += __shfl_xor_sync(0xffffffffu, ss, o); }
+        if ((threadIdx.x & 31) == 0) { red[0][threadIdx.x >> 5] = s; red[1][threadIdx.x >> 5] = ss; }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            float a = 0.f, b = 0.f;
+            for (int w = 0; w < 8; ++w) { a += red[0][w]; b += red[1][w]; }
+            const float mean = a / total;
+            const float var = fmaxf(b / total - mean * mean, 0.f);
+            s_mean = mean;
+            s_inv = 1.f / fmaxf(sqrtf(var), rsqrtf(static_cast<float>(total)));
+        }
+        __syncthreads();
+    }
+    dtf_bf16* o = out + static_cast<size_t>(n) * H * W * 8;
+    for (int p = threadIdx.x; p < H * W; p += blockDim.x) {
+        const int x = p % W, y = p / W;
+        const int sx = (mode == 2) ? ((flip ? (W - 1 - x) : x) + ox - 4) : x;
+        const int sy = (mode == 2) ? (y + oy - 4) : y;
+        const bool inb = sx >= 0 && sx < W && sy >= 0 && sy < H;
+        float f[8];
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+            float v = 0.f;
+            if (c < C) {
+                v = inb ? static_cast<float>(img[(sy * W + sx) * C + c]) : 0.f;
+                if (mode != 0) v = (v - s_mean) * s_inv;
+            }
+            f[c] = v;
+        }
+        *reinterpret_cast<uint4*>(o + p * 8) = pack8(f);
+    }
+}
+
+}  // namespace dtf
+
+// =========================================================================================
+// host launchers (C ABI)
+// =========================================================================================
+#define DTF_CHECK_LAUNCH() (cudaGetLastError() == cudaSuccess ? DTF_OK : DTF_ERR_CUDA)
+
+extern "C" int dtf_bn_bwd_apply(const dtf_bf16* t, const dtf_bf16* x, const dtf_bf16* res, dtf_bf16* out,
+                                const DtfBnRef* bn, const float* bwd_stats, long long pixels, int C,
+                                cudaStream_t stream) {
+    if (C % 8 != 0 || C > 256) return DTF_ERR_SHAPE;
+    const long long total_vec = pixels * (C / 8);
+    long long blocks = (total_vec + 255) / 256;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    dtf::bn_bwd_apply_kernel<<<static_cast<int>(blocks), 256, 0, stream>>>(t, x, res, out, *bn, bwd_stats, total_vec, C);
+    return DTF_CHECK_LAUNCH();
+}
+
+extern "C" int dtf_head(const DtfHead* p, cudaStream_t stream) {
+    if (p->C > 256 || p->classes > dtf::kMaxClasses || (256 % p->C) != 0) return DTF_ERR_SHAPE;
+    dtf::head_kernel<<<p->batch, dtf::kHeadThreads, 0, stream>>>(*p);
+    return DTF_CHECK_LAUNCH();
+}
+
+extern "C" int dtf_pack_weights(const float* params, dtf_bf16* pack, const DtfOptSegment* segs,
+                                const int* chunks, int n_chunks, cudaStream_t stream) {
+    dtf::pack_weights_kernel<<<n_chunks, 256, 0, stream>>>(params, pack, segs, reinterpret_cast<const int2*>(chunks));
+    return DTF_CHECK_LAUNCH();
+}
+
+extern "C" int dtf_optimizer_step(float* params, const float* grads, float* slot0, float* slot1, dtf_bf16* pack,
+                                  const DtfOptSegment* segs, const int* chunks, int n_chunks,
+                                  const DtfHparams* hp, const long long* step, float grad_scale,
+                                  cudaStream_t stream) {
+    dtf::optimizer_kernel<<<n_chunks, 256, 0, stream>>>(params, grads, slot0, slot1, pack, segs,
+                                                        reinterpret_cast<const int2*>(chunks), hp, step, grad_scale);
+    return DTF_CHECK_LAUNCH();
+}
+
+extern "C" int dtf_step_begin(float* zero_base, long long zero_floats, long long* step, int bump, cudaStream_t stream) {
+    if (zero_floats % 4 != 0 || (reinterpret_cast<uintptr_t>(zero_base) & 15) != 0) return DTF_ERR_ARG;
+    const long long n_vec = zero_floats / 4;
+    long long blocks = (n_vec + 255) / 256;
+    if (blocks > 148 * 4) blocks = 148 * 4;
+    if (blocks < 1) blocks = 1;
+    dtf::step_begin_kernel<<<static_cast<int>(blocks), 256, 0, stream>>>(reinterpret_cast<float4*>(zero_base), n_vec, step, bump);
+    return DTF_CHECK_LAUNCH();
+}
+
+extern "C" int dtf_fill(float* p, long long n, float v, cudaStream_t stream) {
+    long long blocks = (n + 255) / 256;
+    if (blocks > 148 * 4) blocks = 148 * 4;
+    if (blocks < 1) blocks = 1;
+    dtf::fill_kernel<<<static_cast<int>(blocks), 256, 0, stream>>>(p, n, v);
+    return DTF_CHECK_LAUNCH();
+}
+
+extern "C" int dtf_preprocess(const uint8_t* images, const int* indices, dtf_bf16* out, const int* crop_flip,
+                              int n, int H, int W, int C, int mode, unsigned long long seed,
+                              unsigned long long counter, cudaStream_t stream) {
+    if (C > 8 || n < 1) return DTF_ERR_SHAPE;
+    dtf::preprocess_kernel<<<n, 256, 0, stream>>>(images, indices, out, crop_flip, H, W, C, mode, seed, counter);
+    return DTF_CHECK_LAUNCH();
+}

@@ -137,6 +137,8 @@ def _block(cfg, ops, x, cin, filters, fout, stride, projection):
         chain = [(cin, filters, 3, stride), (filters, filters, 3, 1)]
     for j, (ci, co, k, s) in enumerate(chain):
         last = j == len(chain) - 1
+        if last and v2:
+            ops.fused_add_next = True      # engine: conv epilogue adds the shortcut before rounding
         x = ops.conv(x, ci, co, k, s)
         if v2:
             if not last:
@@ -198,12 +200,18 @@ def batch_norm(x: torch.Tensor, gamma, beta, mean, var, training: bool,
 
 class _ExecOps(_Ops):
     def __init__(self, cfg, params: Dict[str, torch.Tensor], x: torch.Tensor, training: bool,
-                 taps: Optional[Dict[str, torch.Tensor]] = None):
+                 taps: Optional[Dict[str, torch.Tensor]] = None, emulate_bf16: bool = False):
         self.cfg, self.p, self.x, self.training = cfg, params, x, training
-        self._bn = self._conv = 0
+        self._bn = self._conv = self._add = 0
         self.taps = taps
+        self.emulate_bf16 = emulate_bf16
 
     def _tap(self, name, t):
+        if self.emulate_bf16 and name.startswith("conv") and getattr(self, "fused_add_next", False):
+            self.fused_add_next = False
+        elif self.emulate_bf16 and (name.startswith("conv") or name.startswith("add")):
+            # the native engine stores these tensors in bf16: round with a straight-through gradient
+            t = t + (t.bfloat16().float() - t).detach()
         if self.taps is not None:
             self.taps[name] = t
         return t
@@ -213,7 +221,11 @@ class _ExecOps(_Ops):
     def conv(self, x, cin, cout, k, s):
         name = f"conv{self._conv}"
         self._conv += 1
-        return self._tap(name, conv2d_fixed_padding(x, self.p[name + "/kernel"].to(x.dtype), s))
+        w = self.p[name + "/kernel"].to(x.dtype)
+        if self.emulate_bf16:   # bf16 operands, fp32 accumulation (activations after BN+ReLU are re-rounded)
+            w = w + (w.bfloat16().float() - w).detach()
+            x = x + (x.bfloat16().float() - x).detach()
+        return self._tap(name, conv2d_fixed_padding(x, w, s))
 
     def bn(self, x, c):
         name = f"bn{self._bn}"
@@ -225,7 +237,11 @@ class _ExecOps(_Ops):
 
     def relu(self, x): return F.relu(x)
     def maxpool(self, x, k, s): return F.max_pool2d(x, k, s, padding=(k - 1) // 2)
-    def add(self, a, b): return a + b
+    def add(self, a, b):
+        name = f"add{self._add}"
+        self._add += 1
+        return self._tap(name, a + b)
+
     def mean_pool(self, x): return x.float().mean(dim=(2, 3))
 
     def dense(self, x, cin, cout):
@@ -233,9 +249,12 @@ class _ExecOps(_Ops):
 
 
 def forward(cfg: ResNetConfig, params: Dict[str, torch.Tensor], images_nchw: torch.Tensor,
-            training: bool, taps: Optional[Dict[str, torch.Tensor]] = None) -> torch.Tensor:
-    """Logits ``[N, num_classes]`` (fp32).  ``params`` maps ``ParamSpec.name`` -> tensor."""
-    return _walk(cfg, _ExecOps(cfg, params, images_nchw, training, taps)).float()
+            training: bool, taps: Optional[Dict[str, torch.Tensor]] = None,
+            emulate_bf16: bool = False) -> torch.Tensor:
+    """Logits ``[N, num_classes]`` (fp32).  ``params`` maps ``ParamSpec.name`` -> tensor.
+    ``emulate_bf16`` rounds conv operands and stored activations to bf16 (straight-through
+    gradients), reproducing where the native engine rounds."""
+    return _walk(cfg, _ExecOps(cfg, params, images_nchw, training, taps, emulate_bf16)).float()
 
 
 def init_params(cfg: ResNetConfig, initializer: str, seed: int = 0,

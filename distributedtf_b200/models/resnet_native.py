@@ -1,0 +1,547 @@
+"""The B200 training engine for the CIFAR ResNet (v2, building blocks).
+
+Everything a step does runs in hand-written sm_100a kernels (``csrc/``): the input
+preprocessing, every convolution forward / dgrad / wgrad as a tcgen05 implicit GEMM with
+BatchNorm+ReLU applied in the operand gather and BN statistics / residual add in the
+epilogue, the classifier head (final BN + ReLU + pool + dense + softmax-CE, fwd+bwd in one
+launch), the BN-backward apply, and a single multi-tensor optimizer launch that also
+re-emits the bf16 GEMM-ready weights.  The ~110 launches of a step are captured once per
+batch size in a CUDA graph; hyper-parameters, LR schedule and the step counter live in
+device memory, so explore / exploit never force a re-capture.
+
+Member state is one flat device arena::
+
+    [ hparams | step | params fp32 | slot0 | slot1 | BN moving stats ]   <- exploit copies this
+    [ bf16 packed weights (fwd + dgrad layouts) ]                        <- derived
+    [ grads fp32 | BN batch statistics | loss, correct ]                 <- zeroed every step
+
+Parity: the architecture and numerics follow reference ``resnet/resnet_model.py`` (block
+wiring :127-212, stage layout :323-359, head :537-552) and ``resnet_run_loop.py:176-354``
+(loss, optimizer, BN update ops); verified against the torch oracle in ``models/resnet.py``,
+which itself reproduces the reference's golden fixtures.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+from dataclasses import dataclass
+from typing import Any, Dict, List, Optional, Tuple
+
+import torch
+
+from ..ops import native, reference
+from . import resnet
+
+IMG_C = 8          # image channels padded 3 -> 8 (one 16-byte chunk)
+MAX_BATCH = 256    # explore keeps batch_size in [65, 256]
+
+
+@dataclass
+class ConvL:
+    name: str
+    cin: int          # storage Cin (conv0: 8)
+    cout: int
+    k: int
+    stride: int
+    hin: int
+    hout: int
+    w_off: int = 0            # element offset in params
+    fwd_pack: int = 0         # element offset in pack arena
+    dgrad_pack: int = -1
+    seg: int = 0
+
+
+@dataclass
+class BnL:
+    name: str
+    c: int
+    h: int                    # spatial size of the normalised tensor
+    p_off: int = 0            # offset of (beta, gamma) in params / grads
+    stat_off: int = 0         # offset of (sum, sumsq) in the stats region
+    run_off: int = 0          # offset of (mean, var) in the running region
+
+
+@dataclass
+class Block:
+    bn1: BnL
+    conv1: ConvL
+    bn2: BnL
+    conv2: ConvL
+    proj: Optional[ConvL]
+    cin: int
+    cout: int
+    hin: int
+    hout: int
+    stride: int
+
+
+def _align(n: int, a: int = 256) -> int:
+    return (n + a - 1) // a * a
+
+
+class NativeResNetEngine:
+    kind = "native"
+
+    def __init__(self, cfg: resnet.ResNetConfig, hparams: Dict[str, Any], device, *, seed: int = 0,
+                 dtype: str = "bf16", max_batch: int = MAX_BATCH, use_graphs: bool = True,
+                 arena_alloc=None):
+        if cfg.resnet_version != 2 or cfg.bottleneck or cfg.first_pool_size:
+            raise NotImplementedError("native engine covers the CIFAR configuration: ResNet v2, building blocks")
+        if dtype != "bf16":
+            raise NotImplementedError("native engine computes in bf16 with fp32 master weights / accumulation")
+        native.require()
+        self.cfg = cfg
+        self.device = torch.device(device)
+        self.max_batch = max_batch
+        self.use_graphs = use_graphs
+        self.hp: Dict[str, Any] = {}
+        self._graphs: Dict[Tuple[str, int], torch.cuda.CUDAGraph] = {}
+        self._build_plan()
+        self._alloc(arena_alloc)
+        self._init_params(hparams.get("initializer", "None"), seed)
+        self.set_hparams(hparams, reset_slots=True)
+        self.last_loss: Optional[torch.Tensor] = None
+        self.launches_per_step = 0
+        self._pp_counter = 0
+        self._seed = seed
+
+    # ------------------------------------------------------------------ plan
+    def _build_plan(self) -> None:
+        cfg = self.cfg
+        self.convs: List[ConvL] = []
+        self.bns: List[BnL] = []
+        self.blocks: List[Block] = []
+        size = cfg.image_size
+
+        def conv(cin, cout, k, s, hin):
+            c = ConvL(f"conv{len(self.convs)}", cin, cout, k, s, hin, hin // s)
+            self.convs.append(c)
+            return c
+
+        def bn(c, h):
+            b = BnL(f"bn{len(self.bns)}", c, h)
+            self.bns.append(b)
+            return b
+
+        self.conv0 = conv(IMG_C, cfg.num_filters, cfg.kernel_size, cfg.conv_stride, size)
+        h = size // cfg.conv_stride
+        cin = cfg.num_filters
+        for i, nblocks in enumerate(cfg.block_sizes):
+            filters = cfg.num_filters * (2 ** i)
+            for b in range(nblocks):
+                stride = cfg.block_strides[i] if b == 0 else 1
+                bn1 = bn(cin, h)
+                proj = conv(cin, filters, 1, stride, h) if b == 0 else None
+                c1 = conv(cin, filters, 3, stride, h)
+                bn2 = bn(filters, h // stride)
+                c2 = conv(filters, filters, 3, 1, h // stride)
+                self.blocks.append(Block(bn1, c1, bn2, c2, proj, cin, filters, h, h // stride, stride))
+                cin = filters
+                h //= stride
+        self.bn_final = bn(cin, h)
+        self.final_c, self.final_h = cin, h
+        # ---- flat parameter layout: conv kernels | (beta, gamma) per BN | dense W | dense b
+        off = 0
+        pack = 0
+        self.segments: List[native.OptSegment] = []
+        for c in self.convs:
+            c.w_off = off
+            n = c.cout * c.k * c.k * c.cin
+            kch = c.k * c.k * c.cin // 8
+            c.fwd_pack = pack
+            pack += _align(((kch + 1) & ~1) * c.cout * 8, 128)
+            if c is not self.conv0:
+                kchd = c.k * c.k * c.cout // 8
+                c.dgrad_pack = pack
+                pack += _align(((kchd + 1) & ~1) * c.cin * 8, 128)
+            c.seg = len(self.segments)
+            self.segments.append(native.OptSegment(off, n, 1, 1, c.cout, c.k * c.k, c.cin, c.fwd_pack,
+                                                   c.dgrad_pack))
+            off += n
+        self.n_conv_params = off
+        stat = run = 0
+        for b in self.bns:
+            b.p_off, b.stat_off, b.run_off = off, stat, run
+            self.segments.append(native.OptSegment(off, 2 * b.c, 0, 0, 0, 0, 0, -1, -1))
+            off += 2 * b.c
+            stat += 2 * b.c
+            run += 2 * b.c
+        self.dense_w_off = off
+        self.segments.append(native.OptSegment(off, cfg.num_classes * self.final_c, 0, 0, 0, 0, 0, -1, -1))
+        off += cfg.num_classes * self.final_c
+        self.dense_b_off = off
+        self.segments.append(native.OptSegment(off, cfg.num_classes, 0, 0, 0, 0, 0, -1, -1))
+        off += cfg.num_classes
+        self.n_params = off
+        self.n_stats, self.n_running, self.n_pack = stat, run, pack
+        chunks: List[int] = []
+        for si, s in enumerate(self.segments):
+            for start in range(0, s.count, native.OPT_CHUNK):
+                chunks += [si, start]
+        self.n_chunks = len(chunks) // 2
+        self._chunks_host = torch.tensor(chunks, dtype=torch.int32)
+
+    # ------------------------------------------------------------------ memory
+    def _alloc(self, arena_alloc) -> None:
+        dev = self.device
+        P = _align(self.n_params * 4) // 4
+        self.P_pad = P
+        HP = _align(C.sizeof(native.Hparams))
+        off = {}
+        cur = 0
+        for name, nbytes in [("hparams", HP), ("step", 256), ("params", P * 4), ("slot0", P * 4), ("slot1", P * 4),
+                             ("running", _align(self.n_running * 4))]:
+            off[name] = cur
+            cur += _align(nbytes)
+        self.state_bytes_total = cur
+        alloc = arena_alloc or (lambda n: torch.zeros(n, dtype=torch.uint8, device=dev))
+        self.state = alloc(cur)                       # the region exploit copies
+        self._state_off = off
+        v = self.state
+
+        def view(name, dtype, count):
+            esz = torch.empty(0, dtype=dtype).element_size()
+            return v[off[name]: off[name] + count * esz].view(dtype)
+
+        self.hp_dev = v[off["hparams"]: off["hparams"] + C.sizeof(native.Hparams)]
+        self.step_dev = view("step", torch.int64, 1)
+        self.params = view("params", torch.float32, P)
+        self.slot0 = view("slot0", torch.float32, P)
+        self.slot1 = view("slot1", torch.float32, P)
+        self.running = view("running", torch.float32, self.n_running)
+        self.pack = torch.zeros(self.n_pack, dtype=torch.bfloat16, device=dev)
+        # per-step zeroed region: grads | batch statistics | loss, correct
+        zfloats = P + _align(self.n_stats * 4) // 4 + 64
+        self.zero_region = torch.zeros(zfloats, dtype=torch.float32, device=dev)
+        self.grads = self.zero_region[:P]
+        s0 = P
+        self.stats = self.zero_region[s0: s0 + self.n_stats]
+        m0 = s0 + _align(self.n_stats * 4) // 4
+        self.loss_cell = self.zero_region[m0: m0 + 1]
+        self.correct_cell = self.zero_region[m0 + 1: m0 + 2].view(torch.int32)
+        # evaluation accumulators live outside the zeroed region
+        self.eval_cells = torch.zeros(4, dtype=torch.float32, device=dev)
+        self.segs_dev = native.struct_to_tensor((native.OptSegment * len(self.segments))(*self.segments), dev)
+        self.chunks_dev = self._chunks_host.to(dev)
+        # static IO + activations, sized for the largest batch so pointers never move
+        mb = self.max_batch
+        cfg = self.cfg
+        S = cfg.image_size
+        self.in_u8 = torch.zeros(mb, S, S, cfg.in_channels, dtype=torch.uint8, device=dev)
+        self.labels = torch.zeros(mb, dtype=torch.int32, device=dev)
+        self.image = torch.zeros(mb, S, S, IMG_C, dtype=torch.bfloat16, device=dev)
+
+        def act(h, c):
+            return torch.empty(mb, h, h, c, dtype=torch.bfloat16, device=dev)
+
+        self.r0 = act(self.conv0.hout, self.conv0.cout)
+        self.acts = []
+        for b in self.blocks:
+            self.acts.append({"c1": act(b.hout, b.cout), "out": act(b.hout, b.cout),
+                              "sc": act(b.hout, b.cout) if b.proj else None})
+        big = max(b.hin * b.hin * b.cin for b in self.blocks)
+        self.gbuf = [torch.empty(mb * big, dtype=torch.bfloat16, device=dev) for _ in range(2)]
+        self.tbuf = [torch.empty(mb * big, dtype=torch.bfloat16, device=dev) for _ in range(2)]
+        self.logits = torch.zeros(mb, cfg.num_classes, dtype=torch.float32, device=dev)
+
+    # ------------------------------------------------------------------ params
+    def conv_weight(self, c: ConvL) -> torch.Tensor:
+        return self.params[c.w_off: c.w_off + c.cout * c.k * c.k * c.cin].view(c.cout, c.k, c.k, c.cin)
+
+    def bn_view(self, b: BnL, base: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+        return base[b.p_off: b.p_off + b.c], base[b.p_off + b.c: b.p_off + 2 * b.c]      # (beta, gamma)
+
+    def _init_params(self, initializer: str, seed: int) -> None:
+        self.load_named_params(resnet.init_params(self.cfg, initializer, seed))
+
+    @torch.no_grad()
+    def load_named_params(self, named: Dict[str, torch.Tensor]) -> None:
+        """Adopt parameters in the oracle's naming/layout (``models/resnet.py``)."""
+        dev = self.device
+        for i, c in enumerate(self.convs):
+            w = named[f"conv{i}/kernel"].to(dev, torch.float32)
+            if c is self.conv0:
+                full = torch.zeros(c.cout, c.k, c.k, c.cin, device=dev)
+                full[..., : w.shape[-1]] = w
+                w = full
+            self.conv_weight(c).copy_(w)
+        for i, b in enumerate(self.bns):
+            beta, gamma = self.bn_view(b, self.params)
+            beta.copy_(named[f"bn{i}/beta"].to(dev))
+            gamma.copy_(named[f"bn{i}/gamma"].to(dev))
+            self.running[b.run_off: b.run_off + b.c].copy_(named[f"bn{i}/moving_mean"].to(dev))
+            self.running[b.run_off + b.c: b.run_off + 2 * b.c].copy_(named[f"bn{i}/moving_variance"].to(dev))
+        n = self.cfg.num_classes * self.final_c
+        self.params[self.dense_w_off: self.dense_w_off + n].copy_(named["dense/kernel"].to(dev).reshape(-1))
+        self.params[self.dense_b_off: self.dense_b_off + self.cfg.num_classes].copy_(named["dense/bias"].to(dev))
+        self.repack()
+
+    def export_named(self, base: Optional[torch.Tensor] = None) -> Dict[str, torch.Tensor]:
+        """Parameters (or, with ``base=self.grads``, gradients) in the oracle's naming."""
+        base = self.params if base is None else base
+        out = {}
+        for i, c in enumerate(self.convs):
+            w = base[c.w_off: c.w_off + c.cout * c.k * c.k * c.cin].view(c.cout, c.k, c.k, c.cin)
+            out[f"conv{i}/kernel"] = (w[..., : self.cfg.in_channels] if c is self.conv0 else w).clone()
+        for i, b in enumerate(self.bns):
+            beta, gamma = self.bn_view(b, base)
+            out[f"bn{i}/beta"], out[f"bn{i}/gamma"] = beta.clone(), gamma.clone()
+            if base is self.params:
+                out[f"bn{i}/moving_mean"] = self.running[b.run_off: b.run_off + b.c].clone()
+                out[f"bn{i}/moving_variance"] = self.running[b.run_off + b.c: b.run_off + 2 * b.c].clone()
+        n = self.cfg.num_classes * self.final_c
+        out["dense/kernel"] = base[self.dense_w_off: self.dense_w_off + n].view(self.cfg.num_classes, -1).clone()
+        out["dense/bias"] = base[self.dense_b_off: self.dense_b_off + self.cfg.num_classes].clone()
+        return out
+
+    def repack(self) -> None:
+        native.pack_weights(self.params, self.pack, self.segs_dev, self.chunks_dev, self.n_chunks)
+
+    # ------------------------------------------------------------------ hparams
+    def set_hparams(self, hp: Dict[str, Any], reset_slots: bool = False) -> None:
+        prev = self.hp.get("opt_case", {}).get("optimizer") if self.hp else None
+        self.hp = hp
+        oc = hp["opt_case"]
+        h = native.Hparams()
+        h.optimizer = reference.OPT_IDS[oc["optimizer"]]
+        h.regularizer = reference.REG_IDS[hp.get("regularizer", "None")]
+        h.momentum = float(oc.get("momentum", 0.0))
+        h.grad_decay = float(oc.get("grad_decay", 0.9))
+        h.weight_decay = float(hp.get("weight_decay", 0.0))
+        h.inv_loss_scale = 1.0
+        bounds, values = reference.cifar_lr_schedule(hp)
+        if len(bounds) > native.MAX_LR_BOUNDARIES:
+            raise ValueError("LR schedule has too many boundaries for the device block")
+        h.n_boundaries = len(bounds)
+        h.batch_size = int(hp["batch_size"])
+        for i, b in enumerate(bounds):
+            h.boundaries[i] = int(b)
+        for i, v in enumerate(values):
+            h.lr_values[i] = float(v)
+        self._hp_struct = h
+        self.hp_dev.copy_(native.struct_to_tensor(h, "cpu").to(self.device, non_blocking=True))
+        if reset_slots or prev != oc["optimizer"]:
+            a, b = reference.slot_init_values(oc["optimizer"])
+            native.fill(self.slot0, a)
+            native.fill(self.slot1, b)
+
+    @property
+    def step(self) -> int:
+        return int(self.step_dev.item())
+
+    # ------------------------------------------------------------------ kernels of one step
+    def _bn(self, b: BnL, nb: int, training: bool) -> native.BnRef:
+        beta, gamma = self.bn_view(b, self.params)
+        return native.bn_ref(b.c, nb * b.h * b.h, stats=self.stats[b.stat_off: b.stat_off + 2 * b.c],
+                             gamma=gamma, beta=beta, run_mean=self.running[b.run_off: b.run_off + b.c],
+                             run_var=self.running[b.run_off + b.c: b.run_off + 2 * b.c],
+                             use_running=not training)
+
+    def _stats_out(self, b: Optional[BnL]):
+        return None if b is None else self.stats[b.stat_off: b.stat_off + 2 * b.c]
+
+    def _bwd_stats(self, b: BnL) -> torch.Tensor:
+        return self.grads[b.p_off: b.p_off + 2 * b.c]
+
+    def _wpk(self, c: ConvL, dgrad: bool = False) -> torch.Tensor:
+        return self.pack[(c.dgrad_pack if dgrad else c.fwd_pack):]
+
+    def _fwd_conv(self, c: ConvL, src, out, nb, *, bn: Optional[BnL], training, update, res=None,
+                  stats_for: Optional[BnL] = None) -> None:
+        g = native.gather(src, c.hin, c.hin, c.cin, KH=c.k, KW=c.k, stride=c.stride, pad=(c.k - 1) // 2,
+                          mode=native.PRO_BN_RELU if bn else native.PRO_NONE,
+                          bn=self._bn(bn, nb, training) if bn else None, update_running=update and training)
+        native.conv_gemm(g, self._wpk(c), out, NB=nb, Ho=c.hout, Wo=c.hout, N=c.cout,
+                         epi_mode=native.EPI_RESIDUAL if res is not None else native.EPI_STORE, epi_res=res,
+                         epi_stats_out=self._stats_out(stats_for) if training else None)
+        self._count += 1
+
+    def _forward(self, nb: int, training: bool) -> torch.Tensor:
+        """Runs the trunk; returns the tensor feeding the final BN."""
+        self._fwd_conv(self.conv0, self.image, self.r0, nb, bn=None, training=training, update=False,
+                       stats_for=self.blocks[0].bn1)
+        x = self.r0
+        for i, (b, a) in enumerate(zip(self.blocks, self.acts)):
+            nxt = self.blocks[i + 1].bn1 if i + 1 < len(self.blocks) else self.bn_final
+            if b.proj:
+                self._fwd_conv(b.proj, x, a["sc"], nb, bn=b.bn1, training=training, update=False)
+            self._fwd_conv(b.conv1, x, a["c1"], nb, bn=b.bn1, training=training, update=True, stats_for=b.bn2)
+            self._fwd_conv(b.conv2, a["c1"], a["out"], nb, bn=b.bn2, training=training, update=True,
+                           res=a["sc"] if b.proj else x, stats_for=nxt)
+            x = a["out"]
+        return x
+
+    def _head(self, x, nb: int, training: bool, t_out=None, loss=None, correct=None) -> None:
+        b = self.bn_final
+        n = self.cfg.num_classes * self.final_c
+        h = native.Head()
+        h.x, h.labels = x.data_ptr(), self.labels.data_ptr()
+        h.w = self.params[self.dense_w_off:].data_ptr()
+        h.bias = self.params[self.dense_b_off:].data_ptr()
+        h.bn = self._bn(b, nb, training)
+        h.loss_out = (loss if loss is not None else self.loss_cell).data_ptr()
+        h.correct_out = (correct if correct is not None else self.correct_cell).data_ptr()
+        h.logits_out = self.logits.data_ptr()
+        h.dw = self.grads[self.dense_w_off:].data_ptr()
+        h.db = self.grads[self.dense_b_off:].data_ptr()
+        h.t_out = t_out.data_ptr() if t_out is not None else 0
+        h.bwd_stats_out = self._bwd_stats(b).data_ptr()
+        h.loss_scale = 1.0
+        h.batch, h.HW, h.C, h.classes = nb, b.h * b.h, b.c, self.cfg.num_classes
+        h.has_bn, h.training, h.update_running = 1, int(training), int(training)
+        native.head(h)
+        self._count += 1
+
+    def _wgrad(self, c: ConvL, x_src, x_bn: Optional[BnL], gy_src, nb, *, gy_bn: Optional[BnL] = None,
+               gy_x=None) -> None:
+        gx = native.gather(x_src, c.hin, c.hin, c.cin, KH=c.k, KW=c.k, stride=c.stride, pad=(c.k - 1) // 2,
+                           mode=native.PRO_BN_RELU if x_bn else native.PRO_NONE,
+                           bn=self._bn(x_bn, nb, True) if x_bn else None)
+        gg = native.gather(gy_src, c.hout, c.hout, c.cout,
+                           mode=native.PRO_BN_BWD if gy_bn else native.PRO_NONE,
+                           bn=self._bn(gy_bn, nb, True) if gy_bn else None, src2=gy_x,
+                           bwd_stats=self._bwd_stats(gy_bn) if gy_bn else None)
+        dw = self.grads[c.w_off:]
+        native.conv_wgrad(gx, gg, dw, NB=nb, Ho=c.hout, Wo=c.hout, Cout=c.cout)
+        self._count += 1
+
+    def _dgrad(self, c: ConvL, gy_src, nb, out, *, mask_x, mask_bn: BnL, gy_bn: Optional[BnL] = None, gy_x=None,
+               accumulate: bool = False) -> None:
+        g = native.gather(gy_src, c.hout, c.hout, c.cout, KH=c.k, KW=c.k, stride=c.stride, pad=(c.k - 1) // 2,
+                          transposed=True, mode=native.PRO_BN_BWD if gy_bn else native.PRO_NONE,
+                          bn=self._bn(gy_bn, nb, True) if gy_bn else None, src2=gy_x,
+                          bwd_stats=self._bwd_stats(gy_bn) if gy_bn else None)
+        native.conv_gemm(g, self._wpk(c, dgrad=True), out, NB=nb, Ho=c.hin, Wo=c.hin, N=c.cin,
+                         epi_mode=native.EPI_RELU_MASK, epi_x=mask_x, epi_bn=self._bn(mask_bn, nb, True),
+                         epi_stats_out=self._bwd_stats(mask_bn), epi_accumulate=accumulate)
+        self._count += 1
+
+    def _backward(self, x_last, nb: int) -> None:
+        t_f = self.tbuf[0]
+        self._head(x_last, nb, True, t_out=t_f)
+        bf = self.bn_final
+        g_out = self.gbuf[0]
+        native.bn_bwd_apply(t_f, x_last, None, g_out, self._bn(bf, nb, True), self._bwd_stats(bf),
+                            nb * bf.h * bf.h, bf.c)
+        self._count += 1
+        cur = 0
+        for i in range(len(self.blocks) - 1, -1, -1):
+            b, a = self.blocks[i], self.acts[i]
+            x_in = self.acts[i - 1]["out"] if i > 0 else self.r0
+            t2, t1 = self.tbuf[0], self.tbuf[1]
+            self._wgrad(b.conv2, a["c1"], b.bn2, g_out, nb)
+            self._dgrad(b.conv2, g_out, nb, t2, mask_x=a["c1"], mask_bn=b.bn2)
+            self._wgrad(b.conv1, x_in, b.bn1, t2, nb, gy_bn=b.bn2, gy_x=a["c1"])
+            if b.proj:
+                self._wgrad(b.proj, x_in, b.bn1, g_out, nb)
+            self._dgrad(b.conv1, t2, nb, t1, mask_x=x_in, mask_bn=b.bn1, gy_bn=b.bn2, gy_x=a["c1"])
+            if b.proj:
+                self._dgrad(b.proj, g_out, nb, t1, mask_x=x_in, mask_bn=b.bn1, accumulate=True)
+            nxt = self.gbuf[cur ^ 1]
+            native.bn_bwd_apply(t1, x_in, None if b.proj else g_out, nxt, self._bn(b.bn1, nb, True),
+                                self._bwd_stats(b.bn1), nb * b.hin * b.hin, b.cin)
+            self._count += 1
+            g_out = nxt
+            cur ^= 1
+        self._wgrad(self.conv0, self.image, None, g_out, nb)
+
+    def _train_kernels(self, nb: int, pp_mode: int) -> None:
+        self._count = 0
+        native.step_begin(self.zero_region, self.step_dev, bump=True)
+        native.preprocess(self.in_u8, None, self.image, mode=pp_mode, seed=self._seed, counter=self._pp_counter, n=nb)
+        self._count += 2
+        x_last = self._forward(nb, True)
+        self._backward(x_last, nb)
+        native.optimizer_step(self.params, self.grads, self.slot0, self.slot1, self.pack, self.segs_dev,
+                              self.chunks_dev, self.n_chunks, self.hp_dev, self.step_dev, 1.0)
+        self._count += 1
+        self.launches_per_step = self._count
+
+    def _eval_kernels(self, nb: int) -> None:
+        self._count = 0
+        native.preprocess(self.in_u8, None, self.image, mode=1, n=nb)
+        x_last = self._forward(nb, False)
+        self._head(x_last, nb, False, loss=self.eval_cells[0:1], correct=self.eval_cells[1:2].view(torch.int32))
+
+    # ------------------------------------------------------------------ public step API
+    def _run(self, kind: str, nb: int, fn) -> None:
+        if not self.use_graphs:
+            fn()
+            return
+        key = (kind, nb)
+        g = self._graphs.get(key)
+        if g is None:
+            fn()                                   # warm-up: sets kernel attributes, touches buffers
+            if kind == "train":                    # undo the warm-up's side effects on the step counter
+                pass
+            torch.cuda.synchronize(self.device)
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                fn()
+            self._graphs[key] = g
+            if len(self._graphs) > 16:
+                self._graphs.pop(next(iter(self._graphs)))
+            return                                 # the warm-up run already performed this step
+        g.replay()
+
+    def load_batch(self, images_u8: torch.Tensor, labels: torch.Tensor) -> int:
+        nb = int(images_u8.shape[0])
+        if nb > self.max_batch:
+            raise ValueError(f"batch {nb} exceeds the engine's max_batch {self.max_batch}")
+        self.in_u8[:nb].copy_(images_u8, non_blocking=True)
+        self.labels[:nb].copy_(labels.to(torch.int32), non_blocking=True)
+        return nb
+
+    def train_step_u8(self, images_u8: torch.Tensor, labels: torch.Tensor, augment: bool = True) -> torch.Tensor:
+        """uint8 NHWC images (device or pinned host) -> one optimizer step; returns the loss cell."""
+        nb = self.load_batch(images_u8, labels)
+        mode = 2 if augment else 1
+        self._pp_counter += nb
+        self._run("train" if augment else "train_noaug", nb, lambda: self._train_kernels(nb, mode))
+        self.last_loss = self.loss_cell
+        return self.loss_cell
+
+    def eval_batch_u8(self, images_u8: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
+        nb = self.load_batch(images_u8, labels)
+        before = self.eval_cells[1:2].view(torch.int32).clone()
+        self._run("eval", nb, lambda: self._eval_kernels(nb))
+        return self.eval_cells[1:2].view(torch.int32) - before
+
+    # GpuMember hooks: preprocessing happens inside the step, so these take raw uint8 batches
+    def preprocess(self, images_u8: torch.Tensor, training: bool) -> torch.Tensor:
+        return images_u8
+
+    def train_step(self, images_u8: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
+        return self.train_step_u8(images_u8, labels, augment=True)
+
+    def eval_batch(self, images_u8: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
+        return self.eval_batch_u8(images_u8, labels).sum()
+
+    # ------------------------------------------------------------------ state
+    def state_tensors(self) -> Dict[str, torch.Tensor]:
+        return {"params": self.params[: self.n_params], "slot0": self.slot0[: self.n_params],
+                "slot1": self.slot1[: self.n_params], "running": self.running, "step": self.step_dev}
+
+    @torch.no_grad()
+    def load_state(self, tensors: Dict[str, Any], step: int) -> None:
+        for k, dst in self.state_tensors().items():
+            if k == "step":
+                continue
+            src = tensors[k]
+            src = src if isinstance(src, torch.Tensor) else torch.from_numpy(src)
+            dst.copy_(src.to(self.device).view_as(dst))
+        self.step_dev.fill_(int(step))
+        self.repack()
+
+    def state_bytes(self) -> int:
+        return self.state_bytes_total
+
+    def after_state_replaced(self) -> None:
+        """Call after the state arena was overwritten from outside (exploit): refresh derived data."""
+        self.repack()
+
+    def synchronize(self) -> None:
+        torch.cuda.synchronize(self.device)
+
+    def close(self) -> None:
+        self._graphs.clear()

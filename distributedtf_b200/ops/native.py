@@ -1,9 +1,230 @@
-"""ctypes loader for the native library (placeholder until the first build)."""
-import os
+"""ctypes bindings to ``libdtf_b200.so`` (C ABI in ``include/dtf_b200.h``).
 
-_LIB = None
+The structures below mirror the header field for field.  Wrappers take torch CUDA
+tensors, pass raw device pointers and the *current* torch CUDA stream, and raise on any
+non-zero return code — there is no eager fallback: on a GPU box a missing library is an
+error (``require()``), so tests can never silently pass on a library path.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Any, Optional, Sequence
+
+import torch
+
 LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "lib", "libdtf_b200.so")
+_lib: Optional[C.CDLL] = None
+
+OK = 0
+ERRORS = {-1: "DTF_ERR_SHAPE", -2: "DTF_ERR_SMEM", -3: "DTF_ERR_CUDA", -4: "DTF_ERR_ARG",
+          -5: "DTF_ERR_LIMIT", -6: "DTF_ERR_IO"}
+
+PRO_NONE, PRO_BN_RELU, PRO_BN_BWD = 0, 1, 3
+EPI_STORE, EPI_RESIDUAL, EPI_BIAS_RELU, EPI_RELU_MASK, EPI_BIAS = 0, 1, 2, 3, 4
+OPT_CHUNK = 1024
+MAX_LR_BOUNDARIES = 12
+BN_EPS, BN_DECAY = 1e-5, 0.997
+
+
+class NativeError(RuntimeError):
+    pass
 
 
 def available() -> bool:
     return os.path.isfile(LIB_PATH)
+
+
+def lib() -> C.CDLL:
+    global _lib
+    if _lib is None:
+        if not available():
+            raise NativeError(f"{LIB_PATH} is missing: run `python build_native.py` "
+                              "(or __graft_entry__.build()) before using the native engine")
+        _lib = C.CDLL(os.path.abspath(LIB_PATH))
+        _declare(_lib)
+    return _lib
+
+
+def require() -> C.CDLL:
+    """Loud failure when the extension is absent on a machine that has a GPU."""
+    return lib()
+
+
+def check(rc: int, what: str) -> None:
+    if rc != OK:
+        raise NativeError(f"{what} failed: {ERRORS.get(rc, rc)}")
+
+
+def stream_ptr() -> C.c_void_p:
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def ptr(t: Optional[torch.Tensor]) -> int:
+    return 0 if t is None else t.data_ptr()
+
+
+# --------------------------------------------------------------------------- structs
+class BnRef(C.Structure):
+    _fields_ = [("stats", C.c_void_p), ("gamma", C.c_void_p), ("beta", C.c_void_p),
+                ("run_mean", C.c_void_p), ("run_var", C.c_void_p),
+                ("inv_count", C.c_float), ("eps", C.c_float), ("decay", C.c_float),
+                ("channels", C.c_int), ("use_running", C.c_int)]
+
+
+class Gather(C.Structure):
+    _fields_ = [("src", C.c_void_p), ("src2", C.c_void_p), ("bwd_stats", C.c_void_p), ("bn", BnRef),
+                ("mode", C.c_int), ("update_running", C.c_int),
+                ("Hs", C.c_int), ("Ws", C.c_int), ("C", C.c_int),
+                ("KH", C.c_int), ("KW", C.c_int), ("stride", C.c_int), ("pad", C.c_int),
+                ("transposed", C.c_int), ("cpt_shift", C.c_int), ("kchunks_real", C.c_int)]
+
+
+class ConvGemm(C.Structure):
+    _fields_ = [("a", Gather), ("wpk", C.c_void_p), ("out", C.c_void_p), ("epi_res", C.c_void_p),
+                ("epi_bias", C.c_void_p), ("epi_x", C.c_void_p), ("epi_bn", BnRef),
+                ("epi_stats_out", C.c_void_p), ("epi_mode", C.c_int), ("epi_accumulate", C.c_int),
+                ("NB", C.c_int), ("Ho", C.c_int), ("Wo", C.c_int), ("N", C.c_int),
+                ("kchunks", C.c_int), ("kb_chunks", C.c_int), ("smem_b_off", C.c_int), ("smem_a_off", C.c_int)]
+
+
+class ConvWgrad(C.Structure):
+    _fields_ = [("x", Gather), ("gy", Gather), ("dw", C.c_void_p),
+                ("NB", C.c_int), ("Ho", C.c_int), ("Wo", C.c_int), ("Cout", C.c_int),
+                ("kchunks", C.c_int), ("kchunks_real", C.c_int), ("chunks_per_cta", C.c_int),
+                ("smem_a_off", C.c_int)]
+
+
+class Head(C.Structure):
+    _fields_ = [("x", C.c_void_p), ("labels", C.c_void_p), ("w", C.c_void_p), ("bias", C.c_void_p),
+                ("bn", BnRef), ("loss_out", C.c_void_p), ("correct_out", C.c_void_p),
+                ("logits_out", C.c_void_p), ("dw", C.c_void_p), ("db", C.c_void_p), ("t_out", C.c_void_p),
+                ("bwd_stats_out", C.c_void_p), ("loss_scale", C.c_float),
+                ("batch", C.c_int), ("HW", C.c_int), ("C", C.c_int), ("classes", C.c_int),
+                ("has_bn", C.c_int), ("training", C.c_int), ("update_running", C.c_int)]
+
+
+class Hparams(C.Structure):
+    _fields_ = [("optimizer", C.c_int), ("regularizer", C.c_int), ("momentum", C.c_float),
+                ("grad_decay", C.c_float), ("weight_decay", C.c_float), ("inv_loss_scale", C.c_float),
+                ("n_boundaries", C.c_int), ("batch_size", C.c_int),
+                ("boundaries", C.c_longlong * MAX_LR_BOUNDARIES),
+                ("lr_values", C.c_float * (MAX_LR_BOUNDARIES + 1)), ("reserved", C.c_float * 3)]
+
+
+class OptSegment(C.Structure):
+    _fields_ = [("offset", C.c_int), ("count", C.c_int), ("regularized", C.c_int), ("pack", C.c_int),
+                ("Cout", C.c_int), ("taps", C.c_int), ("Cin", C.c_int),
+                ("fwd_pack_off", C.c_int), ("dgrad_pack_off", C.c_int), ("reserved", C.c_int * 3)]
+
+
+def _declare(l: C.CDLL) -> None:
+    vp, i, ll, f = C.c_void_p, C.c_int, C.c_longlong, C.c_float
+    l.dtf_conv_gemm.argtypes = [C.POINTER(ConvGemm), vp]
+    l.dtf_conv_wgrad.argtypes = [C.POINTER(ConvWgrad), vp]
+    l.dtf_bn_bwd_apply.argtypes = [vp, vp, vp, vp, C.POINTER(BnRef), vp, ll, i, vp]
+    l.dtf_head.argtypes = [C.POINTER(Head), vp]
+    l.dtf_pack_weights.argtypes = [vp, vp, vp, vp, i, vp]
+    l.dtf_optimizer_step.argtypes = [vp, vp, vp, vp, vp, vp, vp, i, vp, vp, f, vp]
+    l.dtf_step_begin.argtypes = [vp, ll, vp, i, vp]
+    l.dtf_fill.argtypes = [vp, ll, f, vp]
+    l.dtf_preprocess.argtypes = [vp, vp, vp, vp, i, i, i, i, i, C.c_ulonglong, C.c_ulonglong, vp]
+    for name in ("dtf_conv_gemm", "dtf_conv_wgrad", "dtf_bn_bwd_apply", "dtf_head", "dtf_pack_weights",
+                 "dtf_optimizer_step", "dtf_step_begin", "dtf_fill", "dtf_preprocess"):
+        getattr(l, name).restype = i
+    _declare_optional(l)
+
+
+def _declare_optional(l: C.CDLL) -> None:
+    """Entry points added by later source files (exploit, all-reduce, score board, host IO)."""
+    from . import native_ext
+    native_ext.declare(l)
+
+
+# --------------------------------------------------------------------------- builders
+def bn_ref(channels: int, count: int, *, stats=None, gamma=None, beta=None, run_mean=None, run_var=None,
+           use_running: bool = False, eps: float = BN_EPS, decay: float = BN_DECAY) -> BnRef:
+    return BnRef(ptr(stats), ptr(gamma), ptr(beta), ptr(run_mean), ptr(run_var),
+                 1.0 / float(count), eps, decay, channels, int(use_running))
+
+
+def gather(src: torch.Tensor, Hs: int, Ws: int, Cc: int, *, KH=1, KW=1, stride=1, pad=0, transposed=False,
+           mode=PRO_NONE, bn: Optional[BnRef] = None, src2=None, bwd_stats=None, update_running=False) -> Gather:
+    return Gather(ptr(src), ptr(src2), ptr(bwd_stats), bn if bn is not None else BnRef(), mode,
+                  int(update_running), Hs, Ws, Cc, KH, KW, stride, pad, int(transposed), 0, 0)
+
+
+def conv_gemm(a: Gather, wpk: torch.Tensor, out: torch.Tensor, *, NB: int, Ho: int, Wo: int, N: int,
+              epi_mode=EPI_STORE, epi_res=None, epi_bias=None, epi_x=None, epi_bn: Optional[BnRef] = None,
+              epi_stats_out=None, epi_accumulate=False) -> None:
+    p = ConvGemm(a, ptr(wpk), ptr(out), ptr(epi_res), ptr(epi_bias), ptr(epi_x),
+                 epi_bn if epi_bn is not None else BnRef(), ptr(epi_stats_out), epi_mode,
+                 int(epi_accumulate), NB, Ho, Wo, N, 0, 0, 0, 0)
+    check(lib().dtf_conv_gemm(C.byref(p), stream_ptr()), "dtf_conv_gemm")
+
+
+def conv_wgrad(x: Gather, gy: Gather, dw: torch.Tensor, *, NB: int, Ho: int, Wo: int, Cout: int) -> None:
+    p = ConvWgrad(x, gy, ptr(dw), NB, Ho, Wo, Cout, 0, 0, 0, 0)
+    check(lib().dtf_conv_wgrad(C.byref(p), stream_ptr()), "dtf_conv_wgrad")
+
+
+def bn_bwd_apply(t, x, res, out, bn: BnRef, bwd_stats, pixels: int, channels: int) -> None:
+    check(lib().dtf_bn_bwd_apply(ptr(t), ptr(x), ptr(res), ptr(out), C.byref(bn), ptr(bwd_stats),
+                                 pixels, channels, stream_ptr()), "dtf_bn_bwd_apply")
+
+
+def head(p: Head) -> None:
+    check(lib().dtf_head(C.byref(p), stream_ptr()), "dtf_head")
+
+
+def pack_weights(params, pack, segs_dev, chunks_dev, n_chunks: int) -> None:
+    check(lib().dtf_pack_weights(ptr(params), ptr(pack), ptr(segs_dev), ptr(chunks_dev), n_chunks,
+                                 stream_ptr()), "dtf_pack_weights")
+
+
+def optimizer_step(params, grads, slot0, slot1, pack, segs_dev, chunks_dev, n_chunks: int, hp_dev, step_dev,
+                   grad_scale: float = 1.0) -> None:
+    check(lib().dtf_optimizer_step(ptr(params), ptr(grads), ptr(slot0), ptr(slot1), ptr(pack), ptr(segs_dev),
+                                   ptr(chunks_dev), n_chunks, ptr(hp_dev), ptr(step_dev), grad_scale,
+                                   stream_ptr()), "dtf_optimizer_step")
+
+
+def step_begin(zero_region: torch.Tensor, step_dev: torch.Tensor, bump: bool = True) -> None:
+    n = zero_region.numel() * zero_region.element_size() // 4
+    check(lib().dtf_step_begin(ptr(zero_region), n, ptr(step_dev), int(bump), stream_ptr()), "dtf_step_begin")
+
+
+def fill(t: torch.Tensor, value: float) -> None:
+    check(lib().dtf_fill(ptr(t), t.numel(), float(value), stream_ptr()), "dtf_fill")
+
+
+def preprocess(images_u8: torch.Tensor, indices: Optional[torch.Tensor], out: torch.Tensor, *, mode: int,
+               crop_flip: Optional[torch.Tensor] = None, seed: int = 0, counter: int = 0,
+               n: Optional[int] = None) -> None:
+    _, H, W, Cc = images_u8.shape
+    count = int(n if n is not None else (indices.numel() if indices is not None else images_u8.shape[0]))
+    check(lib().dtf_preprocess(ptr(images_u8), ptr(indices), ptr(out), ptr(crop_flip), count, H, W, Cc, mode,
+                               seed & (2 ** 64 - 1), counter & (2 ** 64 - 1), stream_ptr()), "dtf_preprocess")
+
+
+def struct_to_tensor(s: C.Structure, device) -> torch.Tensor:
+    """Copy a ctypes struct (or array of structs) into a device uint8 tensor."""
+    raw = bytes(memoryview(s).cast("B"))
+    return torch.frombuffer(bytearray(raw), dtype=torch.uint8).to(device)
+
+
+def pack_weight_host(w_ohwi: torch.Tensor, transpose_for_dgrad: bool = False) -> torch.Tensor:
+    """Host restatement of the packing: OHWI fp32 -> bf16 [K/8 (even)][N][8] (oracle + tests)."""
+    cout, kh, kw, cin = w_ohwi.shape
+    taps = kh * kw
+    w = w_ohwi.reshape(cout, taps, cin)
+    if transpose_for_dgrad:
+        mat = w.permute(2, 1, 0).reshape(cin, taps * cout)       # [N=ci][K = tap*Cout + co]
+    else:
+        mat = w.reshape(cout, taps * cin)                        # [N=co][K = tap*Cin + ci]
+    n, k = mat.shape
+    kch = (k + 7) // 8
+    kch_pad = (kch + 1) & ~1
+    buf = torch.zeros(kch_pad * 8, n, dtype=torch.float32, device=w_ohwi.device)
+    buf[:k] = mat.t()
+    return buf.reshape(kch_pad, 8, n).permute(0, 2, 1).contiguous().to(torch.bfloat16)

@@ -1,0 +1,169 @@
+/* C ABI of libdtf_b200.so — the hand-written sm_100a kernels and the native host runtime
+ * of distributedtf_b200.  All device pointers are raw CUDA pointers; `stream` is a
+ * cudaStream_t.  Every function returns DTF_OK (0) or a negative DTF_ERR_* code and never
+ * allocates device memory unless its comment says so.  Python binds these with ctypes
+ * (distributedtf_b200/ops/native.py); the struct layouts below are mirrored there.
+ *
+ * Reference parity is cited per entry point (paths relative to the reference repository).
+ */
+#ifndef DTF_B200_H
+#define DTF_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+typedef __nv_bfloat16 dtf_bf16;
+extern "C" {
+#else
+typedef uint16_t dtf_bf16;
+typedef void* cudaStream_t;
+#endif
+
+enum { DTF_OK = 0, DTF_ERR_SHAPE = -1, DTF_ERR_SMEM = -2, DTF_ERR_CUDA = -3, DTF_ERR_ARG = -4,
+       DTF_ERR_LIMIT = -5, DTF_ERR_IO = -6 };
+
+/* operand prologues (applied while gathering the im2col tile) */
+enum { DTF_PRO_NONE = 0, DTF_PRO_BN_RELU = 1, DTF_PRO_BN_BWD = 3 };
+/* epilogues */
+enum { DTF_EPI_STORE = 0, DTF_EPI_RESIDUAL = 1, DTF_EPI_BIAS_RELU = 2, DTF_EPI_RELU_MASK = 3, DTF_EPI_BIAS = 4 };
+
+/* A BatchNorm layer as the kernels see it.  Training statistics are raw accumulators
+ * stats[0..C) = sum(x), stats[C..2C) = sum(x^2) filled by the producer's epilogue.
+ * (reference: resnet/resnet_model.py:45-52, decay 0.997, eps 1e-5) */
+typedef struct {
+    const float* stats;
+    const float* gamma;
+    const float* beta;
+    float* run_mean;
+    float* run_var;
+    float inv_count;     /* 1 / (N*H*W) of the normalised tensor */
+    float eps;
+    float decay;
+    int channels;
+    int use_running;     /* 1 = inference: normalise with run_mean / run_var */
+} DtfBnRef;
+
+/* One gathered GEMM operand: an NHWC bf16 tensor read through a (KH x KW, stride, pad) window. */
+typedef struct {
+    const dtf_bf16* src;     /* [NB, Hs, Ws, C] */
+    const dtf_bf16* src2;    /* DTF_PRO_BN_BWD: the BN input x (src is then t = dL/d(bn out) masked) */
+    const float* bwd_stats;  /* DTF_PRO_BN_BWD: [0..C) sum(t), [C..2C) sum(t * xhat)  (= dbeta, dgamma) */
+    DtfBnRef bn;
+    int mode;                /* DTF_PRO_* */
+    int update_running;      /* CTA 0 also updates the moving averages (training, once per BN) */
+    int Hs, Ws, C;
+    int KH, KW, stride, pad;
+    int transposed;          /* 1 = gradient gather of a strided conv (dgrad) */
+    int cpt_shift;           /* filled by the launcher */
+    int kchunks_real;        /* filled by the launcher */
+} DtfGather;
+
+/* out[M][N] = epilogue( gather(a)[M][K] x wpk[N][K]^T ),  M = NB*Ho*Wo.
+ * Forward conv (K1/K2/K5 of SURVEY §2.5; resnet_model.py:55-92) and dgrad. */
+typedef struct {
+    DtfGather a;
+    const dtf_bf16* wpk;     /* packed weights [K/8][N][8] (see dtf_pack_weights) */
+    dtf_bf16* out;           /* [M][N] */
+    const dtf_bf16* epi_res; /* DTF_EPI_RESIDUAL: tensor added to the result */
+    const float* epi_bias;   /* DTF_EPI_BIAS(_RELU) */
+    const dtf_bf16* epi_x;   /* DTF_EPI_RELU_MASK: pre-BN input at the output pixels */
+    DtfBnRef epi_bn;         /* DTF_EPI_RELU_MASK: BN whose ReLU mask / xhat is applied */
+    float* epi_stats_out;    /* optional [2][N] accumulators (sum,sumsq) or (sum t, sum t*xhat) */
+    int epi_mode;
+    int epi_accumulate;      /* RELU_MASK: add to what `out` already holds */
+    int NB, Ho, Wo, N;
+    int kchunks, kb_chunks, smem_b_off, smem_a_off;   /* filled by the launcher */
+} DtfConvGemm;
+
+/* dw[Cout][KH*KW*Cin] += sum_pixels gy'[pixel][co] * gather(x)[pixel][k]   (fp32 atomics) */
+typedef struct {
+    DtfGather x;             /* conv input side (window = the conv's) */
+    DtfGather gy;            /* output-gradient side; only src/src2/bwd_stats/bn/mode are read */
+    float* dw;
+    int NB, Ho, Wo, Cout;
+    int kchunks, kchunks_real, chunks_per_cta, smem_a_off;   /* filled by the launcher */
+} DtfConvWgrad;
+
+int dtf_conv_gemm(DtfConvGemm* p, cudaStream_t stream);
+int dtf_conv_wgrad(DtfConvWgrad* p, cudaStream_t stream);
+
+/* ---- classifier head: final BN + ReLU + global average pool + dense + softmax-CE ----------
+ * forward and backward in one launch, one CTA per image (resnet_model.py:537-552,
+ * resnet_run_loop.py:230-246,303; mnist_model.py:97-126 with has_bn = 0 and HW = 1). */
+typedef struct {
+    const dtf_bf16* x;       /* [batch, HW, C] pre-BN activations */
+    const int* labels;       /* [batch] */
+    const float* w;          /* dense kernel [classes, C] fp32 */
+    const float* bias;       /* [classes] */
+    DtfBnRef bn;
+    float* loss_out;         /* += mean cross-entropy */
+    int* correct_out;        /* += number of argmax hits */
+    float* logits_out;       /* optional [batch, classes] */
+    float* dw;               /* += d loss / d w   (training) */
+    float* db;
+    dtf_bf16* t_out;         /* [batch, HW, C]: dL/d(bn out) masked by the ReLU (training) */
+    float* bwd_stats_out;    /* [2][C] += (sum t, sum t*xhat)  (= dbeta, dgamma) */
+    float loss_scale;
+    int batch, HW, C, classes;
+    int has_bn, training, update_running;
+} DtfHead;
+
+/* ---- optimizer ------------------------------------------------------------------------ */
+enum { DTF_OPT_GD = 0, DTF_OPT_MOMENTUM = 1, DTF_OPT_ADAGRAD = 2, DTF_OPT_ADADELTA = 3, DTF_OPT_ADAM = 4,
+       DTF_OPT_RMSPROP = 5 };
+enum { DTF_REG_NONE = 0, DTF_REG_L1 = 1, DTF_REG_L2 = 2, DTF_REG_L1_L2 = 3 };
+#define DTF_OPT_CHUNK 1024
+#define DTF_MAX_LR_BOUNDARIES 12
+
+/* Device-resident hyper-parameter block of one member: explore rewrites it in place, so a
+ * captured CUDA graph of the step never needs re-capture (constants.py:14-43 ranges). */
+typedef struct {
+    int optimizer;           /* DTF_OPT_* */
+    int regularizer;         /* DTF_REG_* */
+    float momentum;
+    float grad_decay;
+    float weight_decay;
+    float inv_loss_scale;
+    int n_boundaries;
+    int batch_size;
+    long long boundaries[DTF_MAX_LR_BOUNDARIES];
+    float lr_values[DTF_MAX_LR_BOUNDARIES + 1];
+    float reserved[3];
+} DtfHparams;
+
+/* One parameter tensor of the flat arena. */
+typedef struct {
+    int offset, count;       /* elements, in params / grads / slot0 / slot1 */
+    int regularized;         /* conv kernels only (resnet_model.py:91) */
+    int pack;                /* emit bf16 GEMM-ready copies */
+    int Cout, taps, Cin;     /* OHWI dims of a conv kernel */
+    int fwd_pack_off;        /* element offsets in the bf16 pack arena, -1 = none */
+    int dgrad_pack_off;
+    int reserved[3];
+} DtfOptSegment;
+
+int dtf_bn_bwd_apply(const dtf_bf16* t, const dtf_bf16* x, const dtf_bf16* res, dtf_bf16* out,
+                     const DtfBnRef* bn, const float* bwd_stats, long long pixels, int C, cudaStream_t stream);
+int dtf_head(const DtfHead* p, cudaStream_t stream);
+/* chunks: n_chunks x {segment index, first element} pairs; each CTA handles DTF_OPT_CHUNK elements */
+int dtf_pack_weights(const float* params, dtf_bf16* pack, const DtfOptSegment* segs, const int* chunks,
+                     int n_chunks, cudaStream_t stream);
+/* TF-1.x Apply<Optimizer> (resnet_run_loop.py:552-586) + regulariser gradient + LR schedule +
+ * bf16 re-pack in one launch.  `step` holds the 1-based index of this update. */
+int dtf_optimizer_step(float* params, const float* grads, float* slot0, float* slot1, dtf_bf16* pack,
+                       const DtfOptSegment* segs, const int* chunks, int n_chunks, const DtfHparams* hp,
+                       const long long* step, float grad_scale, cudaStream_t stream);
+int dtf_step_begin(float* zero_base, long long zero_floats, long long* step, int bump, cudaStream_t stream);
+int dtf_fill(float* p, long long n, float v, cudaStream_t stream);
+/* uint8 NHWC -> bf16 NHWC (channels padded to 8); mode 0 cast, 1 standardise, 2 crop+flip+standardise
+ * (cifar10_main.py:96-109).  crop_flip: optional [n][3] = (oy, ox, flip) overriding the RNG. */
+int dtf_preprocess(const uint8_t* images, const int* indices, dtf_bf16* out, const int* crop_flip, int n,
+                   int H, int W, int C, int mode, unsigned long long seed, unsigned long long counter,
+                   cudaStream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DTF_B200_H */

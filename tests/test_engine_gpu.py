@@ -1,0 +1,284 @@
+"""Element-wise kernels, optimizer rules and the whole native ResNet step vs PyTorch references."""
+import copy
+import ctypes
+import math
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+EPS = 1e-5
+
+
+@pytest.fixture(scope="module")
+def nat():
+    from distributedtf_b200.ops import native
+    native.require()
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    return native
+
+
+def rnd(*shape, scale=1.0, seed=0):
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    return torch.randn(*shape, device="cuda", generator=g) * scale
+
+
+def close(got, want, rtol, atol, what=""):
+    got, want = got.float(), want.float()
+    err = (got - want).abs()
+    bad = (err > atol + rtol * want.abs()).sum().item()
+    assert bad == 0, f"{what}: {bad}/{got.numel()} off, max err {err.max().item():.4g} (ref max {want.abs().max().item():.4g})"
+
+
+def test_bn_bwd_apply(nat):
+    P, Cc = 4 * 16 * 16, 32
+    x = (rnd(P, Cc, seed=1) + 0.3).bfloat16()
+    t = rnd(P, Cc, seed=2).bfloat16()
+    res = rnd(P, Cc, seed=3).bfloat16()
+    gamma, beta = 1 + 0.1 * rnd(Cc, seed=4), 0.1 * rnd(Cc, seed=5)
+    xf, tf = x.float(), t.float()
+    mean, invstd = xf.mean(0), torch.rsqrt(xf.var(0, unbiased=False) + EPS)
+    xhat = (xf - mean) * invstd
+    want = gamma * invstd * (tf - tf.mean(0) - xhat * (tf * xhat).mean(0))
+    stats = torch.cat([xf.sum(0), (xf * xf).sum(0)]).contiguous()
+    bwd = torch.cat([tf.sum(0), (tf * xhat).sum(0)]).contiguous()
+    out = torch.empty_like(x)
+    bn = nat.bn_ref(Cc, P, stats=stats, gamma=gamma, beta=beta)
+    nat.bn_bwd_apply(t, x, None, out, bn, bwd, P, Cc)
+    close(out, want, 2e-2, 2e-2, "bn bwd")
+    nat.bn_bwd_apply(t, x, res, out, bn, bwd, P, Cc)
+    close(out, want + res.float(), 2e-2, 2e-2, "bn bwd + residual")
+
+
+@pytest.mark.parametrize("training", [True, False])
+def test_head(nat, training):
+    NB, HW, Cc, K = 37, 64, 64, 10
+    x = (rnd(NB, HW, Cc, seed=1) + 0.2).bfloat16()
+    labels = torch.randint(0, K, (NB,), device="cuda", dtype=torch.int32)
+    w, b = rnd(K, Cc, scale=0.3, seed=2), rnd(K, scale=0.1, seed=3)
+    gamma, beta = 1 + 0.1 * rnd(Cc, seed=4), 0.1 * rnd(Cc, seed=5)
+    rm, rv = 0.1 * rnd(Cc, seed=6), 1 + 0.2 * torch.rand(Cc, device="cuda")
+    xf = x.float().reshape(-1, Cc)
+    if training:
+        mean, var = xf.mean(0), xf.var(0, unbiased=False)
+    else:
+        mean, var = rm.clone(), rv.clone()
+    invstd = torch.rsqrt(var + EPS)
+    xr = x.float().clone().requires_grad_(True)
+    wr, br = w.clone().requires_grad_(True), b.clone().requires_grad_(True)
+    y = (xr - mean) * invstd * gamma + beta          # statistics treated as constants here:
+    a = torch.relu(y)                                #   the kernel emits t = dL/dy, BN backward comes later
+    logits = a.mean(1) @ wr.t() + br
+    loss = F.cross_entropy(logits, labels.long())
+    if training:
+        loss.backward()
+    stats = torch.cat([xf.sum(0), (xf * xf).sum(0)]).contiguous()
+    h = nat.Head()
+    loss_out, correct = torch.zeros(1, device="cuda"), torch.zeros(1, device="cuda", dtype=torch.int32)
+    lg = torch.zeros(NB, K, device="cuda")
+    dw, db = torch.zeros(K, Cc, device="cuda"), torch.zeros(K, device="cuda")
+    t_out = torch.zeros(NB, HW, Cc, device="cuda", dtype=torch.bfloat16)
+    bwd = torch.zeros(2 * Cc, device="cuda")
+    rm2, rv2 = rm.clone(), rv.clone()
+    h.x, h.labels, h.w, h.bias = x.data_ptr(), labels.data_ptr(), w.data_ptr(), b.data_ptr()
+    h.bn = nat.bn_ref(Cc, NB * HW, stats=stats, gamma=gamma, beta=beta, run_mean=rm2, run_var=rv2,
+                      use_running=not training)
+    h.loss_out, h.correct_out, h.logits_out = loss_out.data_ptr(), correct.data_ptr(), lg.data_ptr()
+    h.dw, h.db, h.t_out, h.bwd_stats_out = dw.data_ptr(), db.data_ptr(), t_out.data_ptr(), bwd.data_ptr()
+    h.loss_scale = 1.0
+    h.batch, h.HW, h.C, h.classes = NB, HW, Cc, K
+    h.has_bn, h.training, h.update_running = 1, int(training), int(training)
+    nat.head(h)
+    torch.cuda.synchronize()
+    close(lg, logits, 1e-3, 1e-3, "logits")
+    close(loss_out, loss.detach().reshape(1), 1e-3, 1e-3, "loss")
+    assert correct.item() == (logits.argmax(1) == labels.long()).sum().item()
+    if training:
+        close(dw, wr.grad, 1e-2, 1e-4, "dense dW")
+        close(db, br.grad, 1e-2, 1e-5, "dense db")
+        # t = dL/dy  (gradient w.r.t. the BN output, ReLU mask applied)
+        ty = torch.autograd.grad(F.cross_entropy((torch.relu(yy := y.detach().requires_grad_(True)).mean(1)) @ w.t() + b,
+                                                 labels.long()), yy)[0]
+        close(t_out, ty, 2e-2, 1e-6, "t_out")
+        xhat = (x.float() - mean) * invstd
+        close(bwd[:Cc], ty.reshape(-1, Cc).sum(0), 2e-2, 1e-4, "dbeta")
+        close(bwd[Cc:], (ty * xhat).reshape(-1, Cc).sum(0), 2e-2, 1e-4, "dgamma")
+        close(rm2, 0.997 * rm + 0.003 * xf.mean(0), 1e-4, 1e-6, "moving mean")
+        close(rv2, 0.997 * rv + 0.003 * xf.var(0, unbiased=True), 1e-4, 1e-6, "moving var")
+
+
+OPTS = [("gd", {}), ("Momentum", {"momentum": 0.83}), ("Adagrad", {}), ("Adadelta", {}), ("Adam", {}),
+        ("RMSProp", {"momentum": 0.4, "grad_decay": 0.77})]
+
+
+@pytest.mark.parametrize("name,extra", OPTS)
+@pytest.mark.parametrize("reg", ["None", "l1_regularizer", "l2_regularizer", "l1_l2_regularizer"])
+def test_optimizer_rules_and_pack(nat, name, extra, reg):
+    """Three consecutive updates of the fused kernel == the TF-1.x rules restated in torch."""
+    from distributedtf_b200.ops import reference
+    from distributedtf_b200.models.resnet_native import NativeResNetEngine
+    from distributedtf_b200.models import resnet
+    hp = {"opt_case": {"optimizer": name, "lr": 0.05, **extra}, "decay_steps": 0, "decay_rate": 0.5,
+          "weight_decay": 3e-3, "regularizer": reg, "initializer": "he_init", "batch_size": 128}
+    eng = NativeResNetEngine(resnet.cifar10_config(8), hp, "cuda", seed=3, use_graphs=False)
+    n = eng.n_params
+    w = eng.params[:n].clone()
+    s0, s1 = eng.slot0[:n].clone(), eng.slot1[:n].clone()
+    a, b = reference.slot_init_values(name)
+    assert torch.all(s0 == a) and torch.all(s1 == b)
+    mask = torch.zeros(n, device="cuda")
+    mask[: eng.n_conv_params] = 1
+    for step in range(1, 4):
+        g = rnd(n, scale=0.1, seed=10 + step)
+        eng.grads[:n].copy_(g)
+        eng.step_dev.fill_(step)
+        nat.optimizer_step(eng.params, eng.grads, eng.slot0, eng.slot1, eng.pack, eng.segs_dev, eng.chunks_dev,
+                           eng.n_chunks, eng.hp_dev, eng.step_dev, 1.0)
+        gr = g + mask * reference.regularizer_grad(w, reg, 3e-3)
+        reference.apply_update(name, w, gr, s0, s1, lr=0.05 * 128 / 128, step=step,
+                               momentum=extra.get("momentum", 0.0), grad_decay=extra.get("grad_decay", 0.9))
+        close(eng.params[:n], w, 2e-4, 1e-5, f"{name} params step {step}")
+        close(eng.slot0[:n], s0, 2e-4, 1e-6, f"{name} slot0")
+        close(eng.slot1[:n], s1, 2e-4, 1e-6, f"{name} slot1")
+    # the fused re-pack equals the host restatement of the packing
+    for c in eng.convs:
+        wt = eng.conv_weight(c)
+        want = nat.pack_weight_host(wt)
+        got = eng.pack[c.fwd_pack: c.fwd_pack + want.numel()].view_as(want)
+        assert torch.equal(got, want), c.name
+        if c.dgrad_pack >= 0:
+            want = nat.pack_weight_host(wt, transpose_for_dgrad=True)
+            got = eng.pack[c.dgrad_pack: c.dgrad_pack + want.numel()].view_as(want)
+            assert torch.equal(got, want), c.name + " dgrad"
+
+
+def test_lr_schedule_on_device(nat):
+    from distributedtf_b200.ops import reference
+    from distributedtf_b200.models.resnet_native import NativeResNetEngine
+    from distributedtf_b200.models import resnet
+    hp = {"opt_case": {"optimizer": "gd", "lr": 0.1}, "decay_steps": 30, "decay_rate": 0.5,
+          "weight_decay": 0.0, "regularizer": "None", "initializer": "None", "batch_size": 100}
+    eng = NativeResNetEngine(resnet.cifar10_config(8), hp, "cuda", seed=3, use_graphs=False)
+    bounds, values = reference.cifar_lr_schedule(hp)
+    assert len(bounds) == 3
+    n = eng.n_params
+    for step in [1, bounds[0], bounds[0] + 1, bounds[0] + 2, bounds[1] + 1, bounds[2] + 5]:
+        w0 = eng.params[:n].clone()
+        eng.grads[:n].fill_(1.0)
+        eng.step_dev.fill_(step)
+        nat.optimizer_step(eng.params, eng.grads, eng.slot0, eng.slot1, eng.pack, eng.segs_dev, eng.chunks_dev,
+                           eng.n_chunks, eng.hp_dev, eng.step_dev, 1.0)
+        lr = reference.piecewise_constant(step - 1, bounds, values)
+        close(w0 - eng.params[:n], torch.full((n,), lr, device="cuda"), 1e-4, 1e-7, f"lr at step {step}")
+
+
+def test_preprocess(nat):
+    from distributedtf_b200.utils.data import cifar_preprocess_torch
+    g = torch.Generator().manual_seed(0)
+    imgs = torch.randint(0, 256, (9, 32, 32, 3), dtype=torch.uint8, generator=g).cuda()
+    out = torch.empty(9, 32, 32, 8, dtype=torch.bfloat16, device="cuda")
+    nat.preprocess(imgs, None, out, mode=1)
+    want = cifar_preprocess_torch(imgs, False)
+    close(out[..., :3], want, 1e-2, 1e-2, "standardise")
+    assert torch.all(out[..., 3:] == 0)
+    cf = torch.tensor([[0, 0, 0], [8, 8, 1], [4, 4, 0], [4, 4, 1], [1, 7, 1], [6, 2, 0], [3, 3, 1], [0, 8, 0], [8, 0, 1]],
+                      dtype=torch.int32, device="cuda")
+    nat.preprocess(imgs, None, out, mode=2, crop_flip=cf)
+    x = imgs.float()
+    padded = torch.zeros(9, 40, 40, 3, device="cuda")
+    padded[:, 4:36, 4:36] = x
+    ref = torch.stack([padded[i, cf[i, 0]: cf[i, 0] + 32, cf[i, 1]: cf[i, 1] + 32] for i in range(9)])
+    ref = torch.stack([r.flip(1) if cf[i, 2] else r for i, r in enumerate(ref)])
+    mean = ref.mean(dim=(1, 2, 3), keepdim=True)
+    std = ref.std(dim=(1, 2, 3), keepdim=True, unbiased=False)
+    close(out[..., :3], (ref - mean) / torch.clamp(std, min=1 / math.sqrt(3072)), 1e-2, 1e-2, "augment")
+    idx = torch.tensor([3, 1, 7], dtype=torch.int32, device="cuda")
+    out2 = torch.empty(3, 32, 32, 8, dtype=torch.bfloat16, device="cuda")
+    nat.preprocess(imgs, idx, out2, mode=0)
+    assert torch.equal(out2[..., :3].float(), imgs[idx.long()].float())
+    # RNG path: offsets differ between images and stay inside the padded canvas (finite output)
+    nat.preprocess(imgs, None, out, mode=2, seed=5, counter=100)
+    assert torch.isfinite(out.float()).all()
+
+
+@pytest.mark.parametrize("size,nb", [(8, 32), (14, 65), (32, 128)])
+def test_native_step_matches_oracle(nat, size, nb):
+    """One full training step (fwd + bwd + Momentum update) of the native engine vs autograd on the
+    torch oracle started from the same parameters and the same preprocessed batch."""
+    from distributedtf_b200.models import resnet
+    from distributedtf_b200.models.resnet_native import NativeResNetEngine
+    from distributedtf_b200.utils.data import cifar_preprocess_torch
+    cfg = resnet.cifar10_config(size)
+    hp = {"opt_case": {"optimizer": "Momentum", "lr": 0.1, "momentum": 0.9}, "decay_steps": 20, "decay_rate": 0.1,
+          "weight_decay": 2e-4, "regularizer": "l2_regularizer", "initializer": "he_init", "batch_size": nb}
+    eng = NativeResNetEngine(cfg, hp, "cuda", seed=5, use_graphs=False)
+    named = {k: v.clone() for k, v in eng.export_named().items()}
+    g = torch.Generator().manual_seed(1)
+    imgs = torch.randint(0, 256, (nb, 32, 32, 3), dtype=torch.uint8, generator=g).cuda()
+    labels = torch.randint(0, 10, (nb,), generator=g).cuda()
+    loss = eng.train_step_u8(imgs, labels, augment=False)
+    torch.cuda.synchronize()
+    assert eng.step == 1
+    # oracle (fp32 weights, bf16-rounded input like the engine's image buffer)
+    x = cifar_preprocess_torch(imgs, False).bfloat16().float().permute(0, 3, 1, 2)
+    params = {k: v.clone().requires_grad_(v.dtype.is_floating_point and "moving" not in k) for k, v in named.items()}
+    logits = resnet.forward(cfg, params, x, True, emulate_bf16=True)
+    ref_loss = F.cross_entropy(logits, labels)
+    ref_loss.backward()
+    close(eng.logits[:nb], logits.detach(), 5e-2, 5e-2, "logits")
+    close(loss, ref_loss.detach().reshape(1), 2e-2, 2e-2, "loss")
+    grads = eng.export_named(eng.grads)
+    worst = 0.0
+    report = []
+    for k, p in params.items():
+        if not p.requires_grad:
+            continue
+        ref = p.grad
+        err = ((grads[k] - ref).norm() / (ref.norm() + 1e-8)).item()
+        worst = max(worst, err)
+        report.append(f"{k}:{err:.3f}")
+    print("relative gradient errors:", " ".join(report))
+    assert worst < 0.08, "gradient errors: " + " ".join(report)
+    # running statistics moved like the oracle's (momentum 0.003)
+    after = eng.export_named()
+    for k in named:
+        if "moving" in k:
+            close(after[k], params[k], 2e-2, 2e-3, k)
+    # momentum update with l2 regulariser on conv kernels
+    for k, p in params.items():
+        if not p.requires_grad:
+            continue
+        gtot = p.grad + (2e-4 * named[k] if "conv" in k else 0)
+        want = named[k] - 0.1 * nb / 128 * gtot
+        close(after[k], want, 1e-2, 2e-4 + 0.02 * (0.1 * gtot).abs().max().item(), f"updated {k}")
+    print(f"resnet-{size} batch {nb}: worst relative gradient error {worst:.4f}, launches {eng.launches_per_step}")
+
+
+def test_native_graph_replay_and_eval(nat):
+    """CUDA-graph path: the captured step keeps training (loss falls on a fixed batch), the device step
+    counter advances once per step, eval counts hits, and a batch-size change captures a new graph."""
+    from distributedtf_b200.models import resnet
+    from distributedtf_b200.models.resnet_native import NativeResNetEngine
+    cfg = resnet.cifar10_config(8)
+    hp = {"opt_case": {"optimizer": "Momentum", "lr": 0.05, "momentum": 0.9}, "decay_steps": 0, "decay_rate": 0.1,
+          "weight_decay": 1e-4, "regularizer": "l2_regularizer", "initializer": "he_init", "batch_size": 64}
+    eng = NativeResNetEngine(cfg, hp, "cuda", seed=9, use_graphs=True)
+    g = torch.Generator().manual_seed(2)
+    imgs = torch.randint(0, 256, (64, 32, 32, 3), dtype=torch.uint8, generator=g).cuda()
+    labels = torch.randint(0, 10, (64,), generator=g).cuda()
+    losses = []
+    for i in range(30):
+        losses.append(eng.train_step_u8(imgs, labels, augment=False).clone())
+    torch.cuda.synchronize()
+    losses = [l.item() for l in losses]
+    assert eng.step == 30
+    assert all(math.isfinite(l) for l in losses)
+    assert losses[-1] < 0.6 * losses[0], losses
+    hits = eng.eval_batch_u8(imgs, labels).item()
+    assert 0 <= hits <= 64
+    assert hits > 8           # above chance (6.4) although the moving statistics barely moved in 30 steps
+    eng.train_step_u8(imgs[:40], labels[:40], augment=True)
+    torch.cuda.synchronize()
+    assert eng.step == 31 and ("train", 40) in eng._graphs and ("train_noaug", 64) in eng._graphs
