@@ -1,0 +1,309 @@
+#!/usr/bin/env python
+"""Headline benchmark: CIFAR-10 ResNet-32 population-based training throughput.
+
+    python bench.py --gpus N --steps K --warmup W [--impl native|restated|reference]
+
+Metric (BASELINE.json): *CIFAR-10 ResNet PBT images/sec (box, max over ranks)*.  One
+population member per GPU (population = N, weak scaling), ResNet-32 v2 on 32x32x3 images,
+batch 128, Momentum-SGD with l2 regulariser (the hand-tuned point of reference
+``cifar10_model.py:15-22``), synthetic uint8 data of CIFAR-10's shape, random-init weights.
+Every timed step is a complete training step: input gather + augmentation, forward, backward,
+BatchNorm statistic updates and the optimizer update.  One PBT exploit + explore event
+(rank by loss -> winner->loser state transfer -> perturb hyper-parameters) happens in the
+middle of the timed region when N > 1.
+
+For N > 1 the driver launches this file under ``torch.distributed.run``; ranks talk NCCL.
+The kernel-only number (`value`) draws batches from a device-resident 50 000-image dataset
+(153.6 MB > L2); the end-to-end number (`e2e`) additionally copies every batch from pinned host
+memory and reads the loss back every step.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "CIFAR-10 ResNet-32 PBT images/sec (box, max over ranks)"
+BATCH = 128
+DATASET_IMAGES = 50000
+
+
+def parse():
+    p = argparse.ArgumentParser()
+    p.add_argument("--gpus", type=int, default=1)
+    p.add_argument("--steps", type=int, default=200)
+    p.add_argument("--warmup", type=int, default=20)
+    p.add_argument("--impl", choices=["native", "restated", "reference"], default="native")
+    p.add_argument("--batch", type=int, default=BATCH)
+    p.add_argument("--resnet-size", type=int, default=32)
+    p.add_argument("--no-e2e", action="store_true")
+    p.add_argument("--no-graphs", action="store_true")
+    return p.parse_args()
+
+
+# --------------------------------------------------------------------------- clocks
+class ClockSampler:
+    """nvidia-smi sampling DURING the timed region (B200_PROFILING.md clocks line)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.gpu = gpu_index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.gpu)], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# --------------------------------------------------------------------------- main
+def main():
+    args = parse()
+    if args.impl == "reference":
+        # The reference cannot be installed or run here: it has no packaging files at all and needs
+        # TensorFlow 1.x + mpi4py + hyperopt (none in the image, no network).  See DESIGN.md.
+        print(json.dumps({"impl": "reference",
+                          "unavailable": "reference has no setup.py/pyproject (pip install fails) and needs "
+                                         "TensorFlow 1.x (tf.contrib), mpi4py, hyperopt, mpirun: none installable offline"}))
+        return 0
+
+    import torch
+    import torch.distributed as dist
+    from distributedtf_b200.hpspace import default_cifar_hparam
+    from distributedtf_b200 import explore
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world > 1:
+        args.gpus = world
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    hp = default_cifar_hparam()
+    hp["batch_size"] = args.batch
+    B = args.batch
+
+    # ---- member under test ----
+    from distributedtf_b200.models import resnet
+    cfg = resnet.cifar10_config(args.resnet_size)
+    symm_buf = None
+    if args.impl == "native":
+        from distributedtf_b200.models.resnet_native import NativeResNetEngine
+        from distributedtf_b200.parallel import exploit, symm
+
+        def alloc(n):
+            nonlocal symm_buf
+            symm_buf = exploit.MemberBuffer(n, dev)
+            symm.DIRECTORY.register_local(rank, symm_buf.buf, rank)
+            return symm_buf.alloc_state(n)
+
+        eng = NativeResNetEngine(cfg, hp, dev, seed=1234 + rank, use_graphs=not args.no_graphs, arena_alloc=alloc)
+        if world > 1:
+            symm.exchange_directory({rank: symm_buf.buf})
+    else:
+        from distributedtf_b200.models.engine_eager import EagerEngine
+        from distributedtf_b200.utils.data import cifar_preprocess_torch
+        init = resnet.init_params(cfg, hp["initializer"], 1234 + rank)
+        eng = EagerEngine(resnet.param_specs(cfg), lambda p, x, t: resnet.forward(cfg, p, x, t), init, hp, dev,
+                          compute_dtype=torch.bfloat16, lr_schedule=True)
+
+    # ---- synthetic CIFAR-shaped data: resident uint8 dataset larger than L2 + pinned host copy ----
+    g = torch.Generator().manual_seed(99 + rank)
+    host_images = torch.randint(0, 256, (DATASET_IMAGES, 32, 32, 3), dtype=torch.uint8, generator=g).pin_memory()
+    host_labels = torch.randint(0, 10, (DATASET_IMAGES,), dtype=torch.int32, generator=g).pin_memory()
+    dev_images, dev_labels = host_images.to(dev), host_labels.to(dev)
+    perm = torch.randperm(DATASET_IMAGES, generator=g)
+    nbatches = DATASET_IMAGES // B
+    idx_dev = perm[: nbatches * B].view(nbatches, B).to(dev)
+    idx_host = perm[: nbatches * B].view(nbatches, B)
+
+    def step_resident(i):
+        idx = idx_dev[i % nbatches]
+        if args.impl == "native":
+            return eng.train_step_u8(dev_images[idx], dev_labels[idx], augment=True)
+        x = cifar_preprocess_torch(dev_images[idx], True)
+        return eng.train_step(x, dev_labels[idx])
+
+    # staging for the end-to-end path: batch assembled in pinned memory, copied H2D every step
+    stage_img = torch.empty(B, 32, 32, 3, dtype=torch.uint8).pin_memory()
+    stage_lab = torch.empty(B, dtype=torch.int32).pin_memory()
+    loss_host = torch.zeros(1, dtype=torch.float32).pin_memory()
+    d_img = torch.empty(B, 32, 32, 3, dtype=torch.uint8, device=dev)
+    d_lab = torch.empty(B, dtype=torch.int32, device=dev)
+    h2d_bytes = stage_img.numel() + stage_lab.numel() * 4
+    d2h_bytes = 4
+
+    def step_e2e(i):
+        ih = idx_host[i % nbatches]
+        torch.index_select(host_images, 0, ih, out=stage_img)      # host-side batch assembly (data loader)
+        torch.index_select(host_labels, 0, ih, out=stage_lab)
+        d_img.copy_(stage_img, non_blocking=True)
+        d_lab.copy_(stage_lab, non_blocking=True)
+        if args.impl == "native":
+            loss = eng.train_step_u8(d_img, d_lab, augment=True)
+        else:
+            loss = eng.train_step(cifar_preprocess_torch(d_img, True), d_lab)
+        loss_host.copy_(loss.reshape(1), non_blocking=True)
+        torch.cuda.current_stream().synchronize()                   # the user reads the loss every step
+        return float(loss_host[0])
+
+    # ---- PBT event: rank members by loss, truncation selection, transfer, explore ----
+    exploit_ms = None
+    pbt_round = [0]
+
+    def pbt_event():
+        nonlocal exploit_ms
+        if world == 1:
+            return
+        loss = eng.last_loss.reshape(1).float().clone()
+        allv = [torch.zeros_like(loss) for _ in range(world)]
+        dist.all_gather(allv, loss)                                  # scores (device, NCCL plumbing)
+        scores = [-float(v.item()) for v in allv]                    # higher = better
+        order = sorted(range(world), key=lambda r: scores[r])
+        n = -(-world // 4)
+        pairs = [(order[world - n + i], order[i]) for i in range(n)]  # (winner, loser)
+        rnd = pbt_round[0]
+        if args.impl == "native":
+            exploit.copy_kernel(symm_buf.state_ptr + symm_buf.snapshot_offset(rnd), symm_buf.state_ptr,
+                                symm_buf.state_bytes)                 # publish my snapshot
+        barrier()                                                     # every snapshot is visible
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for winner, loser in pairs:
+            if winner == loser:
+                continue
+            if args.impl == "native":
+                if rank == loser:
+                    new_hp = dict(hp, opt_case=dict(hp["opt_case"]))
+                    explore.perturb_hparams(new_hp)
+                    new_hp["batch_size"] = B                          # keep the benchmark's batch fixed
+                    src = symm.DIRECTORY.pointer(winner) + symm_buf.snapshot_offset(rnd)
+                    exploit.copy_kernel(symm_buf.state_ptr, src, symm_buf.state_bytes,
+                                        hp_offset=eng.hp_state_offset, new_hp=eng.hparams_struct(new_hp),
+                                        zero=eng.round_cells, done_flag_ptr=symm_buf.control_ptr, epoch=rnd + 1,
+                                        arrive_ptr=symm_buf.control_ptr + 8)
+                    eng.adopt_hparams(new_hp)
+                    eng.after_state_replaced()
+            else:
+                flat = eng.flat.detach()
+                if rank == winner:
+                    for t in (flat, eng.slot0, eng.slot1):
+                        dist.send(t, dst=loser)
+                elif rank == loser:
+                    for t in (flat, eng.slot0, eng.slot1):
+                        dist.recv(t, src=winner)
+        e1.record()
+        e1.synchronize()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        exploit_ms = float(ms.item())
+        pbt_round[0] += 1
+
+    # ---- warm-up ----
+    for i in range(max(args.warmup, 3)):
+        step_resident(i)
+    barrier()
+
+    def timed(fn, steps, with_pbt):
+        sampler = ClockSampler(local)
+        sampler.start()
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.time()
+        e0.record()
+        for i in range(steps):
+            fn(1000 + i)
+            if with_pbt and i == steps // 2:
+                pbt_event()
+        e1.record()
+        barrier()
+        wall = time.time() - t0
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item()), wall, sampler.stop()
+
+    dev_ms, wall, clocks = timed(step_resident, args.steps, True)
+    value = world * B * args.steps / (dev_ms / 1e3)
+
+    e2e = None
+    if not args.no_e2e:
+        for i in range(3):
+            step_e2e(i)
+        e2e_ms, _, _ = timed(step_e2e, args.steps, False)
+        e2e = {"value": world * B * args.steps / (e2e_ms / 1e3), "unit": "images/s",
+               "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
+               "ms_per_step": e2e_ms / args.steps}
+
+    launches = getattr(eng, "launches_per_step", 0) * args.steps
+    if rank == 0:
+        out = {
+            "metric": METRIC, "value": value, "unit": "images/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
+            "data": "synthetic uint8 CIFAR-10-shaped images (random), random labels, random-init weights",
+            "impl": args.impl,
+            "config": {"model": f"CIFAR-10 ResNet-{args.resnet_size} v2 (resnet_model, 6n+2)",
+                       "global_batch": B * world, "per_gpu_batch": B, "seq_len": None,
+                       "parallelism": f"population {world} x 1 GPU (pbt{world})", "optimizer": "Momentum 0.9 + l2 2e-4",
+                       "l2": "inputs larger than L2: each step gathers a fresh batch from a 153.6 MB resident dataset",
+                       "pbt_event_in_timed_region": world > 1, "cuda_graphs": not args.no_graphs},
+            "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
+            "launches_per_step": getattr(eng, "launches_per_step", 0), "exploit_ms": exploit_ms,
+            "state_bytes": getattr(eng, "state_bytes", lambda: None)(), "wall_s": wall,
+        }
+        print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

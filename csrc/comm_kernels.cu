@@ -1,0 +1,313 @@
+// Communication-bound hot paths as single kernels over NVLink peer memory:
+//
+//   exploit transfer   winner -> loser copy of the whole member state (weights + optimizer slots +
+//                      BN moving statistics + step counter) read straight out of the winner GPU's
+//                      memory with 16-byte peer loads, fused with writing the loser's new (explored)
+//                      hyper-parameter block, resetting its per-round accumulators and publishing a
+//                      completion epoch.   Replaces the master's `rm` + `cp` over a shared file system
+//                      (reference pbt_cluster.py:145-147,168-181).
+//   score board        per-member eval score pushed into the master rank's memory with a release
+//                      store of the round epoch.  Replaces the pickled GET gather as the source of the
+//                      ranking input (reference pbt_cluster.py:114-128).
+//   all-reduce + update one-shot all-reduce of the gradient arena over peer loads fused with 1/W
+//                      scaling, regulariser gradient, the optimizer rule and the bf16 weight re-pack
+//                      (reference: dormant MirroredStrategy path, distribution_utils.py:41-47, followed
+//                      by TF's per-variable Apply* ops, resnet_run_loop.py:552-586).
+//
+// Memory model: cross-GPU flags are written with st.release.sys after a __threadfence_system and
+// polled with ld.acquire.sys; all waits are watchdog-protected (trap, never hang).
+#include "common.cuh"
+#include "dtf_b200.h"
+
+namespace dtf {
+
+DTF_DEVINL void st_release_sys(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+DTF_DEVINL unsigned long long ld_acquire_sys(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+DTF_DEVINL uint4 ld_peer16(const uint4* p) {
+    uint4 r;   // plain (coherent) load: peer memory bypasses the local L2 anyway
+    asm volatile("ld.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory");
+    return r;
+}
+DTF_DEVINL void wait_flag_ge(const unsigned long long* p, unsigned long long want, unsigned int site) {
+    if (ld_acquire_sys(p) >= want) return;
+    const uint64_t t0 = globaltimer_ns();
+    while (ld_acquire_sys(p) < want) {
+        if (globaltimer_ns() - t0 > kWatchdogNs) device_fail(0x2000u | site);
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// exploit: dst[0..bytes) = src[0..bytes) except [hp_off, hp_off+hp_bytes) := new hyper-parameters,
+//          zero[0..zero_bytes) = 0, then *done_flag = epoch (release)
+// `src` may be a peer-mapped pointer (pull) or `dst` may be (push): the code is the same.
+// ---------------------------------------------------------------------------------------
+constexpr int kCopyUnroll = 8;
+
+__global__ void __launch_bounds__(512)
+exploit_copy_kernel(uint4* __restrict__ dst, const uint4* __restrict__ src, long long n_vec,
+                    long long hp_vec_off, int hp_vecs, const __grid_constant__ DtfHparams hp,
+                    uint4* __restrict__ zero, long long zero_vecs,
+                    unsigned long long* done_flag, unsigned long long epoch, unsigned int* arrive_counter) {
+    const long long tid = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    const long long nthreads = (long long)gridDim.x * blockDim.x;
+    long long i = tid;
+    for (; i + (kCopyUnroll - 1) * nthreads < n_vec; i += kCopyUnroll * nthreads) {
+        uint4 v[kCopyUnroll];
+#pragma unroll
+        for (int u = 0; u < kCopyUnroll; ++u) v[u] = ld_peer16(src + i + u * nthreads);
+#pragma unroll
+        for (int u = 0; u < kCopyUnroll; ++u) {
+            const long long k = i + u * nthreads;
+            if (k < hp_vec_off || k >= hp_vec_off + hp_vecs) dst[k] = v[u];
+        }
+    }
+    for (; i < n_vec; i += nthreads)
+        if (i < hp_vec_off || i >= hp_vec_off + hp_vecs) dst[i] = ld_peer16(src + i);
+    // explore write: the (already perturbed) hyper-parameter block replaces the winner's
+    if (hp_vecs > 0 && tid < hp_vecs) {
+        const uint4* hv = reinterpret_cast<const uint4*>(&hp);
+        constexpr int kHpVecs = sizeof(DtfHparams) / 16;
+        dst[hp_vec_off + tid] = tid < kHpVecs ? hv[tid] : make_uint4(0, 0, 0, 0);
+    }
+    // loser state reset (per-round metric accumulators)
+    for (long long z = tid; z < zero_vecs; z += nthreads) zero[z] = make_uint4(0, 0, 0, 0);
+    // publish completion: last CTA to finish releases the flag
+    if (done_flag != nullptr) {
+        __threadfence_system();
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            const unsigned int prev = atomicAdd(arrive_counter, 1u);
+            if (prev == gridDim.x - 1) {
+                *arrive_counter = 0;
+                __threadfence_system();
+                st_release_sys(done_flag, epoch);
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// score board: slot = {float score; uint32 count; uint64 epoch}
+// ---------------------------------------------------------------------------------------
+__global__ void score_publish_kernel(DtfScoreSlot* __restrict__ board_slot, const int* __restrict__ correct,
+                                     int total, unsigned long long epoch, int reset_counter, int* correct_rw) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) {
+        const int c = *correct;
+        board_slot->score = total > 0 ? static_cast<float>(c) / static_cast<float>(total) : 0.f;
+        board_slot->count = static_cast<unsigned int>(total);
+        __threadfence_system();
+        st_release_sys(&board_slot->epoch, epoch);
+        if (reset_counter) *correct_rw = 0;
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// fused one-shot all-reduce + optimizer update (data-parallel member, W = 2 or 4 GPUs)
+// ---------------------------------------------------------------------------------------
+DTF_DEVINL float schedule_lr2(const DtfHparams& hp, long long step) {
+    int i = 0;
+    while (i < hp.n_boundaries && step > hp.boundaries[i]) ++i;
+    return hp.lr_values[i];
+}
+
+DTF_DEVINL void pack_store2(const DtfOptSegment& s, dtf_bf16* pack, int local, float w) {
+    const int ci = local % s.Cin;
+    const int rest = local / s.Cin;
+    const int tap = rest % s.taps;
+    const int co = rest / s.taps;
+    const dtf_bf16 h = __float2bfloat16(w);
+    if (s.fwd_pack_off >= 0) {
+        const int k = tap * s.Cin + ci;
+        pack[s.fwd_pack_off + ((k >> 3) * s.Cout + co) * 8 + (k & 7)] = h;
+    }
+    if (s.dgrad_pack_off >= 0) {
+        const int k = tap * s.Cout + co;
+        pack[s.dgrad_pack_off + ((k >> 3) * s.Cin + ci) * 8 + (k & 7)] = h;
+    }
+}
+
+__global__ void __launch_bounds__(256)
+allreduce_update_kernel(const __grid_constant__ DtfAllreduceUpdate P) {
+    __shared__ DtfHparams hp;
+    const int W = P.world;
+    // ---- entry barrier: tell every peer that my gradients for `epoch` are complete, then wait for theirs
+    if (blockIdx.x == 0 && threadIdx.x < W) {
+        __threadfence_system();
+        st_release_sys(P.peer_ready[threadIdx.x] + P.rank, P.epoch);     // my slot in peer's ready[]
+    }
+    if (threadIdx.x == 0) hp = *P.hp;
+    if (threadIdx.x < W) wait_flag_ge(P.local_ready + threadIdx.x, P.epoch, 1);
+    __syncthreads();
+    const long long step = *P.step;
+    const float lr = schedule_lr2(hp, step - 1);
+    float lr_adam = lr;
+    if (hp.optimizer == DTF_OPT_ADAM) {
+        const float t = static_cast<float>(step);
+        lr_adam = lr * sqrtf(1.f - powf(0.999f, t)) / (1.f - powf(0.9f, t));
+    }
+    const int2 ch = reinterpret_cast<const int2*>(P.chunks)[blockIdx.x];
+    const DtfOptSegment s = P.segs[ch.x];
+    const float gs = P.grad_scale * hp.inv_loss_scale;
+    for (int i = threadIdx.x; i < DTF_OPT_CHUNK; i += blockDim.x) {
+        const int local = ch.y + i;
+        if (local >= s.count) break;
+        const int idx = s.offset + local;
+        float g = 0.f;
+#pragma unroll 4
+        for (int w = 0; w < W; ++w) g += P.peer_grads[w][idx];        // one-shot: every rank reads all replicas
+        g *= gs;
+        const float w0 = P.params[idx];
+        if (s.regularized) {
+            if (hp.regularizer == DTF_REG_L1 || hp.regularizer == DTF_REG_L1_L2)
+                g += hp.weight_decay * (w0 > 0.f ? 1.f : (w0 < 0.f ? -1.f : 0.f));
+            if (hp.regularizer == DTF_REG_L2 || hp.regularizer == DTF_REG_L1_L2) g += hp.weight_decay * w0;
+        }
+        float s0 = P.slot0[idx], s1 = P.slot1[idx], nw;
+        switch (hp.optimizer) {
+            case DTF_OPT_GD: nw = w0 - lr * g; break;
+            case DTF_OPT_MOMENTUM: s0 = hp.momentum * s0 + g; nw = w0 - lr * s0; break;
+            case DTF_OPT_ADAGRAD: s0 += g * g; nw = w0 - lr * g * rsqrtf(s0); break;
+            case DTF_OPT_ADADELTA: {
+                s0 = 0.95f * s0 + 0.05f * g * g;
+                const float upd = sqrtf(s1 + 1e-8f) * rsqrtf(s0 + 1e-8f) * g;
+                s1 = 0.95f * s1 + 0.05f * upd * upd;
+                nw = w0 - lr * upd;
+                break;
+            }
+            case DTF_OPT_ADAM:
+                s0 = 0.9f * s0 + 0.1f * g;
+                s1 = 0.999f * s1 + 0.001f * g * g;
+                nw = w0 - lr_adam * s0 / (sqrtf(s1) + 1e-8f);
+                break;
+            default:
+                s0 = hp.grad_decay * s0 + (1.f - hp.grad_decay) * g * g;
+                s1 = hp.momentum * s1 + lr * g * rsqrtf(s0 + 1e-10f);
+                nw = w0 - s1;
+        }
+        P.params[idx] = nw;
+        P.slot0[idx] = s0;
+        P.slot1[idx] = s1;
+        if (s.pack) pack_store2(s, P.pack, local, nw);
+    }
+    // ---- exit signal: once every CTA of this rank has consumed the peers' gradients, tell the peers
+    // that their gradient arenas may be zeroed for the next step (checked by dtf_dp_step_begin)
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence_system();
+        const unsigned int prev = atomicAdd(P.arrive_counter, 1u);
+        if (prev == gridDim.x - 1) {
+            *P.arrive_counter = 0;
+            __threadfence_system();
+            for (int w = 0; w < W; ++w) st_release_sys(P.peer_done[w] + P.rank, P.epoch);
+        }
+    }
+}
+
+// step begin for a DP member: wait until every peer has finished reading my gradients of the
+// previous step, then zero the accumulators and bump the step counter
+__global__ void __launch_bounds__(256)
+dp_step_begin_kernel(float4* __restrict__ zero, long long n_vec, long long* __restrict__ step_ptr,
+                     const unsigned long long* __restrict__ local_done, int world, unsigned long long prev_epoch) {
+    if (threadIdx.x < world) wait_flag_ge(local_done + threadIdx.x, prev_epoch, 2);
+    __syncthreads();
+    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n_vec;
+         i += (long long)gridDim.x * blockDim.x)
+        zero[i] = z;
+    if (blockIdx.x == 0 && threadIdx.x == 0) *step_ptr += 1;
+}
+
+}  // namespace dtf
+
+#define DTF_CHECK_LAUNCH() (cudaGetLastError() == cudaSuccess ? DTF_OK : DTF_ERR_CUDA)
+
+extern "C" int dtf_exploit_copy(void* dst, const void* src, long long bytes, long long hp_offset,
+                                const DtfHparams* new_hp, void* zero_region, long long zero_bytes,
+                                unsigned long long* done_flag, unsigned long long epoch,
+                                unsigned int* arrive_counter, int max_ctas, cudaStream_t stream) {
+    if ((bytes & 15) || (zero_bytes & 15) || (hp_offset & 15)) return DTF_ERR_ARG;
+    if (((uintptr_t)dst & 15) || ((uintptr_t)src & 15)) return DTF_ERR_ARG;
+    if (done_flag != nullptr && arrive_counter == nullptr) return DTF_ERR_ARG;
+    const long long n_vec = bytes / 16;
+    const int hp_vecs = new_hp ? static_cast<int>((sizeof(DtfHparams) + 15) / 16) : 0;
+    DtfHparams hp_val;
+    if (new_hp) hp_val = *new_hp; else memset(&hp_val, 0, sizeof(hp_val));
+    long long want = (n_vec + 512LL * dtf::kCopyUnroll - 1) / (512LL * dtf::kCopyUnroll);
+    if (want < 1) want = 1;
+    int cap = max_ctas > 0 ? max_ctas : 148 * 2;
+    const int grid = static_cast<int>(want < cap ? want : cap);
+    dtf::exploit_copy_kernel<<<grid, 512, 0, stream>>>(
+        reinterpret_cast<uint4*>(dst), reinterpret_cast<const uint4*>(src), n_vec,
+        new_hp ? hp_offset / 16 : -1, hp_vecs, hp_val, reinterpret_cast<uint4*>(zero_region), zero_bytes / 16,
+        done_flag, epoch, arrive_counter);
+    return DTF_CHECK_LAUNCH();
+}
+
+extern "C" int dtf_score_publish(DtfScoreSlot* board_slot, const int* correct, int total,
+                                 unsigned long long epoch, int reset_counter, int* correct_rw,
+                                 cudaStream_t stream) {
+    dtf::score_publish_kernel<<<1, 32, 0, stream>>>(board_slot, correct, total, epoch, reset_counter, correct_rw);
+    return DTF_CHECK_LAUNCH();
+}
+
+extern "C" int dtf_allreduce_update(const DtfAllreduceUpdate* p, cudaStream_t stream) {
+    if (p->world < 1 || p->world > DTF_MAX_DP) return DTF_ERR_ARG;
+    dtf::allreduce_update_kernel<<<p->n_chunks, 256, 0, stream>>>(*p);
+    return DTF_CHECK_LAUNCH();
+}
+
+extern "C" int dtf_dp_step_begin(float* zero_base, long long zero_floats, long long* step,
+                                 const unsigned long long* local_done, int world, unsigned long long prev_epoch,
+                                 cudaStream_t stream) {
+    if (zero_floats % 4 != 0 || ((uintptr_t)zero_base & 15) != 0) return DTF_ERR_ARG;
+    const long long n_vec = zero_floats / 4;
+    long long blocks = (n_vec + 255) / 256;
+    if (blocks > 148 * 4) blocks = 148 * 4;
+    if (blocks < 1) blocks = 1;
+    dtf::dp_step_begin_kernel<<<static_cast<int>(blocks), 256, 0, stream>>>(
+        reinterpret_cast<float4*>(zero_base), n_vec, step, local_done, world, prev_epoch);
+    return DTF_CHECK_LAUNCH();
+}
+
+// ---------------------------------------------------------------------------------------
+// symmetric memory plumbing (host): allocation + CUDA IPC handles.  These DO allocate.
+// ---------------------------------------------------------------------------------------
+extern "C" int dtf_symm_alloc(long long bytes, void** out) {
+    void* p = nullptr;
+    if (cudaMalloc(&p, static_cast<size_t>(bytes)) != cudaSuccess) return DTF_ERR_CUDA;
+    if (cudaMemset(p, 0, static_cast<size_t>(bytes)) != cudaSuccess) return DTF_ERR_CUDA;
+    *out = p;
+    return DTF_OK;
+}
+extern "C" int dtf_symm_free(void* p) { return cudaFree(p) == cudaSuccess ? DTF_OK : DTF_ERR_CUDA; }
+extern "C" int dtf_ipc_get_handle(void* p, unsigned char* handle64) {
+    cudaIpcMemHandle_t h;
+    if (cudaIpcGetMemHandle(&h, p) != cudaSuccess) return DTF_ERR_CUDA;
+    memcpy(handle64, &h, sizeof(h));
+    return DTF_OK;
+}
+extern "C" int dtf_ipc_open_handle(const unsigned char* handle64, void** out) {
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle64, sizeof(h));
+    void* p = nullptr;
+    if (cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) return DTF_ERR_CUDA;
+    *out = p;
+    return DTF_OK;
+}
+extern "C" int dtf_ipc_close(void* p) { return cudaIpcCloseMemHandle(p) == cudaSuccess ? DTF_OK : DTF_ERR_CUDA; }
+extern "C" int dtf_enable_peer(int peer_device) {
+    cudaError_t e = cudaDeviceEnablePeerAccess(peer_device, 0);
+    if (e == cudaErrorPeerAccessAlreadyEnabled) { cudaGetLastError(); return DTF_OK; }
+    return e == cudaSuccess ? DTF_OK : DTF_ERR_CUDA;
+}
+extern "C" int dtf_last_cuda_error(char* buf, int n) {
+    const char* s = cudaGetErrorString(cudaPeekAtLastError());
+    snprintf(buf, n, "%s", s);
+    return DTF_OK;
+}

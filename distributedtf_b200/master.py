@@ -188,7 +188,8 @@ class PBTCluster:
             loser[1] = winner[1]
             loser[2] = copy.deepcopy(winner[2])
             extras: Dict[str, Any] = {"path": self.exploit_path, "src_id": winner_id,
-                                      "src_rank": owner[winner_id], "round": self.rounds_done}
+                                      "src_rank": owner[winner_id], "round": self.rounds_done,
+                                      "explore_follows": bool(self.do_explore)}
             if self.exploit_path == "file":
                 self.exploit_bytes += self.copyfiles(self.member_dir(winner_id), self.member_dir(loser_id))
             per_rank.setdefault(owner[loser_id], []).append([loser_id, loser[1], loser[2], extras])

@@ -62,6 +62,9 @@ class GpuMember(ModelBase):
         self.eval_batches = eval_batches
         self.device_times: Dict[str, float] = {"train": 0.0, "eval": 0.0, "exploit": 0.0}
         self.train_set, self.eval_set = self.build_datasets()
+        self.symm = None                 # symmetric (peer-addressable) buffer, native engine on CUDA only
+        self._pending_exploit: Optional[Dict[str, Any]] = None
+        self.rounds_trained = 0
         self.engine = self.build_engine()
         self._train_iter = BatchIterator(len(self.train_set), int(self.hparams["batch_size"]), True,
                                          seed=1000 + cluster_id, device=self.device)
@@ -141,7 +144,16 @@ class GpuMember(ModelBase):
             return float("nan")
         return float(correct.item()) / max(seen, 1)
 
+    def make_symmetric_alloc(self, state_bytes: int) -> torch.Tensor:
+        """``arena_alloc`` callback for native engines: puts the member state in exportable memory
+        (state | snapshot 0 | snapshot 1 | control) and lists it in the symmetric directory."""
+        from ..parallel import exploit, symm
+        self.symm = exploit.MemberBuffer(state_bytes, self.device)
+        symm.DIRECTORY.register_local(self.cluster_id, self.symm.buf, int(os.environ.get("RANK", "0")))
+        return self.symm.alloc_state(state_bytes)
+
     def train(self, num_epoch: int, total_epochs: int) -> None:
+        self.flush_exploit()
         rows = []
         for e in range(num_epoch):
             self.train_one_epoch()
@@ -150,6 +162,10 @@ class GpuMember(ModelBase):
         self.bump_epochs(num_epoch)
         if math.isnan(self.accuracy):
             return                      # the worker drops the member; nothing to persist
+        if self.symm is not None:       # publish the round's snapshot where peers can pull it
+            from ..parallel import exploit
+            exploit.publish(self, self.rounds_trained)
+        self.rounds_trained += 1
         self.save()
         report.append_csv(os.path.join(self.ensure_dir(), "learning_curve.csv"), self.csv_fields_now(), rows)
 
@@ -164,9 +180,43 @@ class GpuMember(ModelBase):
 
     # ------------------------------------------------------------------ state
     def on_hparams_changed(self) -> None:
-        self.engine.set_hparams(self.hparams)
+        if self._pending_exploit is not None and not self._pending_exploit.get("explore_follows", False):
+            self.flush_exploit()
+        elif self._pending_exploit is None:
+            self.engine.set_hparams(self.hparams)
+        # else: SET arrived and EXPLORE follows; the fused kernel runs from perturb_hparams()
+
+    def perturb_hparams(self) -> None:
+        from .. import explore as _explore
+        _explore.perturb_hparams(self.hparams, self._rng, tuple(self._perturb_factors))
+        if self._pending_exploit is not None:
+            self.flush_exploit()
+        else:
+            self.engine.set_hparams(self.hparams)
+
+    def get_values(self):
+        self.flush_exploit()
+        return super().get_values()
+
+    def flush_exploit(self) -> None:
+        """Run a deferred device exploit: one kernel copies the winner's snapshot, writes this
+        member's (possibly just explored) hyper-parameter block and resets its round cells."""
+        extras, self._pending_exploit = self._pending_exploit, None
+        if extras is None:
+            return
+        from ..parallel import exploit
+        with self._timed("exploit"):
+            if extras.get("path") == "p2p" and hasattr(self.engine, "hparams_struct"):
+                new_hp = self.engine.hparams_struct(self.hparams)
+                exploit.receive(self, extras, new_hp=new_hp)
+                self.engine.adopt_hparams(self.hparams)
+            else:
+                exploit.receive(self, extras)
+                self.engine.set_hparams(self.hparams, keep_slots=True) if hasattr(self.engine, "adopt_hparams") \
+                    else self.engine.set_hparams(self.hparams)
 
     def save(self) -> None:
+        self.flush_exploit()
         self.engine.synchronize()
         ckpt.save_checkpoint(self.ensure_dir(), self.engine.state_tensors(), step=self.engine.step,
                              optimizer=self.hparams["opt_case"]["optimizer"],
@@ -187,12 +237,11 @@ class GpuMember(ModelBase):
         if extras.get("src_id") == self.cluster_id:
             return
         path = extras.get("path", "file")
-        with self._timed("exploit"):
-            if path == "file":
+        if path == "file":
+            with self._timed("exploit"):
                 self.restore()          # the master already copied the winner's files here
-            else:
-                from ..parallel import exploit
-                exploit.receive(self, extras)
+        else:
+            self._pending_exploit = dict(extras)     # runs fused with the explore write (flush_exploit)
 
     def donate_state(self, extras: Dict[str, Any]) -> None:
         from ..parallel import exploit

@@ -45,7 +45,8 @@ class Cifar10Model(GpuMember):
         seed = 7919 * (self.cluster_id + 1)
         if self.engine_kind == "native":
             from .resnet_native import NativeResNetEngine
-            return NativeResNetEngine(self.net_cfg, self.hparams, self.device, seed=seed, dtype=self.dtype)
+            return NativeResNetEngine(self.net_cfg, self.hparams, self.device, seed=seed, dtype=self.dtype,
+                                      arena_alloc=self.make_symmetric_alloc)
         from .engine_eager import EagerEngine
         cfg = self.net_cfg
         init = resnet.init_params(cfg, self.hparams.get("initializer", "None"), seed)

