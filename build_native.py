@@ -21,7 +21,7 @@ OBJ_DIR = os.path.join(ROOT, "build", "obj")
 LIB = os.path.join(OUT_DIR, "libdtf_b200.so")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 NVCC_FLAGS = ARCH + ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-I" + os.path.join(ROOT, "include"),
-                     "-I" + SRC, "--expt-relaxed-constexpr"]
+                     "-I" + SRC, "--expt-relaxed-constexpr"] + (["-DDTF_TIMING"] if os.environ.get("DTF_TIMING") else [])
 
 
 def nvcc() -> str:

@@ -1,0 +1,588 @@
+// 3x3 / stride-1 / pad-1 convolutions (28 of ResNet-32's 34 convs, forward + dgrad + wgrad) on
+// tcgen05 with a *halo tile* and *shifted descriptor views*.
+//
+// Idea: number the output pixels on a virtual grid  NB x (H+1) x (W+1)  in which one extra zero
+// row per image and one extra zero column per row act as shared padding.  On that grid a 3x3 tap
+// (dy, dx) is the constant flat shift  dy*(W+1) + dx.  A CTA therefore loads, for 128 consecutive
+// virtual pixels, ONE halo tile of 128 + 2(W+1) + 2 input rows into shared memory — every input
+// element read, BatchNorm+ReLU'd and bf16-packed once instead of nine times — stored in the
+// no-swizzle UMMA layout [c/8][row][8].  The nine taps are then nine tcgen05.mma issues whose
+// A-descriptor start address is the tile base advanced by (shift * 16 bytes); no im2col copy
+// exists anywhere.  Virtual pixels that fall on the padding row/column are computed and dropped
+// in the epilogue (6 % waste at W = 32, 21 % at W = 8).
+//
+// wgrad uses the same halo tile viewed MN-major (K = pixels): per 16-pixel K step one MMA per tap
+// with N = Cin into TMEM columns [tap*Cin, (tap+1)*Cin), accumulating over all tiles of the CTA.
+//
+// Warp roles: 0-3 epilogue, 4 MMA issuer (+ TMEM alloc, weight bulk copy), 5-11 gather (one halo
+// row per thread).  4 operand stages, 2 accumulators; two tiles' loads are in flight per gather
+// thread before anything is stored, to cover L2 latency.
+#include "conv_common.cuh"
+
+#include <cstdlib>
+
+namespace dtf {
+
+// optional in-kernel timeline (CTA 0 only): compile with -DDTF_TIMING, read with dtf_debug_timeline
+#ifdef DTF_TIMING
+__device__ unsigned long long g_timeline[64];
+#define DTF_MARK(slot) do { if (blockIdx.x == 0) g_timeline[slot] = globaltimer_ns(); } while (0)
+#else
+#define DTF_MARK(slot) do { } while (0)
+#endif
+
+constexpr int kHGatherWarps = 7;
+constexpr int kHThreads = (kEpiWarps + 1 + kHGatherWarps) * 32;   // 384
+constexpr int kHGatherThreads = kHGatherWarps * 32;               // 224
+constexpr int kHStages = 4;
+
+struct HaloGeom {
+    FastDiv div_wp, div_hp;
+    int H, W, Wp, Hp;
+    int total;         // NB * Hp * Wp virtual pixels
+    int num_tiles;
+    int rows;          // halo rows per tile = 128 + 2*Wp + 2
+    int cs;            // chunk stride in bytes = rows * 16 (rounded to 128)
+    int c8;            // input channel chunks
+    int sign;          // +1 forward, -1 dgrad (gradient gather reads o - tap)
+    int stage_bytes;
+    int smem_b_off, smem_a_off;
+    int tap0, ntaps;   // wgrad: taps handled by blockIdx.y == 0; the rest by y == 1
+    int gy_c8;         // wgrad: output-channel chunks
+};
+
+struct __align__(16) HaloHeader {
+    uint64_t full[kHStages];
+    uint64_t empty[kHStages];
+    uint64_t acc_full[2];
+    uint64_t acc_empty[2];
+    uint64_t bfull;
+    uint32_t tmem_base;
+    uint32_t pad;
+};
+
+// virtual flat index -> dense pixel index; false for padding positions
+DTF_DEVINL bool decode_virtual(int q, const HaloGeom& G, uint32_t& pix) {
+    if (q < 0 || q >= G.total) return false;
+    const uint32_t R = fdiv(static_cast<uint32_t>(q), G.div_wp);
+    const uint32_t xx = static_cast<uint32_t>(q) - R * G.Wp;
+    const uint32_t n = fdiv(R, G.div_hp);
+    const uint32_t yy = R - n * G.Hp;
+    if (xx >= static_cast<uint32_t>(G.W) || yy >= static_cast<uint32_t>(G.H)) return false;
+    pix = (n * G.H + yy) * G.W + xx;
+    return true;
+}
+
+// prologue on one 16-byte chunk (8 channels starting at cb)
+DTF_DEVINL uint4 apply_prologue(int mode, const uint4& raw, const uint4& raw2, const float* p0, const float* p1,
+                                const float* p2, int cb) {
+    if (mode == DTF_PRO_NONE) return raw;
+    float f[8];
+    unpack8(raw, f);
+    const float4 a0 = *reinterpret_cast<const float4*>(p0 + cb), a1 = *reinterpret_cast<const float4*>(p0 + cb + 4);
+    const float4 b0 = *reinterpret_cast<const float4*>(p1 + cb), b1 = *reinterpret_cast<const float4*>(p1 + cb + 4);
+    const float s[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+    const float t[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+    if (mode == DTF_PRO_BN_RELU) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) f[i] = fmaxf(fmaf(f[i], s[i], t[i]), 0.f);
+    } else {
+        float x[8];
+        unpack8(raw2, x);
+        const float4 c0 = *reinterpret_cast<const float4*>(p2 + cb), c1 = *reinterpret_cast<const float4*>(p2 + cb + 4);
+        const float u[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
+#pragma unroll
+        for (int i = 0; i < 8; ++i) f[i] = fmaf(f[i], s[i], fmaf(x[i], t[i], u[i]));
+    }
+    return pack8(f);
+}
+
+// Load + prologue + store the chunks of NJ rows (C8 chunks each): every 16-byte load of the batch
+// is issued before the first one is consumed; all indices are compile-time.
+struct RowJob {
+    const dtf_bf16* src;
+    const dtf_bf16* src2;
+    uint32_t dst;          // shared address of chunk 0 of this row
+    bool valid;
+};
+
+template <int C8, int NJ>
+DTF_DEVINL void gather_rows(const RowJob (&jobs)[NJ], int njobs, int cs, int mode, const float* p0,
+                            const float* p1, const float* p2) {
+    uint4 a[NJ][C8], b[NJ][C8];
+#pragma unroll
+    for (int u = 0; u < NJ; ++u)
+#pragma unroll
+        for (int c = 0; c < C8; ++c) {
+            a[u][c] = make_uint4(0, 0, 0, 0);
+            b[u][c] = a[u][c];
+            if (u < njobs && jobs[u].valid) {
+                a[u][c] = ldg16(jobs[u].src + c * 8);
+                if (mode == DTF_PRO_BN_BWD) b[u][c] = ldg16(jobs[u].src2 + c * 8);
+            }
+        }
+#pragma unroll
+    for (int u = 0; u < NJ; ++u)
+#pragma unroll
+        for (int c = 0; c < C8; ++c)
+            if (u < njobs) {
+                const uint4 v = jobs[u].valid ? apply_prologue(mode, a[u][c], b[u][c], p0, p1, p2, c * 8)
+                                              : make_uint4(0, 0, 0, 0);
+                sts16(jobs[u].dst + c * cs, v);
+            }
+}
+
+// =========================================================================================
+// forward / dgrad
+// =========================================================================================
+template <int C8>
+__global__ void __launch_bounds__(kHThreads, 1)
+conv3x3_kernel(const __grid_constant__ DtfConvGemm P, const __grid_constant__ HaloGeom G) {
+    constexpr int kPairs = C8 / 2;            // UMMA K steps (16 channels) per tap
+    constexpr int kBatch = C8 == 8 ? 1 : 2;   // tiles whose loads are in flight together per gather thread
+    extern __shared__ __align__(1024) uint8_t smem[];
+    HaloHeader* hdr = reinterpret_cast<HaloHeader*>(smem);
+    SmemConsts* cst = reinterpret_cast<SmemConsts*>(smem + 1024);
+    uint8_t* smem_b = smem + G.smem_b_off;
+    uint8_t* smem_a = smem + G.smem_a_off;
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int N = P.N;
+    const uint32_t acc_cols = tmem_cols_pow2(2 * N);
+    const int my_tiles = (G.num_tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
+
+    if (tid == 0) {
+        for (int i = 0; i < kHStages; ++i) {
+            mbar_init(smem_u32(&hdr->full[i]), kHGatherThreads);
+            mbar_init(smem_u32(&hdr->empty[i]), 1);
+        }
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(smem_u32(&hdr->acc_full[i]), 1);
+            mbar_init(smem_u32(&hdr->acc_empty[i]), kEpiWarps * 32);
+        }
+        mbar_init(smem_u32(&hdr->bfull), 1);
+        mbar_fence_init();
+    }
+    fill_prologue(P.a, cst->p0, cst->p1, cst->p2, tid, kHThreads);
+    if (P.epi_mode == DTF_EPI_RELU_MASK)
+        for (int c = tid; c < N; c += kHThreads)
+            bn_fwd_consts(P.epi_bn, c, cst->e_scale[c], cst->e_shift[c], cst->e_mean[c], cst->e_invstd[c]);
+    for (int c = tid; c < 2 * kMaxC; c += kHThreads) (&cst->bins[0][0])[c] = 0.f;
+    if (warp == kMmaWarp) tmem_alloc(smem_u32(&hdr->tmem_base), acc_cols);
+    if (blockIdx.x == 0 && P.a.update_running && P.a.mode == DTF_PRO_BN_RELU && !P.a.bn.use_running)
+        update_running(P.a.bn, tid, kHThreads);
+    if (tid == 0) DTF_MARK(0);
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    const uint32_t tmem_base = hdr->tmem_base;
+    if (tid == 0) DTF_MARK(1);
+
+    if (warp == kMmaWarp) {
+        // Warp-uniform loop: every lane computes the (uniform) descriptors, one elected lane issues.
+        // (Issuing from a divergent `lane == 0` branch makes ptxas serialise every operand through
+        // R2UR waterfall loops: ~170 cycles per MMA instead of ~20.)
+        const uint32_t wbytes = static_cast<uint32_t>(P.kchunks) * N * 16u;
+        if (elect_one()) {
+            mbar_arrive_expect_tx(smem_u32(&hdr->bfull), wbytes);
+            bulk_g2s(smem_u32(smem_b), P.wpk, wbytes, smem_u32(&hdr->bfull));
+        }
+        __syncwarp();
+        mbar_wait(smem_u32(&hdr->bfull), 0, 0x31);
+        DTF_MARK(2);
+        const uint32_t idesc = umma_idesc_bf16(kTileM, N, false, false);
+        // Descriptor arithmetic hoisted out of the tile loop: per MMA only two 32-bit adds remain.
+        // (A descriptor low word = start address >> 4; shifting the view by `s` halo rows adds `s`.)
+        uint32_t a_off[9][kPairs], b_off[9][kPairs];
+#pragma unroll
+        for (int tap = 0; tap < 9; ++tap) {
+            const int dy = tap / 3 - 1, dx = tap % 3 - 1;
+            const int shift = (1 + G.sign * dy) * G.Wp + (1 + G.sign * dx);     // halo row of output row 0
+#pragma unroll
+            for (int kp = 0; kp < kPairs; ++kp) {
+                a_off[tap][kp] = static_cast<uint32_t>(shift + ((2 * kp) * G.cs >> 4));
+                b_off[tap][kp] = static_cast<uint32_t>((tap * C8 + 2 * kp) * N);
+            }
+        }
+        const uint64_t adesc0 = umma_desc(smem_u32(smem_a), G.cs, 128);
+        const uint64_t bdesc0 = umma_desc(smem_u32(smem_b), N * 16, 128);
+        const uint32_t stage_units = static_cast<uint32_t>(G.stage_bytes >> 4);
+        for (int it = 0; it < my_tiles; ++it) {
+            const uint32_t a = it & 1, st = it % kHStages;
+            mbar_wait(smem_u32(&hdr->acc_empty[a]), ((it >> 1) & 1) ^ 1, 0x32);
+            mbar_wait(smem_u32(&hdr->full[st]), (it / kHStages) & 1, 0x33);
+            tc_fence_after_sync();
+            if (it < 4) DTF_MARK(8 + it);
+            const uint64_t adesc_st = adesc0 + st * stage_units;
+            const uint32_t d_tmem = tmem_base + a * N;
+            if (elect_one()) {
+#pragma unroll
+                for (int tap = 0; tap < 9; ++tap)
+#pragma unroll
+                    for (int kp = 0; kp < kPairs; ++kp)
+                        umma_bf16(d_tmem, adesc_st + a_off[tap][kp], bdesc0 + b_off[tap][kp], idesc, (tap | kp) != 0);
+                umma_commit(smem_u32(&hdr->empty[st]));
+                umma_commit(smem_u32(&hdr->acc_full[a]));
+            }
+            __syncwarp();
+            if (it < 4) DTF_MARK(12 + it);
+        }
+    } else if (warp > kMmaWarp) {
+        // ================= gather: thread g owns halo row g =================
+        const int g = tid - (kMmaWarp + 1) * 32;
+        const bool has_row = g < G.rows;
+        for (int it = 0; it < my_tiles; it += kBatch) {
+            const int nt = min(kBatch, my_tiles - it);
+            RowJob jobs[kBatch];
+#pragma unroll
+            for (int u = 0; u < kBatch; ++u) {
+                jobs[u].valid = false;
+                if (u < nt) {
+                    const int tile = blockIdx.x + (it + u) * gridDim.x;
+                    uint32_t pix = 0;
+                    const bool ok = has_row && decode_virtual(tile * kTileM - G.Wp - 1 + g, G, pix);
+                    jobs[u].valid = ok;
+                    jobs[u].src = P.a.src + static_cast<size_t>(pix) * (C8 * 8);
+                    jobs[u].src2 = P.a.src2 ? P.a.src2 + static_cast<size_t>(pix) * (C8 * 8) : nullptr;
+                    jobs[u].dst = smem_u32(smem_a) + ((it + u) % kHStages) * G.stage_bytes + g * 16;
+                }
+            }
+            if (g == 0 && it < 8) DTF_MARK(16 + it);
+#pragma unroll
+            for (int u = 0; u < kBatch; ++u)
+                if (u < nt) mbar_wait(smem_u32(&hdr->empty[(it + u) % kHStages]), (((it + u) / kHStages) & 1) ^ 1, 0x34);
+            if (has_row) gather_rows<C8, kBatch>(jobs, nt, G.cs, P.a.mode, cst->p0, cst->p1, cst->p2);
+            fence_proxy_async_smem();
+#pragma unroll
+            for (int u = 0; u < kBatch; ++u)
+                if (u < nt) mbar_arrive(smem_u32(&hdr->full[(it + u) % kHStages]));
+            if (g == 0 && it < 8) DTF_MARK(24 + it);
+        }
+    } else {
+        // ================= epilogue (N == C8 * 8, compile-time) =================
+        constexpr int kGroups = C8 / 2;                    // 16-column groups
+        constexpr bool kRegStats = C8 <= 4;                // keep BN statistics in registers across tiles
+        const dtf_bf16* aux_src = epilogue_aux_ptr(P);
+        float acc1[kRegStats ? C8 * 8 : 1], acc2[kRegStats ? C8 * 8 : 1];
+#pragma unroll
+        for (int i = 0; i < (kRegStats ? C8 * 8 : 1); ++i) { acc1[i] = 0.f; acc2[i] = 0.f; }
+        // the auxiliary tensor (residual / mask source) does not depend on the MMA: fetch it one tile ahead
+        uint4 aux_nxt[C8];
+        uint32_t pix_nxt = 0;
+        bool valid_nxt = false;
+        if (my_tiles > 0) {
+            valid_nxt = decode_virtual(static_cast<int>(blockIdx.x) * kTileM + warp * 32 + lane, G, pix_nxt);
+            if (aux_src != nullptr && valid_nxt) {
+#pragma unroll
+                for (int j = 0; j < C8; ++j) aux_nxt[j] = ldg16(aux_src + static_cast<size_t>(pix_nxt) * N + j * 8);
+            }
+        }
+        for (int it = 0; it < my_tiles; ++it) {
+            const uint32_t a = it & 1;
+            const bool valid = valid_nxt;
+            const size_t obase = static_cast<size_t>(pix_nxt) * N;
+            uint4 aux[C8];
+#pragma unroll
+            for (int j = 0; j < C8; ++j) aux[j] = aux_nxt[j];
+            if (it + 1 < my_tiles) {
+                const int tile_n = blockIdx.x + (it + 1) * gridDim.x;
+                valid_nxt = decode_virtual(tile_n * kTileM + warp * 32 + lane, G, pix_nxt);
+                if (aux_src != nullptr && valid_nxt) {
+#pragma unroll
+                    for (int j = 0; j < C8; ++j) aux_nxt[j] = ldg16(aux_src + static_cast<size_t>(pix_nxt) * N + j * 8);
+                }
+            }
+            mbar_wait(smem_u32(&hdr->acc_full[a]), (it >> 1) & 1, 0x35);
+            tc_fence_after_sync();
+            if (tid == 0 && it < 8) DTF_MARK(32 + it);
+#pragma unroll
+            for (int cgi = 0; cgi < kGroups; ++cgi) {
+                float v[16];
+                tmem_ld16(tmem_base + ((warp * 32u) << 16) + a * N + cgi * 16, v);
+                epilogue_group(P, cst, v, valid, obase, cgi * 16, lane, aux_src ? &aux[2 * cgi] : nullptr,
+                               kRegStats ? &acc1[cgi * 16] : nullptr, kRegStats ? &acc2[cgi * 16] : nullptr);
+            }
+            tc_fence_before_sync();
+            mbar_arrive(smem_u32(&hdr->acc_empty[a]));
+            if (tid == 0 && it < 8) DTF_MARK(40 + it);
+        }
+        if (kRegStats && P.epi_stats_out) {
+#pragma unroll
+            for (int cgi = 0; cgi < kGroups; ++cgi) flush_stats16(cst, &acc1[cgi * 16], &acc2[cgi * 16], cgi * 16, lane);
+        }
+        if (P.epi_stats_out) {
+            named_bar_sync(1, kEpiWarps * 32);
+            for (int c = tid; c < N; c += kEpiWarps * 32) {
+                atomicAdd(P.epi_stats_out + c, cst->bins[0][c]);
+                atomicAdd(P.epi_stats_out + N + c, cst->bins[1][c]);
+            }
+        }
+    }
+    if (tid == 0) DTF_MARK(3);
+    tc_fence_before_sync();
+    __syncthreads();
+    if (tid == 0) DTF_MARK(4);
+    if (warp == kMmaWarp) {
+        tc_fence_after_sync();
+        tmem_dealloc(tmem_base, acc_cols);
+    }
+}
+
+// =========================================================================================
+// wgrad:  dw[co][tap*Cin + ci] += sum_pixels gy'[p][co] * act(x)[p + shift(tap)][ci]
+// =========================================================================================
+constexpr int kWStages = 3;
+
+template <int C8>
+__global__ void __launch_bounds__(kHThreads, 1)
+conv3x3_wgrad_kernel(const __grid_constant__ DtfConvWgrad P, const __grid_constant__ HaloGeom G) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    HaloHeader* hdr = reinterpret_cast<HaloHeader*>(smem);
+    SmemConsts* cst = reinterpret_cast<SmemConsts*>(smem + 1024);
+    uint8_t* smem_a = smem + G.smem_a_off;       // per stage: [gy: gy_c8 chunks x 128 rows][x halo: c8 chunks x rows]
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    constexpr int Cin = C8 * 8;
+    const int tap_begin = blockIdx.y == 0 ? 0 : G.ntaps;
+    const int ntaps = blockIdx.y == 0 ? G.ntaps : 9 - G.ntaps;
+    const uint32_t acc_cols = tmem_cols_pow2(ntaps * Cin);
+    const int my_tiles = (G.num_tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
+    const int gy_bytes = G.gy_c8 * kChunkBytes;
+
+    if (tid == 0) {
+        for (int i = 0; i < kWStages; ++i) {
+            mbar_init(smem_u32(&hdr->full[i]), kHGatherThreads);
+            mbar_init(smem_u32(&hdr->empty[i]), 1);
+        }
+        mbar_init(smem_u32(&hdr->acc_full[0]), 1);
+        mbar_fence_init();
+    }
+    fill_prologue(P.x, cst->p0, cst->p1, cst->p2, tid, kHThreads);
+    fill_prologue(P.gy, cst->q0, cst->q1, cst->q2, tid, kHThreads);
+    if (warp == kMmaWarp) tmem_alloc(smem_u32(&hdr->tmem_base), acc_cols);
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    const uint32_t tmem_base = hdr->tmem_base;
+
+    if (warp == kMmaWarp) {
+        if (my_tiles > 0) {          // warp-uniform loop, one elected lane issues (see conv3x3_kernel)
+            const uint32_t idesc = umma_idesc_bf16(kTileM, Cin, true, true);
+            // hoisted descriptor arithmetic (units of 16 bytes): x view shift per tap, 16 rows per K step
+            uint32_t x_off[9];
+#pragma unroll
+            for (int t = 0; t < 9; ++t) {
+                const int tap = tap_begin + t;
+                const int dy = tap / 3 - 1, dx = tap % 3 - 1;
+                x_off[t] = static_cast<uint32_t>((1 + dy) * G.Wp + (1 + dx));
+            }
+            const uint64_t gdesc0 = umma_desc(smem_u32(smem_a), 128, kChunkBytes);
+            const uint64_t xdesc0 = umma_desc(smem_u32(smem_a) + gy_bytes, 128, G.cs);
+            const uint32_t stage_units = static_cast<uint32_t>(G.stage_bytes >> 4);
+            for (int it = 0; it < my_tiles; ++it) {
+                const uint32_t st = it % kWStages;
+                mbar_wait(smem_u32(&hdr->full[st]), (it / kWStages) & 1, 0x41);
+                tc_fence_after_sync();
+                if (elect_one()) {
+#pragma unroll
+                    for (int ks = 0; ks < kTileM / 16; ++ks) {
+                        const uint64_t adesc = gdesc0 + st * stage_units + ks * 16;
+                        const uint64_t xdesc = xdesc0 + st * stage_units + ks * 16;
+#pragma unroll
+                        for (int t = 0; t < 9; ++t)
+                            if (t < ntaps) umma_bf16(tmem_base + t * Cin, adesc, xdesc + x_off[t], idesc, (it | ks) != 0);
+                    }
+                    umma_commit(smem_u32(&hdr->empty[st]));
+                }
+                __syncwarp();
+            }
+            if (elect_one()) umma_commit(smem_u32(&hdr->acc_full[0]));
+        }
+        __syncwarp();
+    } else if (warp > kMmaWarp) {
+        const int g = tid - (kMmaWarp + 1) * 32;
+        const bool has_row = g < G.rows;
+        for (int it = 0; it < my_tiles; ++it) {
+            const int tile = blockIdx.x + it * gridDim.x;
+            const uint32_t st = it % kWStages;
+            const uint32_t gy_base = smem_u32(smem_a) + st * G.stage_bytes;
+            RowJob jx, jg;
+            uint32_t pix = 0;
+            jx.valid = has_row && decode_virtual(tile * kTileM - G.Wp - 1 + g, G, pix);
+            jx.src = P.x.src + static_cast<size_t>(pix) * Cin;
+            jx.src2 = nullptr;
+            jx.dst = gy_base + gy_bytes + g * 16;
+            uint32_t pix2 = 0;
+            jg.valid = g < kTileM && decode_virtual(tile * kTileM + g, G, pix2);
+            jg.src = P.gy.src + static_cast<size_t>(pix2) * P.Cout;
+            jg.src2 = P.gy.src2 ? P.gy.src2 + static_cast<size_t>(pix2) * P.Cout : nullptr;
+            jg.dst = gy_base + g * 16;
+            mbar_wait(smem_u32(&hdr->empty[st]), ((it / kWStages) & 1) ^ 1, 0x42);
+            if (has_row) { RowJob j1[1] = {jx}; gather_rows<C8, 1>(j1, 1, G.cs, P.x.mode, cst->p0, cst->p1, cst->p2); }
+            if (g < kTileM) {
+                RowJob j1[1] = {jg};
+                if (G.gy_c8 == 2) gather_rows<2, 1>(j1, 1, kChunkBytes, P.gy.mode, cst->q0, cst->q1, cst->q2);
+                else if (G.gy_c8 == 4) gather_rows<4, 1>(j1, 1, kChunkBytes, P.gy.mode, cst->q0, cst->q1, cst->q2);
+                else gather_rows<8, 1>(j1, 1, kChunkBytes, P.gy.mode, cst->q0, cst->q1, cst->q2);
+            }
+            fence_proxy_async_smem();
+            mbar_arrive(smem_u32(&hdr->full[st]));
+        }
+    } else if (my_tiles > 0) {
+        mbar_wait(smem_u32(&hdr->acc_full[0]), 0, 0x43);
+        tc_fence_after_sync();
+        const int co = warp * 32 + lane;
+        const int ktot = 9 * Cin;
+        for (int t = 0; t < ntaps; ++t) {
+            const int kbase = (tap_begin + t) * Cin;
+            for (int cg = 0; cg < Cin; cg += 16) {
+                float v[16];
+                tmem_ld16(tmem_base + ((warp * 32u) << 16) + t * Cin + cg, v);
+                if (co < P.Cout) {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) atomicAdd(P.dw + static_cast<size_t>(co) * ktot + kbase + cg + i, v[i]);
+                }
+            }
+        }
+    }
+    tc_fence_before_sync();
+    __syncthreads();
+    if (warp == kMmaWarp) {
+        tc_fence_after_sync();
+        tmem_dealloc(tmem_base, acc_cols);
+    }
+}
+
+}  // namespace dtf
+
+// =========================================================================================
+// host side: eligibility + geometry + launch.  Called by dtf_conv_gemm / dtf_conv_wgrad.
+// =========================================================================================
+static dtf::FastDiv make_fastdiv(uint32_t d) {
+    dtf::FastDiv f;
+    f.d = d;
+    uint32_t s = 0;
+    while ((1u << s) < d) ++s;
+    f.s = s;
+    f.m = static_cast<uint32_t>(((1ull << 32) * ((1ull << s) - d)) / d + 1);
+    return f;
+}
+
+static int halo_sms() {
+    static int n = 0;
+    if (n == 0) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+        if (n <= 0) n = 148;
+    }
+    return n;
+}
+
+static bool halo_disabled() {
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("DTF_CONV_GENERIC");
+        v = (e && e[0] == '1') ? 1 : 0;
+    }
+    return v == 1;
+}
+
+static bool fill_geom(dtf::HaloGeom* G, int NB, int H, int W, int C) {
+    G->H = H; G->W = W; G->Wp = W + 1; G->Hp = H + 1;
+    G->div_wp = make_fastdiv(G->Wp);
+    G->div_hp = make_fastdiv(G->Hp);
+    const long long total = static_cast<long long>(NB) * G->Hp * G->Wp;
+    if (total >= (1ll << 30)) return false;
+    G->total = static_cast<int>(total);
+    G->num_tiles = (G->total + dtf::kTileM - 1) / dtf::kTileM;
+    G->rows = dtf::kTileM + 2 * G->Wp + 2;
+    if (G->rows > dtf::kHGatherThreads) return false;
+    G->cs = ((G->rows * 16) + 127) & ~127;
+    G->c8 = C / 8;
+    return true;
+}
+
+// returns 1 if launched, 0 if not eligible, <0 on error
+extern "C" int dtf_conv3x3_try(const DtfConvGemm* p, cudaStream_t stream) {
+    using namespace dtf;
+    const DtfGather& a = p->a;
+    if (halo_disabled()) return 0;
+    if (a.KH != 3 || a.KW != 3 || a.stride != 1 || a.pad != 1) return 0;
+    if (a.C % 16 != 0 || a.C > 64 || p->N != a.C) return 0;      // kernel is specialised for Cout == Cin
+    if (a.Hs != p->Ho || a.Ws != p->Wo) return 0;
+    HaloGeom G{};
+    if (!fill_geom(&G, p->NB, p->Ho, p->Wo, a.C)) return 0;
+    G.sign = a.transposed ? -1 : 1;
+    G.stage_bytes = (G.c8 * G.cs + 127) & ~127;
+    const int header = 1024 + static_cast<int>(sizeof(SmemConsts));
+    G.smem_b_off = (header + 1023) & ~1023;
+    G.smem_a_off = (G.smem_b_off + p->kchunks * p->N * 16 + 1023) & ~1023;
+    const int smem_bytes = G.smem_a_off + kHStages * G.stage_bytes + 256;
+    if (smem_bytes > 227 * 1024) return 0;
+    if (G.c8 != 2 && G.c8 != 4 && G.c8 != 8) return 0;
+    static int attr_set = 0;
+    if (!attr_set) {
+        if (cudaFuncSetAttribute(conv3x3_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess ||
+            cudaFuncSetAttribute(conv3x3_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess ||
+            cudaFuncSetAttribute(conv3x3_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess)
+            return DTF_ERR_CUDA;
+        attr_set = 1;
+    }
+    const int grid = G.num_tiles < halo_sms() ? G.num_tiles : halo_sms();
+    if (G.c8 == 2) conv3x3_kernel<2><<<grid, kHThreads, smem_bytes, stream>>>(*p, G);
+    else if (G.c8 == 4) conv3x3_kernel<4><<<grid, kHThreads, smem_bytes, stream>>>(*p, G);
+    else conv3x3_kernel<8><<<grid, kHThreads, smem_bytes, stream>>>(*p, G);
+    return cudaGetLastError() == cudaSuccess ? 1 : DTF_ERR_CUDA;
+}
+
+extern "C" int dtf_conv3x3_wgrad_try(const DtfConvWgrad* p, cudaStream_t stream) {
+    using namespace dtf;
+    const DtfGather& x = p->x;
+    if (halo_disabled()) return 0;
+    if (x.KH != 3 || x.KW != 3 || x.stride != 1 || x.pad != 1) return 0;
+    if (x.C % 16 != 0 || x.C > 64 || p->Cout % 8 != 0 || p->Cout > 128) return 0;
+    if (x.Hs != p->Ho || x.Ws != p->Wo) return 0;
+    HaloGeom G{};
+    if (!fill_geom(&G, p->NB, p->Ho, p->Wo, x.C)) return 0;
+    G.sign = 1;
+    G.gy_c8 = p->Cout / 8;
+    // TMEM holds ntaps * Cin fp32 columns (<= 512): split the nine taps over blockIdx.y when needed
+    const int max_taps = 512 / x.C;
+    const int ny = max_taps >= 9 ? 1 : 2;
+    G.ntaps = ny == 1 ? 9 : 5;
+    if (ny == 2 && (9 - G.ntaps) * x.C > 512) return 0;
+    G.stage_bytes = (G.gy_c8 * kChunkBytes + G.c8 * G.cs + 127) & ~127;
+    const int header = 1024 + static_cast<int>(sizeof(SmemConsts));
+    G.smem_a_off = (header + 1023) & ~1023;
+    // the gy operand descriptor spans 16 channel chunks (32 KB) from its base: keep slack at the end
+    const int smem_bytes = G.smem_a_off + kWStages * G.stage_bytes + 16 * kChunkBytes;
+    if (smem_bytes > 227 * 1024) return 0;
+    if (G.c8 != 2 && G.c8 != 4 && G.c8 != 8) return 0;
+    if (G.gy_c8 != 2 && G.gy_c8 != 4 && G.gy_c8 != 8) return 0;
+    static int attr_set = 0;
+    if (!attr_set) {
+        if (cudaFuncSetAttribute(conv3x3_wgrad_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess ||
+            cudaFuncSetAttribute(conv3x3_wgrad_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess ||
+            cudaFuncSetAttribute(conv3x3_wgrad_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess)
+            return DTF_ERR_CUDA;
+        attr_set = 1;
+    }
+    int gx = halo_sms() / ny;
+    if (gx > G.num_tiles) gx = G.num_tiles;
+    if (gx < 1) gx = 1;
+    dim3 grid(gx, ny);
+    if (G.c8 == 2) conv3x3_wgrad_kernel<2><<<grid, kHThreads, smem_bytes, stream>>>(*p, G);
+    else if (G.c8 == 4) conv3x3_wgrad_kernel<4><<<grid, kHThreads, smem_bytes, stream>>>(*p, G);
+    else conv3x3_wgrad_kernel<8><<<grid, kHThreads, smem_bytes, stream>>>(*p, G);
+    return cudaGetLastError() == cudaSuccess ? 1 : DTF_ERR_CUDA;
+}
+
+extern "C" int dtf_debug_timeline(unsigned long long* out64) {
+#ifdef DTF_TIMING
+    return cudaMemcpyFromSymbol(out64, dtf::g_timeline, 64 * sizeof(unsigned long long)) == cudaSuccess ? DTF_OK : DTF_ERR_CUDA;
+#else
+    (void)out64;
+    return DTF_ERR_ARG;
+#endif
+}

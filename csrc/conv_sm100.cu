@@ -23,188 +23,9 @@
 // The wgrad kernel reuses the same gathered tiles viewed MN-major (K = pixels): both UMMA
 // operands are transposed by descriptor, D[co][tap*Cin+ci] accumulates over all tiles of the
 // CTA in TMEM and is flushed with fp32 atomics into the gradient arena.
-#include "common.cuh"
-#include "dtf_b200.h"
+#include "conv_common.cuh"
 
 namespace dtf {
-
-constexpr int kEpiWarps = 4;
-constexpr int kGatherWarps = 8;
-constexpr int kThreads = (kEpiWarps + 1 + kGatherWarps) * 32;   // 416
-constexpr int kGatherThreads = kGatherWarps * 32;               // 256
-constexpr int kMmaWarp = kEpiWarps;
-constexpr int kTileM = 128;
-constexpr int kChunkBytes = kTileM * 16;                         // one [128 rows][8 bf16] chunk
-constexpr int kMaxC = 256;                                       // channel bound for constants
-
-struct __align__(16) SmemHeader {
-    uint64_t full[2];
-    uint64_t empty[2];
-    uint64_t acc_full[2];
-    uint64_t acc_empty[2];
-    uint64_t bfull;
-    uint32_t tmem_base;
-    uint32_t pad;
-    int8_t tap_dy[32];
-    int8_t tap_dx[32];
-};
-
-// Per-channel constant tables held in shared memory.
-struct SmemConsts {
-    float p0[kMaxC], p1[kMaxC], p2[kMaxC];        // prologue A-side
-    float q0[kMaxC], q1[kMaxC], q2[kMaxC];        // prologue second operand (wgrad gy side)
-    float e_scale[kMaxC], e_shift[kMaxC], e_mean[kMaxC], e_invstd[kMaxC];   // epilogue
-    float bins[2][kMaxC];
-};
-
-// ---- BN helper math -------------------------------------------------------------------
-// forward: y = x*scale + shift ; training statistics come as (sum, sumsq) accumulators
-DTF_DEVINL void bn_fwd_consts(const DtfBnRef& bn, int c, float& scale, float& shift, float& mean, float& invstd) {
-    float var;
-    if (bn.use_running) {
-        mean = bn.run_mean[c];
-        var = bn.run_var[c];
-    } else {
-        mean = bn.stats[c] * bn.inv_count;
-        var = fmaxf(bn.stats[bn.channels + c] * bn.inv_count - mean * mean, 0.f);
-    }
-    invstd = rsqrtf(var + bn.eps);
-    scale = bn.gamma[c] * invstd;
-    shift = bn.beta[c] - mean * scale;
-}
-
-// Fill prologue tables for one gather source.  mode 1/2: relu(x*p0+p1).  mode 3 (BN backward
-// applied on the fly): g = p0*t + p1*x + p2 with
-//   p0 = gamma*invstd, p1 = -gamma*invstd^2*mean(t*xhat), p2 = gamma*invstd*(mean*invstd*mean(t*xhat) - mean(t))
-DTF_DEVINL void fill_prologue(const DtfGather& g, float* p0, float* p1, float* p2, int tid, int nthreads) {
-    if (g.mode == DTF_PRO_NONE) return;
-    for (int c = tid; c < g.C; c += nthreads) {
-        float scale, shift, mean, invstd;
-        bn_fwd_consts(g.bn, c, scale, shift, mean, invstd);
-        if (g.mode == DTF_PRO_BN_RELU) {
-            p0[c] = scale; p1[c] = shift; p2[c] = 0.f;
-        } else {   // DTF_PRO_BN_BWD
-            const float mt = g.bwd_stats[c] * g.bn.inv_count;                 // mean(t)      (= dbeta / M)
-            const float mtx = g.bwd_stats[g.C + c] * g.bn.inv_count;          // mean(t*xhat) (= dgamma / M)
-            p0[c] = scale;
-            p1[c] = -scale * invstd * mtx;
-            p2[c] = scale * (mean * invstd * mtx - mt);
-        }
-    }
-}
-
-// Moving-average update (training): decay*old + (1-decay)*batch, unbiased variance.
-DTF_DEVINL void update_running(const DtfBnRef& bn, int tid, int nthreads) {
-    const float m = 1.f / bn.inv_count;
-    const float unbias = m > 1.f ? m / (m - 1.f) : 1.f;
-    for (int c = tid; c < bn.channels; c += nthreads) {
-        const float mean = bn.stats[c] * bn.inv_count;
-        const float var = fmaxf(bn.stats[bn.channels + c] * bn.inv_count - mean * mean, 0.f);
-        bn.run_mean[c] = bn.decay * bn.run_mean[c] + (1.f - bn.decay) * mean;
-        bn.run_var[c] = bn.decay * bn.run_var[c] + (1.f - bn.decay) * var * unbias;
-    }
-}
-
-// ---- operand gather -------------------------------------------------------------------
-struct RowCoord { int n, oy, ox; bool valid; };
-
-DTF_DEVINL RowCoord row_coord(int m, int M, int Ho, int Wo) {
-    RowCoord r;
-    r.valid = m < M;
-    const int mm = r.valid ? m : 0;
-    const int hw = Ho * Wo;
-    r.n = mm / hw;
-    const int rem = mm - r.n * hw;
-    r.oy = rem / Wo;
-    r.ox = rem - r.oy * Wo;
-    return r;
-}
-
-// Returns the 16-byte chunk (8 consecutive channels) of the im2col row for global chunk jg.
-DTF_DEVINL uint4 gather16(const DtfGather& g, const int8_t* tap_dy, const int8_t* tap_dx,
-                          const float* p0, const float* p1, const float* p2,
-                          const RowCoord& rc, int jg) {
-    const uint4 zero = make_uint4(0, 0, 0, 0);
-    if (!rc.valid || jg >= g.kchunks_real) return zero;
-    const int tap = jg >> g.cpt_shift;
-    const int c8 = jg & ((1 << g.cpt_shift) - 1);
-    int sy, sx;
-    if (!g.transposed) {
-        sy = rc.oy * g.stride + tap_dy[tap];
-        sx = rc.ox * g.stride + tap_dx[tap];
-    } else {
-        // gradient gather of a strided conv: source = (o + pad - r) / stride when divisible
-        const int ty = rc.oy - tap_dy[tap];
-        const int tx = rc.ox - tap_dx[tap];
-        if ((ty % g.stride) != 0 || (tx % g.stride) != 0 || ty < 0 || tx < 0) return zero;
-        sy = ty / g.stride;
-        sx = tx / g.stride;
-    }
-    if (sy < 0 || sy >= g.Hs || sx < 0 || sx >= g.Ws) return zero;
-    const size_t off = ((static_cast<size_t>(rc.n) * g.Hs + sy) * g.Ws + sx) * g.C + c8 * 8;
-    const uint4 raw = ldg16(g.src + off);
-    if (g.mode == DTF_PRO_NONE) return raw;
-    float f[8];
-    unpack8(raw, f);
-    const int cb = c8 * 8;
-    if (g.mode == DTF_PRO_BN_RELU) {
-#pragma unroll
-        for (int i = 0; i < 8; ++i) f[i] = fmaxf(fmaf(f[i], p0[cb + i], p1[cb + i]), 0.f);
-    } else {
-        float x[8];
-        unpack8(ldg16(g.src2 + off), x);
-#pragma unroll
-        for (int i = 0; i < 8; ++i) f[i] = fmaf(f[i], p0[cb + i], fmaf(x[i], p1[cb + i], p2[cb + i]));
-    }
-    return pack8(f);
-}
-
-DTF_DEVINL void fill_taps(SmemHeader* h, const DtfGather& g, int tid) {
-    if (tid < g.KH * g.KW && tid < 32) {
-        const int r = tid / g.KW, s = tid - r * g.KW;
-        // forward: source = o*stride + r - pad ; transposed: t = o + pad - r  => o - (r - pad)
-        h->tap_dy[tid] = static_cast<int8_t>(r - g.pad);
-        h->tap_dx[tid] = static_cast<int8_t>(s - g.pad);
-    }
-    if (tid == 31) { h->tap_dy[31] = 0; h->tap_dx[31] = 0; }   // identity tap (1x1 gathers)
-}
-
-// 16-value butterfly: on return lanes hold in v[0] the 32-lane sum of channel
-// ((lane>>4)&1)*8 + ((lane>>3)&1)*4 + ((lane>>2)&1)*2 + ((lane>>1)&1).
-DTF_DEVINL float butterfly16(float* v, int lane) {
-#pragma unroll
-    for (int i = 0; i < 8; ++i) {
-        const bool hi = lane & 16;
-        const float send = hi ? v[i] : v[i + 8];
-        const float keep = hi ? v[i + 8] : v[i];
-        v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
-    }
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        const bool hi = lane & 8;
-        const float send = hi ? v[i] : v[i + 4];
-        const float keep = hi ? v[i + 4] : v[i];
-        v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
-    }
-#pragma unroll
-    for (int i = 0; i < 2; ++i) {
-        const bool hi = lane & 4;
-        const float send = hi ? v[i] : v[i + 2];
-        const float keep = hi ? v[i + 2] : v[i];
-        v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
-    }
-    {
-        const bool hi = lane & 2;
-        const float send = hi ? v[0] : v[1];
-        const float keep = hi ? v[1] : v[0];
-        v[0] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
-    }
-    v[0] += __shfl_xor_sync(0xffffffffu, v[0], 1);
-    return v[0];
-}
-DTF_DEVINL int butterfly_channel(int lane) {
-    return ((lane >> 4) & 1) * 8 + ((lane >> 3) & 1) * 4 + ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1);
-}
 
 // =========================================================================================
 // forward / dgrad kernel:  out[M][N] = epilogue( gather(A)[M][K] * Wpacked[N][K]^T )
@@ -254,37 +75,40 @@ conv_gemm_kernel(const __grid_constant__ DtfConvGemm P) {
     const uint32_t tmem_base = hdr->tmem_base;
 
     if (warp == kMmaWarp) {
-        // ================= MMA issuer =================
-        if (lane == 0) {
-            const uint32_t wbytes = static_cast<uint32_t>(P.kchunks) * N * 16u;
+        // ================= MMA issuer (warp-uniform loop, one elected lane issues) =================
+        const uint32_t wbytes = static_cast<uint32_t>(P.kchunks) * N * 16u;
+        if (elect_one()) {
             mbar_arrive_expect_tx(smem_u32(&hdr->bfull), wbytes);
             bulk_g2s(smem_u32(smem_b), P.wpk, wbytes, smem_u32(&hdr->bfull));
-            mbar_wait(smem_u32(&hdr->bfull), 0, 1);
-            const uint32_t idesc = umma_idesc_bf16(kTileM, N, false, false);
-            uint32_t it = 0, local_tile = 0;
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local_tile) {
-                const uint32_t a = local_tile & 1;
-                mbar_wait(smem_u32(&hdr->acc_empty[a]), ((local_tile >> 1) & 1) ^ 1, 2);
+        }
+        __syncwarp();
+        mbar_wait(smem_u32(&hdr->bfull), 0, 1);
+        const uint32_t idesc = umma_idesc_bf16(kTileM, N, false, false);
+        uint32_t it = 0, local_tile = 0;
+        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local_tile) {
+            const uint32_t a = local_tile & 1;
+            mbar_wait(smem_u32(&hdr->acc_empty[a]), ((local_tile >> 1) & 1) ^ 1, 2);
+            tc_fence_after_sync();
+            const uint32_t d_tmem = tmem_base + a * N;
+            for (int kb = 0; kb < num_kb; ++kb, ++it) {
+                const uint32_t buf = it & 1;
+                mbar_wait(smem_u32(&hdr->full[buf]), (it >> 1) & 1, 3);
                 tc_fence_after_sync();
-                const uint32_t d_tmem = tmem_base + a * N;
-                for (int kb = 0; kb < num_kb; ++kb, ++it) {
-                    const uint32_t buf = it & 1;
-                    mbar_wait(smem_u32(&hdr->full[buf]), (it >> 1) & 1, 3);
-                    tc_fence_after_sync();
-                    const int nch = min(kb_chunks, P.kchunks - kb * kb_chunks);
-                    const uint32_t a_base = smem_u32(smem_a) + buf * kb_chunks * kChunkBytes;
-                    const uint32_t b_base = smem_u32(smem_b) + static_cast<uint32_t>(kb * kb_chunks) * N * 16u;
-                    for (int ks = 0; ks < nch / 2; ++ks) {
-                        const uint64_t adesc = umma_desc(a_base + ks * 2 * kChunkBytes, kChunkBytes, 128);
-                        const uint64_t bdesc = umma_desc(b_base + ks * 2 * N * 16, N * 16, 128);
-                        umma_bf16(d_tmem, adesc, bdesc, idesc, (kb | ks) != 0);
-                    }
+                const int nch = min(kb_chunks, P.kchunks - kb * kb_chunks);
+                const uint32_t a_base = smem_u32(smem_a) + buf * kb_chunks * kChunkBytes;
+                const uint32_t b_base = smem_u32(smem_b) + static_cast<uint32_t>(kb * kb_chunks) * N * 16u;
+                for (int ks = 0; ks < nch / 2; ++ks) {
+                    const uint64_t adesc = umma_desc(a_base + ks * 2 * kChunkBytes, kChunkBytes, 128);
+                    const uint64_t bdesc = umma_desc(b_base + ks * 2 * N * 16, N * 16, 128);
+                    if (elect_one()) umma_bf16(d_tmem, adesc, bdesc, idesc, (kb | ks) != 0);
+                }
+                if (elect_one()) {
                     umma_commit(smem_u32(&hdr->empty[buf]));
                     if (kb == num_kb - 1) umma_commit(smem_u32(&hdr->acc_full[a]));
                 }
+                __syncwarp();
             }
         }
-        __syncwarp();
     } else if (warp > kMmaWarp) {
         // ================= gather producers =================
         const int g = tid - (kMmaWarp + 1) * 32;
@@ -328,72 +152,7 @@ conv_gemm_kernel(const __grid_constant__ DtfConvGemm P) {
             for (int cg = 0; cg < N; cg += 16) {
                 float v[16];
                 tmem_ld16(tmem_base + ((warp * 32u) << 16) + a * N + cg, v);
-                float s2[16];
-                if (P.epi_mode == DTF_EPI_RESIDUAL) {
-                    if (valid) {
-                        float r[16];
-                        unpack8(ldg16(P.epi_res + obase + cg), r);
-                        unpack8(ldg16(P.epi_res + obase + cg + 8), r + 8);
-#pragma unroll
-                        for (int i = 0; i < 16; ++i) v[i] += r[i];
-                    }
-                } else if (P.epi_mode == DTF_EPI_BIAS_RELU || P.epi_mode == DTF_EPI_BIAS) {
-#pragma unroll
-                    for (int i = 0; i < 16; ++i) {
-                        v[i] += P.epi_bias[cg + i];
-                        if (P.epi_mode == DTF_EPI_BIAS_RELU) v[i] = fmaxf(v[i], 0.f);
-                    }
-                } else if (P.epi_mode == DTF_EPI_RELU_MASK) {
-                    float x[16];
-                    if (valid) {
-                        unpack8(ldg16(P.epi_x + obase + cg), x);
-                        unpack8(ldg16(P.epi_x + obase + cg + 8), x + 8);
-                    }
-                    float old[16];
-                    if (P.epi_accumulate && valid) {
-                        unpack8(ldg16(P.out + obase + cg), old);
-                        unpack8(ldg16(P.out + obase + cg + 8), old + 8);
-                    }
-                    float s1[16];
-#pragma unroll
-                    for (int i = 0; i < 16; ++i) {
-                        const float xv = valid ? x[i] : 0.f;
-                        const bool on = valid && fmaf(xv, cst->e_scale[cg + i], cst->e_shift[cg + i]) > 0.f;
-                        // statistics only see THIS launch's contribution; an accumulating launch adds
-                        // its own share to the same global accumulators (the sums are linear).
-                        const float t = on ? v[i] : 0.f;
-                        s1[i] = t;
-                        s2[i] = t * (xv - cst->e_mean[cg + i]) * cst->e_invstd[cg + i];
-                        v[i] = (P.epi_accumulate && valid) ? t + old[i] : t;
-                    }
-                    if (P.epi_stats_out) {
-                        const float a1 = butterfly16(s1, lane);
-                        const float a2 = butterfly16(s2, lane);
-                        if ((lane & 1) == 0) {
-                            atomicAdd(&cst->bins[0][cg + butterfly_channel(lane)], a1);
-                            atomicAdd(&cst->bins[1][cg + butterfly_channel(lane)], a2);
-                        }
-                    }
-                }
-                if (P.epi_mode != DTF_EPI_RELU_MASK && P.epi_stats_out) {
-                    float s1[16];
-#pragma unroll
-                    for (int i = 0; i < 16; ++i) {
-                        s1[i] = valid ? v[i] : 0.f;
-                        s2[i] = s1[i] * s1[i];
-                    }
-                    const float a1 = butterfly16(s1, lane);
-                    const float a2 = butterfly16(s2, lane);
-                    if ((lane & 1) == 0) {
-                        atomicAdd(&cst->bins[0][cg + butterfly_channel(lane)], a1);
-                        atomicAdd(&cst->bins[1][cg + butterfly_channel(lane)], a2);
-                    }
-                }
-                if (valid) {
-                    uint4* o = reinterpret_cast<uint4*>(P.out + obase + cg);
-                    o[0] = pack8(v);
-                    o[1] = pack8(v + 8);
-                }
+                epilogue_group(P, cst, v, valid, obase, cg, lane);
             }
             tc_fence_before_sync();
             mbar_arrive(smem_u32(&hdr->acc_empty[a]));
@@ -456,7 +215,7 @@ conv_wgrad_kernel(const __grid_constant__ DtfConvWgrad P) {
     const bool has_work = blockIdx.x < num_tiles;
 
     if (warp == kMmaWarp) {
-        if (lane == 0 && has_work) {
+        if (has_work) {
             // A = gy' viewed MN-major (M index = channel, 8 per 16-byte row), B = im2col MN-major.
             const uint32_t idesc = umma_idesc_bf16(kTileM, ncols, true, true);
             uint32_t it = 0;
@@ -470,11 +229,12 @@ conv_wgrad_kernel(const __grid_constant__ DtfConvWgrad P) {
                     // K step = 16 pixels = 2 groups of 8 rows (LBO = 128); channel chunks SBO apart
                     const uint64_t adesc = umma_desc(a_base + ks * 256, 128, kChunkBytes);
                     const uint64_t bdesc = umma_desc(b_base + ks * 256, 128, kChunkBytes);
-                    umma_bf16(tmem_base, adesc, bdesc, idesc, (it | ks) != 0);
+                    if (elect_one()) umma_bf16(tmem_base, adesc, bdesc, idesc, (it | ks) != 0);
                 }
-                umma_commit(smem_u32(&hdr->empty[buf]));
+                if (elect_one()) umma_commit(smem_u32(&hdr->empty[buf]));
+                __syncwarp();
             }
-            umma_commit(smem_u32(&hdr->acc_full[0]));
+            if (elect_one()) umma_commit(smem_u32(&hdr->acc_full[0]));
         }
         __syncwarp();
     } else if (warp > kMmaWarp) {
@@ -564,12 +324,18 @@ static int prep_gather(DtfGather* g) {
     return DTF_OK;
 }
 
+extern "C" int dtf_conv3x3_try(const DtfConvGemm* p, cudaStream_t stream);
+extern "C" int dtf_conv3x3_wgrad_try(const DtfConvWgrad* p, cudaStream_t stream);
+
 extern "C" int dtf_conv_gemm(DtfConvGemm* p, cudaStream_t stream) {
     using namespace dtf;
     int rc = prep_gather(&p->a);
     if (rc != DTF_OK) return rc;
     if (p->N % 16 != 0 || p->N < 16 || p->N > 256) return DTF_ERR_SHAPE;
     p->kchunks = (p->a.kchunks_real + 1) & ~1;
+    // 3x3 / stride 1: halo-tile kernel with shifted descriptor views (conv3x3_sm100.cu)
+    rc = dtf_conv3x3_try(p, stream);
+    if (rc != 0) return rc > 0 ? DTF_OK : rc;
     // operand buffer: as many chunks as fit next to the weights, even, <= kchunks
     const int header = 1024 + static_cast<int>(sizeof(SmemConsts));
     const int b_off = (header + 1023) & ~1023;
@@ -609,6 +375,8 @@ extern "C" int dtf_conv_wgrad(DtfConvWgrad* p, cudaStream_t stream) {
     if (p->Cout % 8 != 0 || p->Cout > 128) return DTF_ERR_SHAPE;
     p->kchunks_real = p->x.kchunks_real;
     p->kchunks = (p->kchunks_real + 1) & ~1;
+    rc = dtf_conv3x3_wgrad_try(p, stream);
+    if (rc != 0) return rc > 0 ? DTF_OK : rc;
     // columns per CTA: <= 24 chunks (192 columns), even, N % 16 == 0 holds for even chunk counts
     int per = p->kchunks;
     int ny = 1;
