@@ -136,15 +136,18 @@ __global__ void __launch_bounds__(256)
 allreduce_update_kernel(const __grid_constant__ DtfAllreduceUpdate P) {
     __shared__ DtfHparams hp;
     const int W = P.world;
+    // The epoch of this exchange is the device-resident step counter (bumped by dtf_dp_step_begin), so a
+    // captured CUDA graph of the step replays with the right epoch; P.epoch is only an offset.
+    const long long step = *P.step;
+    const unsigned long long epoch = static_cast<unsigned long long>(step) + P.epoch;
     // ---- entry barrier: tell every peer that my gradients for `epoch` are complete, then wait for theirs
     if (blockIdx.x == 0 && threadIdx.x < W) {
         __threadfence_system();
-        st_release_sys(P.peer_ready[threadIdx.x] + P.rank, P.epoch);     // my slot in peer's ready[]
+        st_release_sys(P.peer_ready[threadIdx.x] + P.rank, epoch);     // my slot in peer's ready[]
     }
     if (threadIdx.x == 0) hp = *P.hp;
-    if (threadIdx.x < W) wait_flag_ge(P.local_ready + threadIdx.x, P.epoch, 1);
+    if (threadIdx.x < W) wait_flag_ge(P.local_ready + threadIdx.x, epoch, 1);
     __syncthreads();
-    const long long step = *P.step;
     const float lr = schedule_lr2(hp, step - 1);
     float lr_adam = lr;
     if (hp.optimizer == DTF_OPT_ADAM) {
@@ -204,23 +207,36 @@ allreduce_update_kernel(const __grid_constant__ DtfAllreduceUpdate P) {
         if (prev == gridDim.x - 1) {
             *P.arrive_counter = 0;
             __threadfence_system();
-            for (int w = 0; w < W; ++w) st_release_sys(P.peer_done[w] + P.rank, P.epoch);
+            for (int w = 0; w < W; ++w) st_release_sys(P.peer_done[w] + P.rank, epoch);
         }
     }
 }
 
 // step begin for a DP member: wait until every peer has finished reading my gradients of the
 // previous step, then zero the accumulators and bump the step counter
+// (single CTA grid-stride would be slow; instead every CTA waits, and the LAST CTA to finish bumps the
+// counter so that no CTA can observe the bumped value while computing its wait target)
 __global__ void __launch_bounds__(256)
 dp_step_begin_kernel(float4* __restrict__ zero, long long n_vec, long long* __restrict__ step_ptr,
-                     const unsigned long long* __restrict__ local_done, int world, unsigned long long prev_epoch) {
+                     const unsigned long long* __restrict__ local_done, int world, unsigned long long epoch_offset,
+                     unsigned int* __restrict__ arrive_counter) {
+    // peers must have consumed the gradients of the previous step (= current counter value)
+    const unsigned long long prev_epoch = static_cast<unsigned long long>(*step_ptr) + epoch_offset;
     if (threadIdx.x < world) wait_flag_ge(local_done + threadIdx.x, prev_epoch, 2);
     __syncthreads();
     const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n_vec;
          i += (long long)gridDim.x * blockDim.x)
         zero[i] = z;
-    if (blockIdx.x == 0 && threadIdx.x == 0) *step_ptr += 1;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        const unsigned int prev = atomicAdd(arrive_counter, 1u);
+        if (prev == gridDim.x - 1) {
+            *arrive_counter = 0;
+            *step_ptr += 1;
+        }
+    }
 }
 
 }  // namespace dtf
@@ -263,15 +279,15 @@ extern "C" int dtf_allreduce_update(const DtfAllreduceUpdate* p, cudaStream_t st
 }
 
 extern "C" int dtf_dp_step_begin(float* zero_base, long long zero_floats, long long* step,
-                                 const unsigned long long* local_done, int world, unsigned long long prev_epoch,
-                                 cudaStream_t stream) {
+                                 const unsigned long long* local_done, int world, unsigned long long epoch_offset,
+                                 unsigned int* arrive_counter, cudaStream_t stream) {
     if (zero_floats % 4 != 0 || ((uintptr_t)zero_base & 15) != 0) return DTF_ERR_ARG;
     const long long n_vec = zero_floats / 4;
     long long blocks = (n_vec + 255) / 256;
     if (blocks > 148 * 4) blocks = 148 * 4;
     if (blocks < 1) blocks = 1;
     dtf::dp_step_begin_kernel<<<static_cast<int>(blocks), 256, 0, stream>>>(
-        reinterpret_cast<float4*>(zero_base), n_vec, step, local_done, world, prev_epoch);
+        reinterpret_cast<float4*>(zero_base), n_vec, step, local_done, world, epoch_offset, arrive_counter);
     return DTF_CHECK_LAUNCH();
 }
 

@@ -84,7 +84,7 @@ class NativeResNetEngine:
 
     def __init__(self, cfg: resnet.ResNetConfig, hparams: Dict[str, Any], device, *, seed: int = 0,
                  dtype: str = "bf16", max_batch: int = MAX_BATCH, use_graphs: bool = True,
-                 arena_alloc=None):
+                 arena_alloc=None, dp_group=None):
         if cfg.resnet_version != 2 or cfg.bottleneck or cfg.first_pool_size:
             raise NotImplementedError("native engine covers the CIFAR configuration: ResNet v2, building blocks")
         if dtype != "bf16":
@@ -96,6 +96,8 @@ class NativeResNetEngine:
         self.use_graphs = use_graphs
         self.hp: Dict[str, Any] = {}
         self._graphs: Dict[Tuple[str, int], torch.cuda.CUDAGraph] = {}
+        self.dp_group = dp_group          # torch.distributed group of this member's replicas (None = 1 GPU)
+        self.dp = None
         self._build_plan()
         self._alloc(arena_alloc)
         self._init_params(hparams.get("initializer", "None"), seed)
@@ -213,7 +215,13 @@ class NativeResNetEngine:
         self.pack = torch.zeros(self.n_pack, dtype=torch.bfloat16, device=dev)
         # per-step zeroed region: grads | batch statistics | loss, correct
         zfloats = P + _align(self.n_stats * 4) // 4 + 64
-        self.zero_region = torch.zeros(zfloats, dtype=torch.float32, device=dev)
+        if self.dp_group is not None:
+            # data-parallel member: the gradient arena must be addressable by the peer replicas
+            from ..parallel.dp import DataParallelGroup
+            self.dp = DataParallelGroup(zfloats * 4, dev, group=self.dp_group)
+            self.zero_region = self.dp.alloc_grads(zfloats * 4).view(torch.float32)
+        else:
+            self.zero_region = torch.zeros(zfloats, dtype=torch.float32, device=dev)
         self.grads = self.zero_region[:P]
         s0 = P
         self.stats = self.zero_region[s0: s0 + self.n_stats]
@@ -459,13 +467,20 @@ class NativeResNetEngine:
 
     def _train_kernels(self, nb: int, pp_mode: int) -> None:
         self._count = 0
-        native.step_begin(self.zero_region, self.step_dev, bump=True)
+        if self.dp is not None:
+            self.dp.step_begin(self.zero_region, self.step_dev)
+        else:
+            native.step_begin(self.zero_region, self.step_dev, bump=True)
         native.preprocess(self.in_u8, None, self.image, mode=pp_mode, seed=self._seed, counter=self._pp_counter, n=nb)
         self._count += 2
         x_last = self._forward(nb, True)
         self._backward(x_last, nb)
-        native.optimizer_step(self.params, self.grads, self.slot0, self.slot1, self.pack, self.segs_dev,
-                              self.chunks_dev, self.n_chunks, self.hp_dev, self.step_dev, 1.0)
+        if self.dp is not None:
+            self.dp.allreduce_update(self.params, self.slot0, self.slot1, self.pack, self.segs_dev,
+                                     self.chunks_dev, self.n_chunks, self.hp_dev, self.step_dev)
+        else:
+            native.optimizer_step(self.params, self.grads, self.slot0, self.slot1, self.pack, self.segs_dev,
+                                  self.chunks_dev, self.n_chunks, self.hp_dev, self.step_dev, 1.0)
         self._count += 1
         self.launches_per_step = self._count
 

@@ -46,7 +46,7 @@ class ScoreBoard:
         deadline = time.time() + timeout
         while True:
             with torch.cuda.stream(self._stream):
-                self._host.copy_(self.buf.tensor, non_blocking=True)
+                self._host.copy_(self.buf.tensor[: self._host.numel()], non_blocking=True)
             self._stream.synchronize()
             scores = self._host.view(torch.float32).view(-1, 4)[:, 0]
             epochs = self._host.view(torch.int64).view(-1, 2)[:, 1]

@@ -196,14 +196,16 @@ typedef struct {
     const DtfOptSegment* segs; const int* chunks;
     const DtfHparams* hp; const long long* step;
     unsigned int* arrive_counter;
-    unsigned long long epoch;
+    unsigned long long epoch;                        /* offset added to *step to form the exchange epoch */
     float grad_scale;
     int world, rank, n_chunks;
 } DtfAllreduceUpdate;
 int dtf_allreduce_update(const DtfAllreduceUpdate* p, cudaStream_t stream);
+/* Step begin of a data-parallel member: waits until every peer has consumed this replica's gradients
+ * of the previous step (done[w] >= *step + epoch_offset), zeroes the accumulators, bumps *step. */
 int dtf_dp_step_begin(float* zero_base, long long zero_floats, long long* step,
-                      const unsigned long long* local_done, int world, unsigned long long prev_epoch,
-                      cudaStream_t stream);
+                      const unsigned long long* local_done, int world, unsigned long long epoch_offset,
+                      unsigned int* arrive_counter, cudaStream_t stream);
 
 /* Symmetric-memory plumbing.  These allocate / map device memory (cudaMalloc, CUDA IPC). */
 int dtf_symm_alloc(long long bytes, void** out);

@@ -1,0 +1,248 @@
+"""Exploit copy, score board, fused all-reduce+update: single-GPU semantics and 2-GPU peer paths."""
+import ctypes as C
+import os
+import socket
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def nat():
+    from distributedtf_b200.ops import native
+    native.require()
+    return native
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _hp_struct(nat, lr=0.25, opt=1):
+    h = nat.Hparams()
+    h.optimizer, h.regularizer, h.momentum, h.grad_decay = opt, 2, 0.9, 0.8
+    h.weight_decay, h.inv_loss_scale, h.n_boundaries, h.batch_size = 1e-3, 1.0, 1, 96
+    h.boundaries[0] = 1000
+    h.lr_values[0], h.lr_values[1] = lr, lr / 2
+    return h
+
+
+def test_exploit_copy_local(nat):
+    """state copy + hyper-parameter block rewrite + round-cell reset + completion epoch, one launch."""
+    from distributedtf_b200.parallel import exploit
+    nbytes = 3 * 1024 * 1024 + 256
+    src = torch.randint(0, 255, (nbytes,), dtype=torch.uint8, device="cuda")
+    dst = torch.zeros_like(src)
+    hp_off = 512
+    hp = _hp_struct(nat, lr=0.125)
+    cells = torch.ones(64, dtype=torch.float32, device="cuda")
+    ctrl = torch.zeros(32, dtype=torch.int64, device="cuda")
+    exploit.copy_kernel(dst.data_ptr(), src.data_ptr(), nbytes, hp_offset=hp_off, new_hp=hp, zero=cells,
+                        done_flag_ptr=ctrl.data_ptr(), epoch=7, arrive_ptr=ctrl.data_ptr() + 8)
+    torch.cuda.synchronize()
+    n_hp = C.sizeof(nat.Hparams)
+    assert torch.equal(dst[:hp_off], src[:hp_off]) and torch.equal(dst[hp_off + n_hp:], src[hp_off + n_hp:])
+    want = torch.frombuffer(bytearray(bytes(memoryview(hp).cast("B"))), dtype=torch.uint8).cuda()
+    assert torch.equal(dst[hp_off: hp_off + n_hp], want)
+    assert torch.all(cells == 0)
+    assert ctrl[0].item() == 7 and (ctrl[1].item() & 0xFFFFFFFF) == 0
+    # plain copy (publish) leaves everything identical
+    exploit.copy_kernel(dst.data_ptr(), src.data_ptr(), nbytes)
+    torch.cuda.synchronize()
+    assert torch.equal(dst, src)
+    with pytest.raises(nat.NativeError):
+        exploit.copy_kernel(dst.data_ptr(), src.data_ptr(), nbytes - 3)
+
+
+def test_scoreboard_local(nat):
+    from distributedtf_b200.parallel import scoreboard
+    board = scoreboard.ScoreBoard(8, torch.device("cuda", 0))
+    for member, hits in [(0, 10), (3, 73), (5, 100)]:
+        cell = torch.tensor([hits], dtype=torch.int32, device="cuda")
+        scoreboard.publish(board.ptr, member, cell, 100, epoch=4)
+        torch.cuda.synchronize()
+        assert cell.item() == 0                      # counter reset for the next round
+    got = board.read(4, members=[0, 3, 5], timeout=5)
+    assert got == {0: pytest.approx(0.10), 3: pytest.approx(0.73), 5: pytest.approx(1.0)}
+    with pytest.raises(TimeoutError):
+        board.read(5, members=[0], timeout=0.2)
+
+
+def test_member_exploit_p2p_same_process(nat, tmp_path):
+    """Two native CIFAR members in one process: SET + EXPLORE => loser == winner's snapshot, bit-identical
+    (weights, slots, moving statistics, step), with the loser's explored hyper-parameters on the device."""
+    from distributedtf_b200.hpspace import default_cifar_hparam
+    from distributedtf_b200.models.cifar10 import Cifar10Model
+    base = str(tmp_path / "model_")
+    kw = dict(engine="native", resnet_size=8, max_train_steps=3, eval_batches=1)
+    hp_w = default_cifar_hparam(); hp_w["batch_size"] = 72
+    hp_l = default_cifar_hparam(); hp_l["batch_size"] = 80; hp_l["opt_case"] = {"optimizer": "Adam", "lr": 1e-3}
+    winner, loser = Cifar10Model(0, hp_w, base, **kw), Cifar10Model(1, hp_l, base, **kw)
+    winner.train(1, 1); loser.train(1, 1)
+    assert winner.engine.step == 3 and loser.engine.step == 3
+    snap = winner.engine.state.clone()
+    winner.train(1, 1)                                  # winner already trains the next round ...
+    import copy
+    loser.set_values([1, winner.accuracy, copy.deepcopy(hp_w),
+                      {"path": "p2p", "src_id": 0, "src_rank": 1, "round": 0, "explore_follows": True}])
+    loser.need_explore = True
+    loser.seed(3)
+    loser.perturb_hparams()                             # ... while the loser pulls round 0's snapshot
+    torch.cuda.synchronize()
+    eng = loser.engine
+    off, n_hp = eng.hp_state_offset, C.sizeof(nat.Hparams)
+    assert torch.equal(eng.state[:off], snap[:off]) and torch.equal(eng.state[off + n_hp:], snap[off + n_hp:])
+    assert eng.step == 3 and winner.engine.step == 6
+    assert loser.hparams["opt_case"]["optimizer"] == "Momentum"          # adopted winner's optimizer type
+    assert loser.hparams["opt_case"]["lr"] != hp_w["opt_case"]["lr"]      # ... and explored around its values
+    dev_hp = nat.Hparams.from_buffer_copy(bytes(eng.hp_dev.cpu().numpy()))
+    assert dev_hp.optimizer == 1 and dev_hp.batch_size == loser.hparams["batch_size"]
+    want = eng.hparams_struct(loser.hparams)
+    assert abs(dev_hp.lr_values[0] - want.lr_values[0]) < 1e-9 and abs(dev_hp.momentum - want.momentum) < 1e-9
+    # packed weights were refreshed from the adopted parameters: training continues finite
+    loser.train(1, 1)
+    assert eng.step == 6 and loser.accuracy == loser.accuracy
+
+
+# --------------------------------------------------------------------------- 2 GPUs
+def _two_rank(rank, world, port, fn_name, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
+                      LOCAL_RANK=str(rank))
+    import torch.distributed as dist
+    torch.cuda.set_device(rank)
+    dist.init_process_group("cpu:gloo,cuda:nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        out = globals()[fn_name](rank, world)
+        q.put((rank, "ok", out))
+    except Exception as e:  # surfaced in the parent
+        import traceback
+        q.put((rank, "error", traceback.format_exc()))
+    finally:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def _run2(fn_name):
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_two_rank, args=(r, 2, port, fn_name, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=240) for _ in procs]
+    for p in procs:
+        p.join(60)
+    for rank, status, out in res:
+        assert status == "ok", f"rank {rank}:\n{out}"
+    return {rank: out for rank, _, out in res}
+
+
+def _peer_exploit_and_board(rank, world):
+    import torch.distributed as dist
+    from distributedtf_b200.ops import native as nat
+    from distributedtf_b200.parallel import exploit, scoreboard, symm
+    dev = torch.device("cuda", rank)
+    nbytes = 8 * 1024 * 1024
+    mb = exploit.MemberBuffer(nbytes, dev)
+    state = mb.alloc_state(nbytes)
+    g = torch.Generator(device=dev).manual_seed(100 + rank)
+    state.copy_(torch.randint(0, 255, (nbytes,), dtype=torch.uint8, device=dev, generator=g))
+    symm.DIRECTORY.register_local(rank, mb.buf, rank)
+    board = scoreboard.ScoreBoard(4, dev) if rank == 0 else None
+    handles = [None, None]
+    dist.all_gather_object(handles, board.handle() if rank == 0 else None)
+    symm.exchange_directory({rank: mb.buf})
+    exploit.copy_kernel(mb.state_ptr + mb.snapshot_offset(0), mb.state_ptr, mb.state_bytes)     # publish
+    torch.cuda.synchronize()
+    dist.barrier()
+    out = {}
+    if rank == 1:
+        src = symm.DIRECTORY.pointer(0) + mb.snapshot_offset(0)
+        hp = nat.Hparams(); hp.optimizer = 4; hp.batch_size = 77
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        exploit.copy_kernel(mb.state_ptr, src, mb.state_bytes, hp_offset=0, new_hp=hp,
+                            done_flag_ptr=mb.control_ptr, epoch=1, arrive_ptr=mb.control_ptr + 8)
+        e1.record()
+        torch.cuda.synchronize()
+        out["ms"] = e0.elapsed_time(e1)
+        out["state"] = state.cpu()
+        out["flag"] = int(mb.control_tensor().view(torch.int64)[0].item())
+        # score board lives on rank 0; publish through the peer mapping
+        bptr = C.c_void_p()
+        nat.check(nat.lib().dtf_ipc_open_handle(handles[0], C.byref(bptr)), "open board")
+        cell = torch.tensor([41], dtype=torch.int32, device=dev)
+        scoreboard.publish(int(bptr.value), 2, cell, 50, epoch=9)
+        torch.cuda.synchronize()
+    else:
+        out["state"] = state.cpu()
+    dist.barrier()
+    if rank == 0:
+        out["scores"] = board.read(9, members=[2], timeout=10)
+    return out
+
+
+@pytest.mark.multigpu
+def test_peer_exploit_and_scoreboard_two_gpus(nat):
+    res = _run2("_peer_exploit_and_board")
+    n_hp = C.sizeof(nat.Hparams)
+    assert torch.equal(res[1]["state"][n_hp:], res[0]["state"][n_hp:])         # bit-exact over NVLink
+    got_hp = nat.Hparams.from_buffer_copy(bytes(res[1]["state"][:n_hp].numpy()))
+    assert got_hp.optimizer == 4 and got_hp.batch_size == 77
+    assert res[1]["flag"] == 1
+    assert res[0]["scores"] == {2: pytest.approx(0.82)}
+    print(f"8 MiB peer pull: {res[1]['ms']*1000:.1f} us")
+
+
+def _dp_step(rank, world):
+    """DP-2 member: two replicas, each half of the batch.  Step 1 (eager launches) is checked against
+    the TF-1.x Momentum rule applied to the MEAN of the two replicas' gradients; steps 2-4 replay the
+    captured CUDA graph and must keep the replicas bit-identical."""
+    import torch.distributed as dist
+    from distributedtf_b200.models import resnet
+    from distributedtf_b200.models.resnet_native import NativeResNetEngine
+    dev = torch.device("cuda", rank)
+    cfg = resnet.cifar10_config(8)
+    hp = {"opt_case": {"optimizer": "Momentum", "lr": 0.1, "momentum": 0.9}, "decay_steps": 20, "decay_rate": 0.1,
+          "weight_decay": 2e-4, "regularizer": "l2_regularizer", "initializer": "he_init", "batch_size": 64}
+    eng = NativeResNetEngine(cfg, hp, dev, seed=5, use_graphs=True, dp_group=dist.group.WORLD)
+    start = eng.params[: eng.n_params].clone()
+    g = torch.Generator().manual_seed(1)
+    imgs = torch.randint(0, 256, (64, 32, 32, 3), dtype=torch.uint8, generator=g)
+    labels = torch.randint(0, 10, (64,), generator=g)
+    lo, hi = rank * 32, rank * 32 + 32
+    losses = [eng.train_step_u8(imgs[lo:hi].to(dev), labels[lo:hi].to(dev), augment=False).clone()]
+    torch.cuda.synchronize()
+    dist.barrier()
+    mine = eng.grads[: eng.n_params].clone()
+    both = [torch.zeros_like(mine) for _ in range(world)]
+    dist.all_gather(both, mine)
+    gmean = (both[0] + both[1]) / 2
+    reg = torch.zeros_like(start)
+    reg[: eng.n_conv_params] = 2e-4 * start[: eng.n_conv_params]
+    want = start - 0.1 * 64 / 128 * (gmean + reg)          # first Momentum step: accumulator = gradient
+    err = (eng.params[: eng.n_params] - want).abs().max().item()
+    for _ in range(3):
+        losses.append(eng.train_step_u8(imgs[lo:hi].to(dev), labels[lo:hi].to(dev), augment=False).clone())
+    torch.cuda.synchronize()
+    return {"params": eng.params[: eng.n_params].cpu(), "step": eng.step, "loss": [l.item() for l in losses],
+            "err": err, "grads_differ": not torch.equal(both[0], both[1]), "ref_start": start.cpu()}
+
+
+@pytest.mark.multigpu
+def test_dp2_allreduce_update_two_gpus(nat):
+    res = _run2("_dp_step")
+    assert res[0]["step"] == 4 and res[1]["step"] == 4
+    # replicas stay bit-identical: every rank sums the same values in the same order
+    assert torch.equal(res[0]["params"], res[1]["params"])
+    assert not torch.equal(res[0]["params"], res[0]["ref_start"])
+    assert all(l == l for l in res[0]["loss"])
+    assert res[0]["grads_differ"]                      # the replicas really saw different shards
+    assert res[0]["err"] < 1e-6 and res[1]["err"] < 1e-6, (res[0]["err"], res[1]["err"])
