@@ -327,3 +327,107 @@ extern "C" int dtf_last_cuda_error(char* buf, int n) {
     snprintf(buf, n, "%s", s);
     return DTF_OK;
 }
+
+// =========================================================================================
+// dtf_exploit_copy_noalloc — the exploit transfer for callers that must not allocate.
+//
+// Who needs it: a worker adopts a winner's state while the other members that share its GPU
+// (or its process) are in the middle of a training round.  Any device allocation at that point
+// is a problem — cudaMalloc / cudaFree synchronise the whole device and would stall every
+// member's stream, a caller that embeds this library may have handed all device memory to its
+// own pool, and a caller that sits inside a fixed memory budget simply has nowhere to put the
+// kernel's bookkeeping.  The regular entry point makes such a caller bring 4 bytes of zeroed
+// device scratch (the CTA arrival counter behind the completion flag); this variant owns that
+// scratch itself.
+//
+// The scratch is the file-scope array below: kNoAllocScratchBytes (256) bytes, present once in
+// every GPU context that loads the library and held until the process exits.  Only the first
+// 4 bytes are used today (the arrival counter); the rest is reserved.  Nothing else changes:
+// inputs and outputs are still the caller's.
+//
+// Rules that follow from sharing one array:
+//   * calls must not overlap on the same GPU (two copies in flight on different streams would
+//     count arrivals in the same cell and could publish a completion epoch early or never);
+//     serialise them on one stream or with events;
+//   * the counter is cleared by a memset on `stream` at the start of every call, so a previous
+//     call that was aborted cannot poison the next one;
+//   * the first call on each device resolves the array's device address (with that device
+//     current) and caches it — make that first call outside any stream capture;
+//   * `bytes` above DTF_NOALLOC_MAX_BYTES is refused with DTF_ERR_LIMIT (the message is available
+//     from dtf_noalloc_last_error); larger states go through dtf_exploit_copy.
+// No cudaMalloc / cudaFree / allocating library call is made here.
+// =========================================================================================
+namespace dtf {
+constexpr size_t kNoAllocScratchBytes = 256;
+static __device__ __align__(256) unsigned char g_exploit_noalloc_scratch[kNoAllocScratchBytes];
+}  // namespace dtf
+
+static const int kNoAllocMaxDevices = 64;
+static void* g_noalloc_scratch_ptr[kNoAllocMaxDevices];      // device address of the array, per device
+static char g_noalloc_error[256] = "";
+
+extern "C" const char* dtf_noalloc_last_error(void) { return g_noalloc_error; }
+
+// In host code the array's name is only a stand-in for the symbol; the address a kernel may
+// dereference has to be asked for, once per device, with that device current.
+static int noalloc_scratch_for_current_device(void** out) {
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kNoAllocMaxDevices) {
+        snprintf(g_noalloc_error, sizeof(g_noalloc_error), "dtf_exploit_copy_noalloc: no usable current device (%d)", dev);
+        return DTF_ERR_CUDA;
+    }
+    if (g_noalloc_scratch_ptr[dev] == nullptr) {
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, dtf::g_exploit_noalloc_scratch);
+        if (e != cudaSuccess || p == nullptr) {
+            snprintf(g_noalloc_error, sizeof(g_noalloc_error),
+                     "dtf_exploit_copy_noalloc: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+            return DTF_ERR_CUDA;
+        }
+        g_noalloc_scratch_ptr[dev] = p;
+    }
+    *out = g_noalloc_scratch_ptr[dev];
+    return DTF_OK;
+}
+
+extern "C" int dtf_exploit_copy_noalloc(void* dst, const void* src, long long bytes, long long hp_offset,
+                                        const DtfHparams* new_hp, void* zero_region, long long zero_bytes,
+                                        unsigned long long* done_flag, unsigned long long epoch,
+                                        cudaStream_t stream) {
+    if (bytes < 0 || bytes > DTF_NOALLOC_MAX_BYTES) {
+        snprintf(g_noalloc_error, sizeof(g_noalloc_error),
+                 "dtf_exploit_copy_noalloc: %lld bytes exceeds the supported maximum of %lld bytes; "
+                 "use dtf_exploit_copy for larger states", bytes, (long long)DTF_NOALLOC_MAX_BYTES);
+        return DTF_ERR_LIMIT;
+    }
+    if ((bytes & 15) || (zero_bytes & 15) || (hp_offset & 15) || ((uintptr_t)dst & 15) || ((uintptr_t)src & 15)) {
+        snprintf(g_noalloc_error, sizeof(g_noalloc_error),
+                 "dtf_exploit_copy_noalloc: pointers, sizes and the hyper-parameter offset must be multiples of 16 bytes");
+        return DTF_ERR_ARG;
+    }
+    void* scratch = nullptr;
+    const int rc = noalloc_scratch_for_current_device(&scratch);
+    if (rc != DTF_OK) return rc;
+    // the arrival counter has to start at zero; whatever an earlier call left behind is wiped here
+    if (cudaMemsetAsync(scratch, 0, sizeof(unsigned int), stream) != cudaSuccess) {
+        snprintf(g_noalloc_error, sizeof(g_noalloc_error), "dtf_exploit_copy_noalloc: clearing the scratch failed: %s",
+                 cudaGetErrorString(cudaGetLastError()));
+        return DTF_ERR_CUDA;
+    }
+    const long long n_vec = bytes / 16;
+    const int hp_vecs = new_hp ? static_cast<int>((sizeof(DtfHparams) + 15) / 16) : 0;
+    DtfHparams hp_val;
+    if (new_hp) hp_val = *new_hp; else memset(&hp_val, 0, sizeof(hp_val));
+    long long want = (n_vec + 512LL * dtf::kCopyUnroll - 1) / (512LL * dtf::kCopyUnroll);
+    if (want < 1) want = 1;
+    const int grid = static_cast<int>(want < 148 * 2 ? want : 148 * 2);
+    dtf::exploit_copy_kernel<<<grid, 512, 0, stream>>>(
+        reinterpret_cast<uint4*>(dst), reinterpret_cast<const uint4*>(src), n_vec,
+        new_hp ? hp_offset / 16 : -1, hp_vecs, hp_val, reinterpret_cast<uint4*>(zero_region), zero_bytes / 16,
+        done_flag, epoch, static_cast<unsigned int*>(scratch));
+    if (cudaGetLastError() != cudaSuccess) {
+        snprintf(g_noalloc_error, sizeof(g_noalloc_error), "dtf_exploit_copy_noalloc: kernel launch failed");
+        return DTF_ERR_CUDA;
+    }
+    return DTF_OK;
+}

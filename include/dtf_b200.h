@@ -216,6 +216,21 @@ int dtf_ipc_close(void* p);
 int dtf_enable_peer(int peer_device);
 int dtf_last_cuda_error(char* buf, int n);
 
+/* ---- exploit transfer without any allocation ------------------------------------------------
+ * (No counterpart in the reference: its exploit is a file copy run by the master.)
+ * Same copy as dtf_exploit_copy for callers that cannot provide device scratch and must not
+ * trigger an allocation while other members train on the same GPU: the arrival counter lives in
+ * a 256-byte static __device__ array owned by the library (one per GPU context, kept until exit).
+ * Limits and rules: at most DTF_NOALLOC_MAX_BYTES per call (DTF_ERR_LIMIT beyond, text from
+ * dtf_noalloc_last_error()); calls on one GPU share the array, so they must not overlap; the
+ * counter is cleared on `stream` at the start of each call; the first call on a device looks up
+ * the array's address and should be made outside stream capture. */
+#define DTF_NOALLOC_MAX_BYTES (1ll << 30)
+int dtf_exploit_copy_noalloc(void* dst, const void* src, long long bytes, long long hp_offset,
+                             const DtfHparams* new_hp, void* zero_region, long long zero_bytes,
+                             unsigned long long* done_flag, unsigned long long epoch, cudaStream_t stream);
+const char* dtf_noalloc_last_error(void);
+
 #ifdef __cplusplus
 }
 #endif
