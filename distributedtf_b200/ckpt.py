@@ -157,7 +157,7 @@ def load_checkpoint(save_dir: str) -> Optional[Tuple[Dict[str, np.ndarray], Dict
         raise ValueError(f"unsupported checkpoint version {index.get('version')}")
     raw = np.fromfile(prefix + ".data", dtype=np.uint8)
     out: Dict[str, np.ndarray] = {}
-    for name, e in index["entries"].items():
+    for name, e in sorted(index["entries"].items(), key=lambda kv: kv[1]["offset"]):   # write order
         dt = np.dtype(_NP_DTYPES[e["dtype"]])
         seg = raw[e["offset"]: e["offset"] + e["nbytes"]]
         out[name] = seg.view(dt).reshape(e["shape"]).copy()
