@@ -123,15 +123,40 @@ def run_local(cfg: RunConfig) -> Dict[str, Any]:
     return result
 
 
-def _tcp_worker_entry(cfg: RunConfig, rank: int, gpu: Optional[int]) -> None:
+def _init_worker_group(cfg: RunConfig, rank: int, group_port: int) -> None:
+    """Process group among the WORKERS (the master is not in it).  It carries the 64-byte CUDA IPC
+    handles of the members' symmetric buffers (device exploit paths) and, for the library baselines,
+    the NCCL / gloo state transfers.  Never used for control messages."""
+    import torch
+    import torch.distributed as dist
+    backend = "cpu:gloo,cuda:nccl" if torch.cuda.is_available() else "gloo"
+    kw = {}
+    if torch.cuda.is_available():
+        idx = int(os.environ.get("DTF_LOCAL_GPU", "0")) % torch.cuda.device_count()
+        torch.cuda.set_device(idx)
+        kw["device_id"] = torch.device("cuda", idx)
+    os.environ["RANK"] = str(rank - 1)
+    dist.init_process_group(backend, init_method=f"tcp://{cfg.master_addr}:{group_port}", rank=rank - 1,
+                            world_size=cfg.workers, **kw)
+
+
+def _tcp_worker_entry(cfg: RunConfig, rank: int, gpu: Optional[int], group_port: int = 0) -> None:
     from .parallel.tcp import TcpWorkerComm
     if gpu is not None:
-        os.environ.setdefault("DTF_LOCAL_GPU", str(gpu))
+        os.environ["DTF_LOCAL_GPU"] = str(gpu)
+    if group_port and cfg.workers > 1 and cfg.exploit_path != "file":
+        _init_worker_group(cfg, rank, group_port)
     comm = TcpWorkerComm(cfg.master_addr, cfg.master_port, rank, cfg.workers + 1)
     try:
         run_worker(cfg, comm)
     finally:
         comm.close()
+        try:
+            import torch.distributed as dist
+            if dist.is_initialized():
+                dist.destroy_process_group()
+        except Exception:
+            pass
 
 
 def spawn_tcp(cfg: RunConfig, gpus: Optional[List[int]] = None) -> Dict[str, Any]:
@@ -140,10 +165,21 @@ def spawn_tcp(cfg: RunConfig, gpus: Optional[List[int]] = None) -> Dict[str, Any
     ctx = mp.get_context("spawn")
     master = TcpMasterComm(cfg.master_addr, cfg.master_port, cfg.workers + 1)
     cfg = cfg.replace(master_port=master.port)
+    import socket
+    with socket.socket() as probe:                       # a free port for the workers' own process group
+        probe.bind((cfg.master_addr, 0))
+        group_port = probe.getsockname()[1]
+    if gpus is None:
+        try:
+            import torch
+            if torch.cuda.is_available() and cfg.target_model != "toy":
+                gpus = list(range(torch.cuda.device_count()))
+        except ImportError:
+            pass
     procs = []
     for r in range(1, cfg.workers + 1):
         gpu = gpus[(r - 1) % len(gpus)] if gpus else None
-        p = ctx.Process(target=_tcp_worker_entry, args=(cfg, r, gpu), daemon=True)
+        p = ctx.Process(target=_tcp_worker_entry, args=(cfg, r, gpu, group_port), daemon=True)
         p.start()
         procs.append(p)
     try:

@@ -50,9 +50,11 @@ class GpuMember(ModelBase):
                  engine: str = "auto", dtype: str = "bf16", synthetic: bool = True,
                  data_dir: str = "./datasets", max_train_steps: Optional[int] = None,
                  eval_batches: Optional[int] = None, resume: bool = False,
-                 synthetic_mode: str = "random", device: Optional[torch.device] = None, **_):
+                 synthetic_mode: str = "random", device: Optional[torch.device] = None,
+                 hooks: Optional[List[Any]] = None, **_):
         super().__init__(cluster_id, hparams, save_base_dir)
         self.device = device or pick_device()
+        self._engine_requested = engine
         self.engine_kind = resolve_engine(engine, self.device)
         self.dtype = dtype
         self.synthetic = synthetic
@@ -61,6 +63,7 @@ class GpuMember(ModelBase):
         self.max_train_steps = max_train_steps
         self.eval_batches = eval_batches
         self.device_times: Dict[str, float] = {"train": 0.0, "eval": 0.0, "exploit": 0.0}
+        self.hooks = list(hooks or [])          # utils.logs.hooks.Hook objects, called once per step
         self.train_set, self.eval_set = self.build_datasets()
         self.symm = None                 # symmetric (peer-addressable) buffer, native engine on CUDA only
         self._pending_exploit: Optional[Dict[str, Any]] = None
@@ -122,7 +125,12 @@ class GpuMember(ModelBase):
             for _ in range(steps):
                 idx = self._train_iter.next_indices()
                 x = self.preprocess(self.train_set.images[idx], True)
-                self.engine.train_step(x, self.train_set.labels[idx])
+                loss = self.engine.train_step(x, self.train_set.labels[idx])
+                if self.hooks:                    # values stay on the device unless a hook logs them
+                    self._global_step = getattr(self, "_global_step", 0) + 1
+                    vals = {"cross_entropy": loss, "learning_rate": self.hparams["opt_case"]["lr"]}
+                    for h in self.hooks:
+                        h.after_step(self._global_step, vals)
         dt = max(self.device_times["train"], 1e-9)
         self.last_images_per_sec = steps * bs / max(time.time() - t0, 1e-9)
         return steps

@@ -37,8 +37,15 @@ class MNISTModel(GpuMember):
     def build_engine(self):
         seed = 104729 * (self.cluster_id + 1)
         if self.engine_kind == "native":
-            from .mnist_native import NativeMnistEngine
-            return NativeMnistEngine(self.hparams, self.device, seed=seed, dtype=self.dtype)
+            try:
+                from .mnist_native import NativeMnistEngine
+            except ImportError:
+                if self._engine_requested == "native":
+                    raise
+                self.engine_kind = "eager"          # `auto`: the MNIST kernels are not built into this version
+            else:
+                return NativeMnistEngine(self.hparams, self.device, seed=seed, dtype=self.dtype,
+                                         arena_alloc=self.make_symmetric_alloc)
         from .engine_eager import EagerEngine
         init = mnist_net.init_params(self.hparams.get("initializer", "None"), seed)
         return EagerEngine(mnist_net.param_specs(), mnist_net.forward, init, self.hparams, self.device,
