@@ -117,6 +117,7 @@ DTF_DEVINL float schedule_lr2(const DtfHparams& hp, long long step) {
 }
 
 DTF_DEVINL void pack_store2(const DtfOptSegment& s, dtf_bf16* pack, int local, float w) {
+    if (s.pack == 2) { pack[s.fwd_pack_off + local] = __float2bfloat16(w); return; }
     const int ci = local % s.Cin;
     const int rest = local / s.Cin;
     const int tap = rest % s.taps;

@@ -72,8 +72,9 @@ constexpr int kMaxClasses = 16;
 
 __global__ void __launch_bounds__(kHeadThreads)
 head_kernel(const __grid_constant__ DtfHead P) {
-    __shared__ float s_scale[256], s_shift[256], s_mean[256], s_invstd[256];
-    __shared__ float pooled[256], gpool[256], st1[256], st2[256];
+    constexpr int kMaxHeadC = 1024;
+    __shared__ float s_scale[kMaxHeadC], s_shift[kMaxHeadC], s_mean[kMaxHeadC], s_invstd[kMaxHeadC];
+    __shared__ float pooled[kMaxHeadC], gpool[kMaxHeadC], st1[kMaxHeadC], st2[kMaxHeadC];
     __shared__ float logits[kMaxClasses], dlog[kMaxClasses];
     const int n = blockIdx.x;
     const int C = P.C, HW = P.HW, K = P.classes;
@@ -97,7 +98,7 @@ head_kernel(const __grid_constant__ DtfHead P) {
     const dtf_bf16* xn = P.x + static_cast<size_t>(n) * HW * C;
     // forward: activation + average pool (thread owns channel c = idx % C for all its elements
     // when C divides the thread count, which holds for C in {64, 128, 256})
-    {
+    if (kHeadThreads % C == 0) {        // a thread keeps one channel for all its elements
         const int c = tid % C;
         float acc = 0.f;
         for (int idx = tid; idx < HW * C; idx += kHeadThreads) {
@@ -107,6 +108,14 @@ head_kernel(const __grid_constant__ DtfHead P) {
             acc += a;
         }
         atomicAdd(&pooled[c], acc);
+    } else {
+        for (int idx = tid; idx < HW * C; idx += kHeadThreads) {
+            const int c = idx % C;
+            const float v = __bfloat162float(xn[idx]);
+            float a = fmaf(v, s_scale[c], s_shift[c]);
+            if (P.has_bn) a = fmaxf(a, 0.f);
+            atomicAdd(&pooled[c], a);
+        }
     }
     __syncthreads();
     const float inv_hw = 1.f / HW;
@@ -146,19 +155,19 @@ head_kernel(const __grid_constant__ DtfHead P) {
     }
     __syncthreads();
     {
-        const int c = tid % C;
-        float a1 = 0.f, a2 = 0.f;
         dtf_bf16* tn = P.t_out + static_cast<size_t>(n) * HW * C;
+        const bool fixed_c = kHeadThreads % C == 0;
+        float a1 = 0.f, a2 = 0.f;
         for (int idx = tid; idx < HW * C; idx += kHeadThreads) {
+            const int c = fixed_c ? tid % C : idx % C;
             const float v = __bfloat162float(xn[idx]);
             const bool on = !P.has_bn || fmaf(v, s_scale[c], s_shift[c]) > 0.f;
             const float t = on ? gpool[c] : 0.f;
             tn[idx] = __float2bfloat16(t);
-            a1 += t;
-            a2 += t * (v - s_mean[c]) * s_invstd[c];
+            if (fixed_c) { a1 += t; a2 += t * (v - s_mean[c]) * s_invstd[c]; }
+            else if (P.bwd_stats_out != nullptr) { atomicAdd(&st1[c], t); atomicAdd(&st2[c], t * (v - s_mean[c]) * s_invstd[c]); }
         }
-        atomicAdd(&st1[c], a1);
-        atomicAdd(&st2[c], a2);
+        if (fixed_c) { atomicAdd(&st1[tid % C], a1); atomicAdd(&st2[tid % C], a2); }
     }
     __syncthreads();
     if (P.bwd_stats_out != nullptr)
@@ -172,6 +181,10 @@ head_kernel(const __grid_constant__ DtfHead P) {
 // weight packing: fp32 OHWI master -> bf16 [K/8][N][8] for the forward and dgrad GEMMs
 // ---------------------------------------------------------------------------------------
 DTF_DEVINL void pack_store(const DtfOptSegment& s, dtf_bf16* pack, int local, float w) {
+    if (s.pack == 2) {            // dense kernel: plain bf16 copy, row-major as stored
+        pack[s.fwd_pack_off + local] = __float2bfloat16(w);
+        return;
+    }
     // local index inside the OHWI tensor: ((co*taps + tap)*Cin + ci)
     const int ci = local % s.Cin;
     const int rest = local / s.Cin;
@@ -388,7 +401,7 @@ extern "C" int dtf_bn_bwd_apply(const dtf_bf16* t, const dtf_bf16* x, const dtf_
 }
 
 extern "C" int dtf_head(const DtfHead* p, cudaStream_t stream) {
-    if (p->C > 256 || p->classes > dtf::kMaxClasses || (256 % p->C) != 0) return DTF_ERR_SHAPE;
+    if (p->C > 1024 || p->classes > dtf::kMaxClasses) return DTF_ERR_SHAPE;
     dtf::head_kernel<<<p->batch, dtf::kHeadThreads, 0, stream>>>(*p);
     return DTF_CHECK_LAUNCH();
 }

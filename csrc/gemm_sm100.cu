@@ -1,0 +1,308 @@
+// Dense-layer GEMM on tcgen05 (MNIST: dense 3136 -> 1024 forward, dgrad and wgrad — reference
+// mnist_model.py:90-97 — the only "real" GEMM of the reference) plus the small kernels around it:
+// 2x2 max-pool forward / backward (+ReLU mask + bias gradient), activation-mask + bias gradient.
+//
+// D[M][N] = A x B^T where each operand is a row-major bf16 matrix that is either
+//   K-major   X[i][k]  (rows index M or N, columns index K)   or
+//   MN-major  X[k][i]  (rows index K, columns index M or N);
+// both land in shared memory as 16-byte chunks [chunk][row][8] and are described to the tensor core
+// with SWIZZLE_NONE descriptors (K-major: LBO = chunk stride, SBO = 128; MN-major: SBO = chunk stride,
+// LBO = 128), exactly like the convolution kernels.  Chunk strides are padded by 16 bytes so that the
+// coalesced global->shared gather (consecutive threads = consecutive chunks of one row) is free of bank
+// conflicts.  Tile 128 x 128 x 64, three operand stages, two TMEM accumulators are not needed (one tile
+// per CTA): 4 epilogue warps + 1 MMA warp + 8 gather warps.
+#include "common.cuh"
+#include "dtf_b200.h"
+
+namespace dtf {
+
+constexpr int kGThreads = 13 * 32;
+constexpr int kGGather = 8 * 32;
+constexpr int kGStages = 3;
+constexpr int kBM = 128, kBN = 128, kBK = 64;
+constexpr int kCsK = 128 * 16 + 16;      // K-major chunk stride (128 rows), padded
+constexpr int kCsMN = 64 * 16 + 16;      // MN-major chunk stride (64 k-rows), padded
+constexpr int kPanelBytes = 16 * kCsMN > 8 * kCsK ? 16 * kCsMN : 8 * kCsK;   // 16640
+
+struct __align__(16) GemmHeader {
+    uint64_t full[kGStages], empty[kGStages], acc_full;
+    uint32_t tmem_base, pad;
+};
+
+DTF_DEVINL uint32_t hash32(uint32_t x) {
+    x ^= x >> 16; x *= 0x7feb352dU; x ^= x >> 15; x *= 0x846ca68bU; x ^= x >> 16;
+    return x;
+}
+
+// one 128-wide panel (rows0.. of the M or N dimension) for K range [k0, k0+64)
+DTF_DEVINL void load_panel(const dtf_bf16* __restrict__ base, long long ld, int mn_major, int rows0, int rows_total,
+                           int k0, int K, uint32_t dst, int g) {
+    if (!mn_major) {      // X[i][k]: 128 rows x 8 chunks; thread -> (row = g/8 + 32 j, chunk = g%8)
+        const int c = g & 7;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int r = (g >> 3) + 32 * j;
+            uint4 v = make_uint4(0, 0, 0, 0);
+            const int row = rows0 + r, k = k0 + c * 8;
+            if (row < rows_total && k < K) v = ldg16(base + static_cast<long long>(row) * ld + k);
+            sts16(dst + c * kCsK + r * 16, v);
+        }
+    } else {              // X[k][i]: 64 k-rows x 16 chunks; thread -> (k-row = g/16 + 16 j, chunk = g%16)
+        const int c = g & 15;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int r = (g >> 4) + 16 * j;
+            uint4 v = make_uint4(0, 0, 0, 0);
+            const int k = k0 + r, col = rows0 + c * 8;
+            if (k < K && col < rows_total) v = ldg16(base + static_cast<long long>(k) * ld + col);
+            sts16(dst + c * kCsMN + r * 16, v);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kGThreads, 1)
+gemm_kernel(const __grid_constant__ DtfGemm P) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    GemmHeader* hdr = reinterpret_cast<GemmHeader*>(smem);
+    uint8_t* stages = smem + 1024;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int m0 = blockIdx.x * kBM, n0 = blockIdx.y * kBN;
+    const int num_kb = (P.K + kBK - 1) / kBK;
+    if (tid == 0) {
+        for (int i = 0; i < kGStages; ++i) { mbar_init(smem_u32(&hdr->full[i]), kGGather); mbar_init(smem_u32(&hdr->empty[i]), 1); }
+        mbar_init(smem_u32(&hdr->acc_full), 1);
+        mbar_fence_init();
+    }
+    if (warp == 4) tmem_alloc(smem_u32(&hdr->tmem_base), 128);
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    const uint32_t tmem_base = hdr->tmem_base;
+    if (warp == 4) {
+        const uint32_t idesc = umma_idesc_bf16(kBM, kBN, P.a_mn_major != 0, P.b_mn_major != 0);
+        for (int kb = 0; kb < num_kb; ++kb) {
+            const uint32_t st = kb % kGStages;
+            mbar_wait(smem_u32(&hdr->full[st]), (kb / kGStages) & 1, 0x51);
+            tc_fence_after_sync();
+            const uint32_t a_base = smem_u32(stages) + st * 2 * kPanelBytes, b_base = a_base + kPanelBytes;
+            if (elect_one()) {
+#pragma unroll
+                for (int ks = 0; ks < kBK / 16; ++ks) {
+                    const uint64_t ad = P.a_mn_major ? umma_desc(a_base + ks * 256, 128, kCsMN)
+                                                     : umma_desc(a_base + ks * 2 * kCsK, kCsK, 128);
+                    const uint64_t bd = P.b_mn_major ? umma_desc(b_base + ks * 256, 128, kCsMN)
+                                                     : umma_desc(b_base + ks * 2 * kCsK, kCsK, 128);
+                    umma_bf16(tmem_base, ad, bd, idesc, (kb | ks) != 0);
+                }
+                umma_commit(smem_u32(&hdr->empty[st]));
+                if (kb == num_kb - 1) umma_commit(smem_u32(&hdr->acc_full));
+            }
+            __syncwarp();
+        }
+    } else if (warp > 4) {
+        const int g = tid - 5 * 32;
+        for (int kb = 0; kb < num_kb; ++kb) {
+            const uint32_t st = kb % kGStages;
+            mbar_wait(smem_u32(&hdr->empty[st]), ((kb / kGStages) & 1) ^ 1, 0x52);
+            const uint32_t a_dst = smem_u32(stages) + st * 2 * kPanelBytes, b_dst = a_dst + kPanelBytes;
+            load_panel(P.a, P.lda, P.a_mn_major, m0, P.M, kb * kBK, P.K, a_dst, g);
+            load_panel(P.b, P.ldb, P.b_mn_major, n0, P.N, kb * kBK, P.K, b_dst, g);
+            fence_proxy_async_smem();
+            mbar_arrive(smem_u32(&hdr->full[st]));
+        }
+    } else {
+        mbar_wait(smem_u32(&hdr->acc_full), 0, 0x53);
+        tc_fence_after_sync();
+        const int m = m0 + warp * 32 + lane;
+        const bool mvalid = m < P.M;
+        const long long step = P.step ? *P.step : 0;
+        for (int cg = 0; cg < kBN; cg += 16) {
+            float v[16];
+            tmem_ld16(tmem_base + ((warp * 32u) << 16) + cg, v);
+            const int n = n0 + cg;
+            if (!mvalid || n >= P.N) continue;
+            const long long o = static_cast<long long>(m) * P.ldo + n;
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+                float x = v[i];
+                if (n + i < P.N) {
+                    if (P.bias) x += P.bias[n + i];
+                    if (P.relu) x = fmaxf(x, 0.f);
+                    if (P.dropout_keep < 1.f) {      // inverted dropout, counter-based mask (seed, step, element)
+                        const uint32_t h = hash32(static_cast<uint32_t>(o + i) ^ hash32(P.seed + static_cast<uint32_t>(step) * 0x9E3779B9u));
+                        x = (h >> 8) * (1.f / 16777216.f) < P.dropout_keep ? x / P.dropout_keep : 0.f;
+                    }
+                }
+                v[i] = x;
+            }
+            if (P.out_fp32) {
+                float* op = static_cast<float*>(P.out) + o;
+#pragma unroll
+                for (int i = 0; i < 16; ++i) if (n + i < P.N) op[i] = v[i];
+            } else {
+                dtf_bf16* op = static_cast<dtf_bf16*>(P.out) + o;
+                if (n + 16 <= P.N && ((o & 7) == 0)) {
+                    reinterpret_cast<uint4*>(op)[0] = pack8(v);
+                    reinterpret_cast<uint4*>(op)[1] = pack8(v + 8);
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) if (n + i < P.N) op[i] = __float2bfloat16(v[i]);
+                }
+            }
+        }
+    }
+    tc_fence_before_sync();
+    __syncthreads();
+    if (warp == 4) { tc_fence_after_sync(); tmem_dealloc(tmem_base, 128); }
+}
+
+// ---------------------------------------------------------------------------------------
+// 2x2 / stride-2 max pool, NHWC bf16 (mnist_model.py:77,87)
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+maxpool_fwd_kernel(const dtf_bf16* __restrict__ x, dtf_bf16* __restrict__ y, int NB, int H, int W, int C) {
+    const int Ho = H / 2, Wo = W / 2, cv = C / 8;
+    const long long total = static_cast<long long>(NB) * Ho * Wo * cv;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const int c8 = static_cast<int>(i % cv);
+        long long p = i / cv;
+        const int ox = static_cast<int>(p % Wo); p /= Wo;
+        const int oy = static_cast<int>(p % Ho);
+        const int n = static_cast<int>(p / Ho);
+        float m[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) m[k] = -3.0e38f;
+#pragma unroll
+        for (int dy = 0; dy < 2; ++dy)
+#pragma unroll
+            for (int dx = 0; dx < 2; ++dx) {
+                float f[8];
+                unpack8(ldg16(x + ((static_cast<long long>(n) * H + 2 * oy + dy) * W + 2 * ox + dx) * C + c8 * 8), f);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) m[k] = fmaxf(m[k], f[k]);
+            }
+        *reinterpret_cast<uint4*>(y + ((static_cast<long long>(n) * Ho + oy) * Wo + ox) * C + c8 * 8) = pack8(m);
+    }
+}
+
+// gx = gy routed to the first maximum of each window, times the ReLU mask of x (x is a post-ReLU
+// activation, so mask = x > 0); also accumulates the bias gradient db[c] += sum gx.
+__global__ void __launch_bounds__(256)
+maxpool_bwd_kernel(const dtf_bf16* __restrict__ x, const dtf_bf16* __restrict__ y, const dtf_bf16* __restrict__ gy,
+                   dtf_bf16* __restrict__ gx, float* __restrict__ db, int NB, int H, int W, int C) {
+    extern __shared__ float s_db[];
+    for (int c = threadIdx.x; c < C; c += blockDim.x) s_db[c] = 0.f;
+    __syncthreads();
+    const int Ho = H / 2, Wo = W / 2, cv = C / 8;
+    const long long total = static_cast<long long>(NB) * Ho * Wo * cv;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const int c8 = static_cast<int>(i % cv);
+        long long p = i / cv;
+        const int ox = static_cast<int>(p % Wo); p /= Wo;
+        const int oy = static_cast<int>(p % Ho);
+        const int n = static_cast<int>(p / Ho);
+        const long long ob = ((static_cast<long long>(n) * Ho + oy) * Wo + ox) * C + c8 * 8;
+        float ym[8], g[8];
+        unpack8(ldg16(y + ob), ym);
+        unpack8(ldg16(gy + ob), g);
+        bool taken[8] = {false, false, false, false, false, false, false, false};
+        float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+        for (int dy = 0; dy < 2; ++dy)
+#pragma unroll
+            for (int dx = 0; dx < 2; ++dx) {
+                const long long ib = ((static_cast<long long>(n) * H + 2 * oy + dy) * W + 2 * ox + dx) * C + c8 * 8;
+                float f[8], o[8];
+                unpack8(ldg16(x + ib), f);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    const bool hit = !taken[k] && f[k] == ym[k];
+                    taken[k] = taken[k] || hit;
+                    o[k] = (hit && f[k] > 0.f) ? g[k] : 0.f;
+                    acc[k] += o[k];
+                }
+                *reinterpret_cast<uint4*>(gx + ib) = pack8(o);
+            }
+        if (db != nullptr) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) atomicAdd(&s_db[c8 * 8 + k], acc[k]);
+        }
+    }
+    __syncthreads();
+    if (db != nullptr)
+        for (int c = threadIdx.x; c < C; c += blockDim.x) atomicAdd(db + c, s_db[c]);
+}
+
+// g_out = g_in * (act > 0) * scale ;  db[c] += column sums      (dense + ReLU + dropout backward)
+__global__ void __launch_bounds__(256)
+act_mask_kernel(const dtf_bf16* __restrict__ g_in, const dtf_bf16* __restrict__ act, dtf_bf16* __restrict__ g_out,
+                float* __restrict__ db, float scale, long long rows, int C) {
+    const int cv = C / 8;
+    const int c8 = blockIdx.x * blockDim.x + threadIdx.x;          // one thread = one 8-channel column strip
+    if (c8 >= cv) return;
+    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (long long r = blockIdx.y; r < rows; r += gridDim.y) {
+        const long long o = r * C + c8 * 8;
+        float g[8], a[8];
+        unpack8(ldg16(g_in + o), g);
+        unpack8(ldg16(act + o), a);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) { g[k] = a[k] > 0.f ? g[k] * scale : 0.f; acc[k] += g[k]; }
+        *reinterpret_cast<uint4*>(g_out + o) = pack8(g);
+    }
+    if (db != nullptr) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) atomicAdd(db + c8 * 8 + k, acc[k]);
+    }
+}
+
+}  // namespace dtf
+
+#define DTF_CHECK_LAUNCH() (cudaGetLastError() == cudaSuccess ? DTF_OK : DTF_ERR_CUDA)
+
+extern "C" int dtf_gemm(const DtfGemm* p, cudaStream_t stream) {
+    using namespace dtf;
+    if (p->M < 1 || p->N < 1 || p->K < 1) return DTF_ERR_SHAPE;
+    if ((p->lda & 7) || (p->ldb & 7) || ((uintptr_t)p->a & 15) || ((uintptr_t)p->b & 15)) return DTF_ERR_ARG;
+    if (!p->a_mn_major && (p->K & 7)) return DTF_ERR_SHAPE;          // 16-byte chunks along K
+    if (!p->b_mn_major && (p->K & 7)) return DTF_ERR_SHAPE;
+    if (p->a_mn_major && (p->M & 7)) return DTF_ERR_SHAPE;
+    if (p->b_mn_major && (p->N & 7)) return DTF_ERR_SHAPE;
+    const int smem_bytes = 1024 + kGStages * 2 * kPanelBytes;
+    static int set = 0;
+    if (!set) {
+        if (cudaFuncSetAttribute(gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes) != cudaSuccess) return DTF_ERR_CUDA;
+        set = 1;
+    }
+    dim3 grid((p->M + kBM - 1) / kBM, (p->N + kBN - 1) / kBN);
+    gemm_kernel<<<grid, kGThreads, smem_bytes, stream>>>(*p);
+    return DTF_CHECK_LAUNCH();
+}
+
+extern "C" int dtf_maxpool_fwd(const dtf_bf16* x, dtf_bf16* y, int NB, int H, int W, int C, cudaStream_t stream) {
+    if ((C & 7) || (H & 1) || (W & 1)) return DTF_ERR_SHAPE;
+    const long long total = static_cast<long long>(NB) * (H / 2) * (W / 2) * (C / 8);
+    long long blocks = (total + 255) / 256;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    dtf::maxpool_fwd_kernel<<<static_cast<int>(blocks < 1 ? 1 : blocks), 256, 0, stream>>>(x, y, NB, H, W, C);
+    return DTF_CHECK_LAUNCH();
+}
+
+extern "C" int dtf_maxpool_bwd(const dtf_bf16* x, const dtf_bf16* y, const dtf_bf16* gy, dtf_bf16* gx, float* db,
+                               int NB, int H, int W, int C, cudaStream_t stream) {
+    if ((C & 7) || (H & 1) || (W & 1) || C > 1024) return DTF_ERR_SHAPE;
+    const long long total = static_cast<long long>(NB) * (H / 2) * (W / 2) * (C / 8);
+    long long blocks = (total + 255) / 256;
+    if (blocks > 148 * 4) blocks = 148 * 4;
+    dtf::maxpool_bwd_kernel<<<static_cast<int>(blocks < 1 ? 1 : blocks), 256, C * sizeof(float), stream>>>(x, y, gy, gx, db, NB, H, W, C);
+    return DTF_CHECK_LAUNCH();
+}
+
+extern "C" int dtf_act_mask(const dtf_bf16* g_in, const dtf_bf16* act, dtf_bf16* g_out, float* db, float scale,
+                            long long rows, int C, cudaStream_t stream) {
+    if (C & 7) return DTF_ERR_SHAPE;
+    const int cv = C / 8;
+    dim3 grid((cv + 127) / 128, static_cast<unsigned>(rows < 64 ? (rows < 1 ? 1 : rows) : 64));
+    dtf::act_mask_kernel<<<grid, 128, 0, stream>>>(g_in, act, g_out, db, scale, rows, C);
+    return DTF_CHECK_LAUNCH();
+}

@@ -31,6 +31,7 @@ import torch
 
 from ..ops import native, reference
 from . import resnet
+from .native_base import NativeEngineBase, _align
 
 IMG_C = 8          # image channels padded 3 -> 8 (one 16-byte chunk)
 MAX_BATCH = 256    # explore keeps batch_size in [65, 256]
@@ -75,12 +76,7 @@ class Block:
     stride: int
 
 
-def _align(n: int, a: int = 256) -> int:
-    return (n + a - 1) // a * a
-
-
-class NativeResNetEngine:
-    kind = "native"
+class NativeResNetEngine(NativeEngineBase):
 
     def __init__(self, cfg: resnet.ResNetConfig, hparams: Dict[str, Any], device, *, seed: int = 0,
                  dtype: str = "bf16", max_batch: int = MAX_BATCH, use_graphs: bool = True,
@@ -89,23 +85,17 @@ class NativeResNetEngine:
             raise NotImplementedError("native engine covers the CIFAR configuration: ResNet v2, building blocks")
         if dtype != "bf16":
             raise NotImplementedError("native engine computes in bf16 with fp32 master weights / accumulation")
-        native.require()
+        super().__init__(device, max_batch=max_batch, use_graphs=use_graphs, arena_alloc=arena_alloc,
+                         dp_group=dp_group, seed=seed)
         self.cfg = cfg
-        self.device = torch.device(device)
-        self.max_batch = max_batch
-        self.use_graphs = use_graphs
-        self.hp: Dict[str, Any] = {}
-        self._graphs: Dict[Tuple[str, int], torch.cuda.CUDAGraph] = {}
-        self.dp_group = dp_group          # torch.distributed group of this member's replicas (None = 1 GPU)
-        self.dp = None
+        self.image_size, self.image_channels = cfg.image_size, cfg.in_channels
         self._build_plan()
-        self._alloc(arena_alloc)
+        self._alloc()
         self._init_params(hparams.get("initializer", "None"), seed)
         self.set_hparams(hparams, reset_slots=True)
-        self.last_loss: Optional[torch.Tensor] = None
-        self.launches_per_step = 0
-        self._pp_counter = 0
-        self._seed = seed
+
+    def lr_schedule(self, hp):
+        return reference.cifar_lr_schedule(hp)
 
     # ------------------------------------------------------------------ plan
     def _build_plan(self) -> None:
@@ -176,69 +166,16 @@ class NativeResNetEngine:
         off += cfg.num_classes
         self.n_params = off
         self.n_stats, self.n_running, self.n_pack = stat, run, pack
-        chunks: List[int] = []
-        for si, s in enumerate(self.segments):
-            for start in range(0, s.count, native.OPT_CHUNK):
-                chunks += [si, start]
-        self.n_chunks = len(chunks) // 2
-        self._chunks_host = torch.tensor(chunks, dtype=torch.int32)
+        self._finish_segments()
 
     # ------------------------------------------------------------------ memory
-    def _alloc(self, arena_alloc) -> None:
+    def _alloc(self) -> None:
+        self._alloc_arena()
         dev = self.device
-        P = _align(self.n_params * 4) // 4
-        self.P_pad = P
-        HP = _align(C.sizeof(native.Hparams))
-        off = {}
-        cur = 0
-        for name, nbytes in [("hparams", HP), ("step", 256), ("params", P * 4), ("slot0", P * 4), ("slot1", P * 4),
-                             ("running", _align(self.n_running * 4))]:
-            off[name] = cur
-            cur += _align(nbytes)
-        self.state_bytes_total = cur
-        alloc = arena_alloc or (lambda n: torch.zeros(n, dtype=torch.uint8, device=dev))
-        self.state = alloc(cur)[:cur]                 # the region exploit copies
-        self.hp_state_offset = off["hparams"]
-        self._state_off = off
-        v = self.state
-
-        def view(name, dtype, count):
-            esz = torch.empty(0, dtype=dtype).element_size()
-            return v[off[name]: off[name] + count * esz].view(dtype)
-
-        self.hp_dev = v[off["hparams"]: off["hparams"] + C.sizeof(native.Hparams)]
-        self.step_dev = view("step", torch.int64, 1)
-        self.params = view("params", torch.float32, P)
-        self.slot0 = view("slot0", torch.float32, P)
-        self.slot1 = view("slot1", torch.float32, P)
-        self.running = view("running", torch.float32, self.n_running)
-        self.pack = torch.zeros(self.n_pack, dtype=torch.bfloat16, device=dev)
-        # per-step zeroed region: grads | batch statistics | loss, correct
-        zfloats = P + _align(self.n_stats * 4) // 4 + 64
-        if self.dp_group is not None:
-            # data-parallel member: the gradient arena must be addressable by the peer replicas
-            from ..parallel.dp import DataParallelGroup
-            self.dp = DataParallelGroup(zfloats * 4, dev, group=self.dp_group)
-            self.zero_region = self.dp.alloc_grads(zfloats * 4).view(torch.float32)
-        else:
-            self.zero_region = torch.zeros(zfloats, dtype=torch.float32, device=dev)
-        self.grads = self.zero_region[:P]
-        s0 = P
-        self.stats = self.zero_region[s0: s0 + self.n_stats]
-        m0 = s0 + _align(self.n_stats * 4) // 4
-        self.loss_cell = self.zero_region[m0: m0 + 1]
-        self.correct_cell = self.zero_region[m0 + 1: m0 + 2].view(torch.int32)
-        # evaluation accumulators live outside the zeroed region; exploit clears them for the loser
-        self.eval_cells = torch.zeros(4, dtype=torch.float32, device=dev)
-        self.round_cells = self.eval_cells
-        self.segs_dev = native.struct_to_tensor((native.OptSegment * len(self.segments))(*self.segments), dev)
-        self.chunks_dev = self._chunks_host.to(dev)
         # static IO + activations, sized for the largest batch so pointers never move
         mb = self.max_batch
         cfg = self.cfg
         S = cfg.image_size
-        self.in_u8 = torch.zeros(mb, S, S, cfg.in_channels, dtype=torch.uint8, device=dev)
-        self.labels = torch.zeros(mb, dtype=torch.int32, device=dev)
         self.image = torch.zeros(mb, S, S, IMG_C, dtype=torch.bfloat16, device=dev)
 
         def act(h, c):
@@ -303,51 +240,6 @@ class NativeResNetEngine:
         out["dense/kernel"] = base[self.dense_w_off: self.dense_w_off + n].view(self.cfg.num_classes, -1).clone()
         out["dense/bias"] = base[self.dense_b_off: self.dense_b_off + self.cfg.num_classes].clone()
         return out
-
-    def repack(self) -> None:
-        native.pack_weights(self.params, self.pack, self.segs_dev, self.chunks_dev, self.n_chunks)
-
-    # ------------------------------------------------------------------ hparams
-    def hparams_struct(self, hp: Dict[str, Any]) -> "native.Hparams":
-        oc = hp["opt_case"]
-        h = native.Hparams()
-        h.optimizer = reference.OPT_IDS[oc["optimizer"]]
-        h.regularizer = reference.REG_IDS[hp.get("regularizer", "None")]
-        h.momentum = float(oc.get("momentum", 0.0))
-        h.grad_decay = float(oc.get("grad_decay", 0.9))
-        h.weight_decay = float(hp.get("weight_decay", 0.0))
-        h.inv_loss_scale = 1.0
-        bounds, values = reference.cifar_lr_schedule(hp)
-        if len(bounds) > native.MAX_LR_BOUNDARIES:
-            raise ValueError("LR schedule has too many boundaries for the device block")
-        h.n_boundaries = len(bounds)
-        h.batch_size = int(hp["batch_size"])
-        for i, b in enumerate(bounds):
-            h.boundaries[i] = int(b)
-        for i, v in enumerate(values):
-            h.lr_values[i] = float(v)
-        return h
-
-    def adopt_hparams(self, hp: Dict[str, Any]) -> None:
-        """The device block was already written by the exploit kernel: only mirror it on the host."""
-        self.hp = hp
-        self._hp_struct = self.hparams_struct(hp)
-
-    def set_hparams(self, hp: Dict[str, Any], reset_slots: bool = False, keep_slots: bool = False) -> None:
-        prev = self.hp.get("opt_case", {}).get("optimizer") if self.hp else None
-        self.hp = hp
-        oc = hp["opt_case"]
-        h = self.hparams_struct(hp)
-        self._hp_struct = h
-        self.hp_dev.copy_(native.struct_to_tensor(h, "cpu").to(self.device, non_blocking=True))
-        if reset_slots or (prev != oc["optimizer"] and not keep_slots):
-            a, b = reference.slot_init_values(oc["optimizer"])
-            native.fill(self.slot0, a)
-            native.fill(self.slot1, b)
-
-    @property
-    def step(self) -> int:
-        return int(self.step_dev.item())
 
     # ------------------------------------------------------------------ kernels of one step
     def _bn(self, b: BnL, nb: int, training: bool) -> native.BnRef:
@@ -467,22 +359,12 @@ class NativeResNetEngine:
 
     def _train_kernels(self, nb: int, pp_mode: int) -> None:
         self._count = 0
-        if self.dp is not None:
-            self.dp.step_begin(self.zero_region, self.step_dev)
-        else:
-            native.step_begin(self.zero_region, self.step_dev, bump=True)
+        self._begin_step()
         native.preprocess(self.in_u8, None, self.image, mode=pp_mode, seed=self._seed, counter=self._pp_counter, n=nb)
-        self._count += 2
+        self._count += 1
         x_last = self._forward(nb, True)
         self._backward(x_last, nb)
-        if self.dp is not None:
-            self.dp.allreduce_update(self.params, self.slot0, self.slot1, self.pack, self.segs_dev,
-                                     self.chunks_dev, self.n_chunks, self.hp_dev, self.step_dev)
-        else:
-            native.optimizer_step(self.params, self.grads, self.slot0, self.slot1, self.pack, self.segs_dev,
-                                  self.chunks_dev, self.n_chunks, self.hp_dev, self.step_dev, 1.0)
-        self._count += 1
-        self.launches_per_step = self._count
+        self._apply_update()
 
     def _eval_kernels(self, nb: int) -> None:
         self._count = 0
@@ -490,85 +372,3 @@ class NativeResNetEngine:
         x_last = self._forward(nb, False)
         self._head(x_last, nb, False, loss=self.eval_cells[0:1], correct=self.eval_cells[1:2].view(torch.int32))
 
-    # ------------------------------------------------------------------ public step API
-    def _run(self, kind: str, nb: int, fn) -> None:
-        if not self.use_graphs:
-            fn()
-            return
-        key = (kind, nb)
-        g = self._graphs.get(key)
-        if g is None:
-            fn()                                   # warm-up: sets kernel attributes, touches buffers
-            if kind == "train":                    # undo the warm-up's side effects on the step counter
-                pass
-            torch.cuda.synchronize(self.device)
-            g = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(g):
-                fn()
-            self._graphs[key] = g
-            if len(self._graphs) > 16:
-                self._graphs.pop(next(iter(self._graphs)))
-            return                                 # the warm-up run already performed this step
-        g.replay()
-
-    def load_batch(self, images_u8: torch.Tensor, labels: torch.Tensor) -> int:
-        nb = int(images_u8.shape[0])
-        if nb > self.max_batch:
-            raise ValueError(f"batch {nb} exceeds the engine's max_batch {self.max_batch}")
-        self.in_u8[:nb].copy_(images_u8, non_blocking=True)
-        self.labels[:nb].copy_(labels.to(torch.int32), non_blocking=True)
-        return nb
-
-    def train_step_u8(self, images_u8: torch.Tensor, labels: torch.Tensor, augment: bool = True) -> torch.Tensor:
-        """uint8 NHWC images (device or pinned host) -> one optimizer step; returns the loss cell."""
-        nb = self.load_batch(images_u8, labels)
-        mode = 2 if augment else 1
-        self._pp_counter += nb
-        self._run("train" if augment else "train_noaug", nb, lambda: self._train_kernels(nb, mode))
-        self.last_loss = self.loss_cell
-        return self.loss_cell
-
-    def eval_batch_u8(self, images_u8: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
-        nb = self.load_batch(images_u8, labels)
-        before = self.eval_cells[1:2].view(torch.int32).clone()
-        self._run("eval", nb, lambda: self._eval_kernels(nb))
-        return self.eval_cells[1:2].view(torch.int32) - before
-
-    # GpuMember hooks: preprocessing happens inside the step, so these take raw uint8 batches
-    def preprocess(self, images_u8: torch.Tensor, training: bool) -> torch.Tensor:
-        return images_u8
-
-    def train_step(self, images_u8: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
-        return self.train_step_u8(images_u8, labels, augment=True)
-
-    def eval_batch(self, images_u8: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
-        return self.eval_batch_u8(images_u8, labels).sum()
-
-    # ------------------------------------------------------------------ state
-    def state_tensors(self) -> Dict[str, torch.Tensor]:
-        return {"params": self.params[: self.n_params], "slot0": self.slot0[: self.n_params],
-                "slot1": self.slot1[: self.n_params], "running": self.running, "step": self.step_dev}
-
-    @torch.no_grad()
-    def load_state(self, tensors: Dict[str, Any], step: int) -> None:
-        for k, dst in self.state_tensors().items():
-            if k == "step":
-                continue
-            src = tensors[k]
-            src = src if isinstance(src, torch.Tensor) else torch.from_numpy(src)
-            dst.copy_(src.to(self.device).view_as(dst))
-        self.step_dev.fill_(int(step))
-        self.repack()
-
-    def state_bytes(self) -> int:
-        return self.state_bytes_total
-
-    def after_state_replaced(self) -> None:
-        """Call after the state arena was overwritten from outside (exploit): refresh derived data."""
-        self.repack()
-
-    def synchronize(self) -> None:
-        torch.cuda.synchronize(self.device)
-
-    def close(self) -> None:
-        self._graphs.clear()

@@ -129,10 +129,44 @@ def _declare(l: C.CDLL) -> None:
     l.dtf_step_begin.argtypes = [vp, ll, vp, i, vp]
     l.dtf_fill.argtypes = [vp, ll, f, vp]
     l.dtf_preprocess.argtypes = [vp, vp, vp, vp, i, i, i, i, i, C.c_ulonglong, C.c_ulonglong, vp]
+    l.dtf_gemm.argtypes = [C.POINTER(Gemm), vp]
+    l.dtf_maxpool_fwd.argtypes = [vp, vp, i, i, i, i, vp]
+    l.dtf_maxpool_bwd.argtypes = [vp, vp, vp, vp, vp, i, i, i, i, vp]
+    l.dtf_act_mask.argtypes = [vp, vp, vp, vp, f, ll, i, vp]
+    for name in ("dtf_gemm", "dtf_maxpool_fwd", "dtf_maxpool_bwd", "dtf_act_mask"):
+        getattr(l, name).restype = i
     for name in ("dtf_conv_gemm", "dtf_conv_wgrad", "dtf_bn_bwd_apply", "dtf_head", "dtf_pack_weights",
                  "dtf_optimizer_step", "dtf_step_begin", "dtf_fill", "dtf_preprocess"):
         getattr(l, name).restype = i
     _declare_optional(l)
+
+
+class Gemm(C.Structure):
+    _fields_ = [("a", C.c_void_p), ("b", C.c_void_p), ("out", C.c_void_p), ("bias", C.c_void_p), ("step", C.c_void_p),
+                ("lda", C.c_longlong), ("ldb", C.c_longlong), ("ldo", C.c_longlong),
+                ("M", C.c_int), ("N", C.c_int), ("K", C.c_int),
+                ("a_mn_major", C.c_int), ("b_mn_major", C.c_int), ("out_fp32", C.c_int), ("relu", C.c_int),
+                ("dropout_keep", C.c_float), ("seed", C.c_uint)]
+
+
+def gemm(a, b, out, *, M: int, N: int, K: int, lda: int, ldb: int, ldo: int, a_mn_major=False, b_mn_major=False,
+         bias=None, relu=False, dropout_keep: float = 1.0, seed: int = 0, step=None) -> None:
+    """out[M][N] = A x B^T (see include/dtf_b200.h: DtfGemm); ``out`` fp32 or bf16."""
+    p = Gemm(ptr(a), ptr(b), ptr(out), ptr(bias), ptr(step), lda, ldb, ldo, M, N, K, int(a_mn_major),
+             int(b_mn_major), int(out.dtype == torch.float32), int(relu), dropout_keep, seed & 0xFFFFFFFF)
+    check(lib().dtf_gemm(C.byref(p), stream_ptr()), "dtf_gemm")
+
+
+def maxpool_fwd(x, y, NB, H, W, Cc) -> None:
+    check(lib().dtf_maxpool_fwd(ptr(x), ptr(y), NB, H, W, Cc, stream_ptr()), "dtf_maxpool_fwd")
+
+
+def maxpool_bwd(x, y, gy, gx, db, NB, H, W, Cc) -> None:
+    check(lib().dtf_maxpool_bwd(ptr(x), ptr(y), ptr(gy), ptr(gx), ptr(db), NB, H, W, Cc, stream_ptr()), "dtf_maxpool_bwd")
+
+
+def act_mask(g_in, act, g_out, db, scale: float, rows: int, Cc: int) -> None:
+    check(lib().dtf_act_mask(ptr(g_in), ptr(act), ptr(g_out), ptr(db), scale, rows, Cc, stream_ptr()), "dtf_act_mask")
 
 
 def _declare_optional(l: C.CDLL) -> None:

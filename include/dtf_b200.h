@@ -137,7 +137,7 @@ typedef struct {
 typedef struct {
     int offset, count;       /* elements, in params / grads / slot0 / slot1 */
     int regularized;         /* conv kernels only (resnet_model.py:91) */
-    int pack;                /* emit bf16 GEMM-ready copies */
+    int pack;                /* 1 = conv kernel: emit GEMM-ready bf16 copies; 2 = dense: plain bf16 copy */
     int Cout, taps, Cin;     /* OHWI dims of a conv kernel */
     int fwd_pack_off;        /* element offsets in the bf16 pack arena, -1 = none */
     int dgrad_pack_off;
@@ -230,6 +230,28 @@ int dtf_exploit_copy_noalloc(void* dst, const void* src, long long bytes, long l
                              const DtfHparams* new_hp, void* zero_region, long long zero_bytes,
                              unsigned long long* done_flag, unsigned long long epoch, cudaStream_t stream);
 const char* dtf_noalloc_last_error(void);
+
+/* ---- dense layers and pooling (MNIST member: mnist_model.py:62-126) ------------------------------
+ * D[M][N] = A x B^T on tcgen05.  An operand is row-major bf16, either K-major X[i][k] (ld = row pitch,
+ * K multiple of 8) or MN-major X[k][i] (the M/N extent multiple of 8).  Epilogue: + bias[n], ReLU,
+ * inverted dropout with a counter-based mask (seed, *step, element index); output bf16 or fp32. */
+typedef struct {
+    const dtf_bf16* a; const dtf_bf16* b;
+    void* out; const float* bias; const long long* step;
+    long long lda, ldb, ldo;
+    int M, N, K;
+    int a_mn_major, b_mn_major, out_fp32, relu;
+    float dropout_keep;      /* 1.0 = no dropout */
+    unsigned int seed;
+} DtfGemm;
+int dtf_gemm(const DtfGemm* p, cudaStream_t stream);
+int dtf_maxpool_fwd(const dtf_bf16* x, dtf_bf16* y, int NB, int H, int W, int C, cudaStream_t stream);
+/* gx = gy at the first maximum of each 2x2 window, masked by x > 0 (x is post-ReLU); db[c] += sum gx */
+int dtf_maxpool_bwd(const dtf_bf16* x, const dtf_bf16* y, const dtf_bf16* gy, dtf_bf16* gx, float* db,
+                    int NB, int H, int W, int C, cudaStream_t stream);
+/* g_out = g_in * (act > 0) * scale; db[c] += column sums   (ReLU + dropout backward, bias gradient) */
+int dtf_act_mask(const dtf_bf16* g_in, const dtf_bf16* act, dtf_bf16* g_out, float* db, float scale,
+                 long long rows, int C, cudaStream_t stream);
 
 #ifdef __cplusplus
 }
