@@ -330,8 +330,23 @@ conv3x3_kernel(const __grid_constant__ DtfConvGemm P, const __grid_constant__ Ha
 
 // =========================================================================================
 // wgrad:  dw[co][tap*Cin + ci] += sum_pixels gy'[p][co] * act(x)[p + shift(tap)][ci]
+//
+// Per 128-pixel tile the gather warps (1) load the x halo tile and the gy' tile into shared memory with
+// their prologues applied once, (2) expand the halo into an explicit im2col operand
+// [tap*C8 + c8][128 rows][8] with shared->shared 16-byte copies (the nine shifted views of the halo),
+// so that (3) one tcgen05.mma per 16-pixel K step covers ALL taps at once (N = 9*Cin, split into
+// groups of <= 256 columns) instead of one MMA per tap.  Both operands are MN-major views (K = pixels).
+// The accumulator D[co][tap*Cin+ci] lives in TMEM across all tiles of the CTA and is flushed once with
+// vector reductions (red.global.add.v4.f32).
 // =========================================================================================
-constexpr int kWStages = 3;
+DTF_DEVINL uint4 lds16(uint32_t addr) {
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
+    return v;
+}
+DTF_DEVINL void red_add_v4(float* p, float a, float b, float c, float d) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
 
 template <int C8>
 __global__ void __launch_bounds__(kHThreads, 1)
@@ -339,18 +354,23 @@ conv3x3_wgrad_kernel(const __grid_constant__ DtfConvWgrad P, const __grid_consta
     extern __shared__ __align__(1024) uint8_t smem[];
     HaloHeader* hdr = reinterpret_cast<HaloHeader*>(smem);
     SmemConsts* cst = reinterpret_cast<SmemConsts*>(smem + 1024);
-    uint8_t* smem_a = smem + G.smem_a_off;       // per stage: [gy: gy_c8 chunks x 128 rows][x halo: c8 chunks x rows]
+    uint8_t* smem_a = smem + G.smem_a_off;   // per stage: [gy: gy_c8 chunks][im2col: ntaps*C8 chunks][halo: C8 x rows]
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     constexpr int Cin = C8 * 8;
     const int tap_begin = blockIdx.y == 0 ? 0 : G.ntaps;
     const int ntaps = blockIdx.y == 0 ? G.ntaps : 9 - G.ntaps;
-    const uint32_t acc_cols = tmem_cols_pow2(ntaps * Cin);
+    const int nchunks = ntaps * C8;                          // im2col chunks (8 columns each)
+    const int ngroups = (nchunks + 31) / 32;                 // MMA column groups of <= 256
+    const int gchunks = (((nchunks + ngroups - 1) / ngroups) + 1) & ~1;
+    const uint32_t acc_cols = tmem_cols_pow2(nchunks * 8);
     const int my_tiles = (G.num_tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
     const int gy_bytes = G.gy_c8 * kChunkBytes;
+    const int im_bytes = G.tap0;                             // byte size of the im2col area (set by the host)
+    const int nstages = G.sign;                              // number of operand stages (set by the host)
 
     if (tid == 0) {
-        for (int i = 0; i < kWStages; ++i) {
+        for (int i = 0; i < kHStages; ++i) {
             mbar_init(smem_u32(&hdr->full[i]), kHGatherThreads);
             mbar_init(smem_u32(&hdr->empty[i]), 1);
         }
@@ -366,31 +386,23 @@ conv3x3_wgrad_kernel(const __grid_constant__ DtfConvWgrad P, const __grid_consta
     const uint32_t tmem_base = hdr->tmem_base;
 
     if (warp == kMmaWarp) {
-        if (my_tiles > 0) {          // warp-uniform loop, one elected lane issues (see conv3x3_kernel)
-            const uint32_t idesc = umma_idesc_bf16(kTileM, Cin, true, true);
-            // hoisted descriptor arithmetic (units of 16 bytes): x view shift per tap, 16 rows per K step
-            uint32_t x_off[9];
-#pragma unroll
-            for (int t = 0; t < 9; ++t) {
-                const int tap = tap_begin + t;
-                const int dy = tap / 3 - 1, dx = tap % 3 - 1;
-                x_off[t] = static_cast<uint32_t>((1 + dy) * G.Wp + (1 + dx));
-            }
+        if (my_tiles > 0) {          // warp-uniform loop, one elected lane issues
             const uint64_t gdesc0 = umma_desc(smem_u32(smem_a), 128, kChunkBytes);
-            const uint64_t xdesc0 = umma_desc(smem_u32(smem_a) + gy_bytes, 128, G.cs);
+            const uint64_t idesc0 = umma_desc(smem_u32(smem_a) + gy_bytes, 128, kChunkBytes);
             const uint32_t stage_units = static_cast<uint32_t>(G.stage_bytes >> 4);
             for (int it = 0; it < my_tiles; ++it) {
-                const uint32_t st = it % kWStages;
-                mbar_wait(smem_u32(&hdr->full[st]), (it / kWStages) & 1, 0x41);
+                const uint32_t st = it % nstages;
+                mbar_wait(smem_u32(&hdr->full[st]), (it / nstages) & 1, 0x41);
                 tc_fence_after_sync();
                 if (elect_one()) {
+                    for (int grp = 0; grp < ngroups; ++grp) {
+                        const int c0 = grp * gchunks;
+                        const int nc = min(gchunks, nchunks - c0);
+                        const uint32_t idesc = umma_idesc_bf16(kTileM, nc * 8, true, true);
 #pragma unroll
-                    for (int ks = 0; ks < kTileM / 16; ++ks) {
-                        const uint64_t adesc = gdesc0 + st * stage_units + ks * 16;
-                        const uint64_t xdesc = xdesc0 + st * stage_units + ks * 16;
-#pragma unroll
-                        for (int t = 0; t < 9; ++t)
-                            if (t < ntaps) umma_bf16(tmem_base + t * Cin, adesc, xdesc + x_off[t], idesc, (it | ks) != 0);
+                        for (int ks = 0; ks < kTileM / 16; ++ks)
+                            umma_bf16(tmem_base + c0 * 8, gdesc0 + st * stage_units + ks * 16,
+                                      idesc0 + st * stage_units + c0 * (kChunkBytes >> 4) + ks * 16, idesc, (it | ks) != 0);
                     }
                     umma_commit(smem_u32(&hdr->empty[st]));
                 }
@@ -404,26 +416,39 @@ conv3x3_wgrad_kernel(const __grid_constant__ DtfConvWgrad P, const __grid_consta
         const bool has_row = g < G.rows;
         for (int it = 0; it < my_tiles; ++it) {
             const int tile = blockIdx.x + it * gridDim.x;
-            const uint32_t st = it % kWStages;
+            const uint32_t st = it % nstages;
             const uint32_t gy_base = smem_u32(smem_a) + st * G.stage_bytes;
+            const uint32_t im_base = gy_base + gy_bytes;
+            const uint32_t halo_base = im_base + im_bytes;
             RowJob jx, jg;
             uint32_t pix = 0;
             jx.valid = has_row && decode_virtual(tile * kTileM - G.Wp - 1 + g, G, pix);
             jx.src = P.x.src + static_cast<size_t>(pix) * Cin;
             jx.src2 = nullptr;
-            jx.dst = gy_base + gy_bytes + g * 16;
+            jx.dst = halo_base + g * 16;
             uint32_t pix2 = 0;
             jg.valid = g < kTileM && decode_virtual(tile * kTileM + g, G, pix2);
             jg.src = P.gy.src + static_cast<size_t>(pix2) * P.Cout;
             jg.src2 = P.gy.src2 ? P.gy.src2 + static_cast<size_t>(pix2) * P.Cout : nullptr;
             jg.dst = gy_base + g * 16;
-            mbar_wait(smem_u32(&hdr->empty[st]), ((it / kWStages) & 1) ^ 1, 0x42);
+            mbar_wait(smem_u32(&hdr->empty[st]), ((it / nstages) & 1) ^ 1, 0x42);
             if (has_row) { RowJob j1[1] = {jx}; gather_rows<C8, 1>(j1, 1, G.cs, P.x.mode, cst->p0, cst->p1, cst->p2); }
             if (g < kTileM) {
                 RowJob j1[1] = {jg};
                 if (G.gy_c8 == 2) gather_rows<2, 1>(j1, 1, kChunkBytes, P.gy.mode, cst->q0, cst->q1, cst->q2);
                 else if (G.gy_c8 == 4) gather_rows<4, 1>(j1, 1, kChunkBytes, P.gy.mode, cst->q0, cst->q1, cst->q2);
                 else gather_rows<8, 1>(j1, 1, kChunkBytes, P.gy.mode, cst->q0, cst->q1, cst->q2);
+            }
+            named_bar_sync(2, kHGatherThreads);          // the halo tile is complete (gather warps only)
+            // im2col expansion: chunk (tap, c8), row r  <-  halo chunk c8, row r + shift(tap)
+            const int items = nchunks * kTileM;
+            for (int i = g; i < items; i += kHGatherThreads) {
+                const int r = i & (kTileM - 1);
+                const int j = i >> 7;
+                const int t = j / C8, c8 = j - t * C8;
+                const int tap = tap_begin + t;
+                const int shift = (tap / 3) * G.Wp + (tap % 3);          // (1+dy)*Wp + (1+dx)
+                sts16(im_base + j * kChunkBytes + r * 16, lds16(halo_base + c8 * G.cs + (r + shift) * 16));
             }
             fence_proxy_async_smem();
             mbar_arrive(smem_u32(&hdr->full[st]));
@@ -433,15 +458,14 @@ conv3x3_wgrad_kernel(const __grid_constant__ DtfConvWgrad P, const __grid_consta
         tc_fence_after_sync();
         const int co = warp * 32 + lane;
         const int ktot = 9 * Cin;
-        for (int t = 0; t < ntaps; ++t) {
-            const int kbase = (tap_begin + t) * Cin;
-            for (int cg = 0; cg < Cin; cg += 16) {
-                float v[16];
-                tmem_ld16(tmem_base + ((warp * 32u) << 16) + t * Cin + cg, v);
-                if (co < P.Cout) {
+        const int kbase = tap_begin * Cin;
+        for (int cg = 0; cg < nchunks * 8; cg += 16) {
+            float v[16];
+            tmem_ld16(tmem_base + ((warp * 32u) << 16) + cg, v);
+            if (co < P.Cout) {
+                float* dst = P.dw + static_cast<size_t>(co) * ktot + kbase + cg;
 #pragma unroll
-                    for (int i = 0; i < 16; ++i) atomicAdd(P.dw + static_cast<size_t>(co) * ktot + kbase + cg + i, v[i]);
-                }
+                for (int i = 0; i < 16; i += 4) red_add_v4(dst + i, v[i], v[i + 1], v[i + 2], v[i + 3]);
             }
         }
     }
@@ -548,16 +572,24 @@ extern "C" int dtf_conv3x3_wgrad_try(const DtfConvWgrad* p, cudaStream_t stream)
     G.sign = 1;
     G.gy_c8 = p->Cout / 8;
     // TMEM holds ntaps * Cin fp32 columns (<= 512): split the nine taps over blockIdx.y when needed
-    const int max_taps = 512 / x.C;
-    const int ny = max_taps >= 9 ? 1 : 2;
+    const int tmem_taps = 512 / x.C;
+    const int ny = tmem_taps >= 9 ? 1 : 2;
     G.ntaps = ny == 1 ? 9 : 5;
     if (ny == 2 && (9 - G.ntaps) * x.C > 512) return 0;
-    G.stage_bytes = (G.gy_c8 * kChunkBytes + G.c8 * G.cs + 127) & ~127;
+    // stage = [gy tile][im2col: max taps per CTA * C8 chunks][halo tile]
+    const int max_taps = G.ntaps > 9 - G.ntaps ? G.ntaps : 9 - G.ntaps;
+    G.tap0 = max_taps * G.c8 * kChunkBytes;                              // im2col area bytes
+    G.stage_bytes = (G.gy_c8 * kChunkBytes + G.tap0 + G.c8 * G.cs + 127) & ~127;
     const int header = 1024 + static_cast<int>(sizeof(SmemConsts));
     G.smem_a_off = (header + 1023) & ~1023;
-    // the gy operand descriptor spans 16 channel chunks (32 KB) from its base: keep slack at the end
-    const int smem_bytes = G.smem_a_off + kWStages * G.stage_bytes + 16 * kChunkBytes;
-    if (smem_bytes > 227 * 1024) return 0;
+    // the gy operand descriptor spans 16 channel chunks (32 KB) from its base: the im2col area that follows
+    // it inside the stage is at least that large whenever gy_c8 + chunks >= 16, else keep slack at the end
+    const int slack = 16 * kChunkBytes;
+    int stages = (227 * 1024 - G.smem_a_off - slack) / G.stage_bytes;
+    if (stages > kHStages) stages = kHStages;
+    if (stages < 1) return 0;
+    G.sign = stages;                                                      // (re-used field: operand stages)
+    const int smem_bytes = G.smem_a_off + stages * G.stage_bytes + slack;
     if (G.c8 != 2 && G.c8 != 4 && G.c8 != 8) return 0;
     if (G.gy_c8 != 2 && G.gy_c8 != 4 && G.gy_c8 != 8) return 0;
     static int attr_set = 0;

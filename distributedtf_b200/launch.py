@@ -47,7 +47,7 @@ def _fault_hook(cfg: RunConfig) -> Optional[Callable[[Any, int], None]]:
     return hook
 
 
-def model_kwargs(cfg: RunConfig) -> Dict[str, Any]:
+def model_kwargs(cfg: RunConfig, dp_group=None, dp_rank: int = 0) -> Dict[str, Any]:
     if cfg.target_model == "toy":
         return {}
     kw = dict(engine=cfg.engine, dtype=cfg.dtype, synthetic=cfg.synthetic, data_dir=cfg.data_dir,
@@ -55,6 +55,8 @@ def model_kwargs(cfg: RunConfig) -> Dict[str, Any]:
               resume=cfg.resume)
     if cfg.target_model == "cifar10":
         kw.update(resnet_size=cfg.resnet_size, resnet_version=cfg.resnet_version)
+    if cfg.dp_size > 1:
+        kw.update(dp_group=dp_group, dp_rank=dp_rank, dp_size=cfg.dp_size)
     return kw
 
 
@@ -88,11 +90,11 @@ def run_master(cfg: RunConfig, comm) -> Dict[str, Any]:
             "pop_size": cluster.pop_size}
 
 
-def run_worker(cfg: RunConfig, comm) -> TrainingWorker:
+def run_worker(cfg: RunConfig, comm, dp_group=None, mirror=None) -> TrainingWorker:
     worker = TrainingWorker(comm, cfg.master_rank, get_model_class(cfg.target_model),
                             save_base_dir=os.path.join(cfg.save_root, "model_"),
-                            verbose=cfg.verbose, model_kwargs=model_kwargs(cfg),
-                            fault_hook=_fault_hook(cfg))
+                            verbose=cfg.verbose, model_kwargs=model_kwargs(cfg, dp_group, 0),
+                            fault_hook=_fault_hook(cfg), mirror=mirror)
     if cfg.seed is not None:
         random.seed(cfg.seed * 1000003 + comm.Get_rank())
     worker.main_loop()
@@ -123,7 +125,7 @@ def run_local(cfg: RunConfig) -> Dict[str, Any]:
     return result
 
 
-def _init_worker_group(cfg: RunConfig, rank: int, group_port: int) -> None:
+def _init_worker_group(cfg: RunConfig, rank: int, group_port: int, dp_rank: int = 0):
     """Process group among the WORKERS (the master is not in it).  It carries the 64-byte CUDA IPC
     handles of the members' symmetric buffers (device exploit paths) and, for the library baselines,
     the NCCL / gloo state transfers.  Never used for control messages."""
@@ -135,20 +137,50 @@ def _init_worker_group(cfg: RunConfig, rank: int, group_port: int) -> None:
         idx = int(os.environ.get("DTF_LOCAL_GPU", "0")) % torch.cuda.device_count()
         torch.cuda.set_device(idx)
         kw["device_id"] = torch.device("cuda", idx)
-    os.environ["RANK"] = str(rank - 1)
-    dist.init_process_group(backend, init_method=f"tcp://{cfg.master_addr}:{group_port}", rank=rank - 1,
-                            world_size=cfg.workers, **kw)
+    world_rank = (rank - 1) * cfg.dp_size + dp_rank
+    os.environ["RANK"] = str(world_rank)
+    dist.init_process_group(backend, init_method=f"tcp://{cfg.master_addr}:{group_port}", rank=world_rank,
+                            world_size=cfg.workers * cfg.dp_size, **kw)
+    dp_group = None
+    if cfg.dp_size > 1:            # one sub-group per member group; every process creates all of them
+        for w in range(cfg.workers):
+            grp = dist.new_group(list(range(w * cfg.dp_size, (w + 1) * cfg.dp_size)))
+            if w == rank - 1:
+                dp_group = grp
+    return dp_group
 
 
-def _tcp_worker_entry(cfg: RunConfig, rank: int, gpu: Optional[int], group_port: int = 0) -> None:
+def _tcp_worker_entry(cfg: RunConfig, rank: int, gpu: Optional[int], group_port: int = 0, dp_rank: int = 0) -> None:
     from .parallel.tcp import TcpWorkerComm
     if gpu is not None:
         os.environ["DTF_LOCAL_GPU"] = str(gpu)
-    if group_port and cfg.workers > 1 and cfg.exploit_path != "file":
-        _init_worker_group(cfg, rank, group_port)
+    dp_group = None
+    if group_port and (cfg.workers * cfg.dp_size) > 1 and (cfg.exploit_path != "file" or cfg.dp_size > 1):
+        dp_group = _init_worker_group(cfg, rank, group_port, dp_rank)
+    if dp_rank > 0:                # follower replica: driven by its group leader, never by the master
+        import torch.distributed as dist
+        from .worker import FollowerWorker
+        leader = (rank - 1) * cfg.dp_size
+
+        def recv_from_leader():
+            box = [None]
+            dist.broadcast_object_list(box, src=leader, group=dp_group)
+            return box[0]
+        FollowerWorker(recv_from_leader, get_model_class(cfg.target_model),
+                       save_base_dir=os.path.join(cfg.save_root, f".replica{dp_rank}_model_"), verbose=False,
+                       model_kwargs=model_kwargs(cfg, dp_group, dp_rank)).main_loop()
+        dist.destroy_process_group()
+        return
+    mirror = None
+    if cfg.dp_size > 1:
+        import torch.distributed as dist
+        me = (rank - 1) * cfg.dp_size
+
+        def mirror(msg):
+            dist.broadcast_object_list([msg], src=me, group=dp_group)
     comm = TcpWorkerComm(cfg.master_addr, cfg.master_port, rank, cfg.workers + 1)
     try:
-        run_worker(cfg, comm)
+        run_worker(cfg, comm, dp_group=dp_group, mirror=mirror)
     finally:
         comm.close()
         try:
@@ -178,10 +210,12 @@ def spawn_tcp(cfg: RunConfig, gpus: Optional[List[int]] = None) -> Dict[str, Any
             pass
     procs = []
     for r in range(1, cfg.workers + 1):
-        gpu = gpus[(r - 1) % len(gpus)] if gpus else None
-        p = ctx.Process(target=_tcp_worker_entry, args=(cfg, r, gpu, group_port), daemon=True)
-        p.start()
-        procs.append(p)
+        for d in range(cfg.dp_size):
+            slot = (r - 1) * cfg.dp_size + d
+            gpu = gpus[slot % len(gpus)] if gpus else None
+            p = ctx.Process(target=_tcp_worker_entry, args=(cfg, r, gpu, group_port, d), daemon=True)
+            p.start()
+            procs.append(p)
     try:
         master.wait_for_workers()
         result = run_master(cfg, master)

@@ -51,9 +51,10 @@ class GpuMember(ModelBase):
                  data_dir: str = "./datasets", max_train_steps: Optional[int] = None,
                  eval_batches: Optional[int] = None, resume: bool = False,
                  synthetic_mode: str = "random", device: Optional[torch.device] = None,
-                 hooks: Optional[List[Any]] = None, **_):
+                 hooks: Optional[List[Any]] = None, dp_group=None, dp_rank: int = 0, dp_size: int = 1, **_):
         super().__init__(cluster_id, hparams, save_base_dir)
         self.device = device or pick_device()
+        self.dp_group, self.dp_rank, self.dp_size = dp_group, int(dp_rank), int(dp_size)
         self._engine_requested = engine
         self.engine_kind = resolve_engine(engine, self.device)
         self.dtype = dtype
@@ -124,6 +125,9 @@ class GpuMember(ModelBase):
             t0 = time.time()
             for _ in range(steps):
                 idx = self._train_iter.next_indices()
+                if self.dp_size > 1:          # same permutation on every replica; each takes its slice
+                    per = bs // self.dp_size
+                    idx = idx[self.dp_rank * per: (self.dp_rank + 1) * per]
                 x = self.preprocess(self.train_set.images[idx], True)
                 loss = self.engine.train_step(x, self.train_set.labels[idx])
                 if self.hooks:                    # values stay on the device unless a hook logs them
@@ -133,6 +137,8 @@ class GpuMember(ModelBase):
                         h.after_step(self._global_step, vals)
         dt = max(self.device_times["train"], 1e-9)
         self.last_images_per_sec = steps * bs / max(time.time() - t0, 1e-9)
+        if self.dp_size > 1 and bs % self.dp_size:
+            raise ValueError(f"batch_size {bs} is not a multiple of dp_size {self.dp_size}")
         return steps
 
     def evaluate(self) -> float:
@@ -157,8 +163,14 @@ class GpuMember(ModelBase):
         (state | snapshot 0 | snapshot 1 | control) and lists it in the symmetric directory."""
         from ..parallel import exploit, symm
         self.symm = exploit.MemberBuffer(state_bytes, self.device)
-        symm.DIRECTORY.register_local(self.cluster_id, self.symm.buf, int(os.environ.get("RANK", "0")))
+        symm.DIRECTORY.register_local(self.directory_key(self.cluster_id), self.symm.buf,
+                                      int(os.environ.get("RANK", "0")))
         return self.symm.alloc_state(state_bytes)
+
+    def directory_key(self, cluster_id: int) -> int:
+        """Symmetric-directory key of replica ``dp_rank`` of member ``cluster_id`` (a loser replica pulls
+        from the winner replica with the same data-parallel rank)."""
+        return int(cluster_id) * 8 + self.dp_rank
 
     def train(self, num_epoch: int, total_epochs: int) -> None:
         self.flush_exploit()

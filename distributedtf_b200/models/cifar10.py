@@ -46,7 +46,8 @@ class Cifar10Model(GpuMember):
         if self.engine_kind == "native":
             from .resnet_native import NativeResNetEngine
             return NativeResNetEngine(self.net_cfg, self.hparams, self.device, seed=seed, dtype=self.dtype,
-                                      arena_alloc=self.make_symmetric_alloc)
+                                      arena_alloc=self.make_symmetric_alloc,
+                                      dp_group=self.dp_group if self.dp_size > 1 else None)
         from .engine_eager import EagerEngine
         cfg = self.net_cfg
         init = resnet.init_params(cfg, self.hparams.get("initializer", "None"), seed)

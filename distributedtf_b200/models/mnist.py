@@ -45,7 +45,8 @@ class MNISTModel(GpuMember):
                 self.engine_kind = "eager"          # `auto`: the MNIST kernels are not built into this version
             else:
                 return NativeMnistEngine(self.hparams, self.device, seed=seed, dtype=self.dtype,
-                                         arena_alloc=self.make_symmetric_alloc)
+                                         arena_alloc=self.make_symmetric_alloc,
+                                         dp_group=self.dp_group if self.dp_size > 1 else None)
         from .engine_eager import EagerEngine
         init = mnist_net.init_params(self.hparams.get("initializer", "None"), seed)
         return EagerEngine(mnist_net.param_specs(), mnist_net.forward, init, self.hparams, self.device,

@@ -26,7 +26,7 @@ class TrainingWorker:
     def __init__(self, comm, master_rank: int, target_model_class: Callable[..., Any], *,
                  save_base_dir: str = "./savedata/model_", verbose: bool = True,
                  model_kwargs: Optional[Dict[str, Any]] = None,
-                 fault_hook: Optional[Callable[[Any, int], None]] = None):
+                 fault_hook: Optional[Callable[[Any, int], None]] = None, mirror=None):
         self.worker_graphs: List[Any] = []
         self.is_expolore_only = False          # (sic) reference attribute name
         self.rank = comm.Get_rank()
@@ -37,6 +37,7 @@ class TrainingWorker:
         self.verbose = verbose
         self.model_kwargs = dict(model_kwargs or {})
         self.fault_hook = fault_hook           # test hook: f(member, round) may raise / poison
+        self.mirror = mirror                   # DP group leader: callable(msg) that forwards to the followers
         self.train_time = 0.0
         self.explore_time = 0.0
         self.exploit_time = 0.0
@@ -56,6 +57,9 @@ class TrainingWorker:
         while True:
             data = self.comm.recv(source=self.master_rank)
             inst = validate(data)
+            if self.mirror is not None and inst in (WorkerInstruction.ADD_GRAPHS, WorkerInstruction.TRAIN,
+                                                    WorkerInstruction.SET, WorkerInstruction.EXIT):
+                self.mirror(data)
             if inst == WorkerInstruction.ADD_GRAPHS:
                 self.is_expolore_only = data[3]
                 self.add_graphs(data[1], data[2])
@@ -120,6 +124,8 @@ class TrainingWorker:
                 self.worker_graphs.remove(g)
         self.rounds_seen += 1
         self.train_time += time.time() - t0
+        if self.mirror is not None:            # the followers drop exactly what the leader dropped
+            self.mirror(("DROP", [g.cluster_id for g in failed]))
 
     def get_all_values(self) -> List[List[Any]]:
         return [g.get_values() for g in self.worker_graphs]
@@ -142,11 +148,15 @@ class TrainingWorker:
 
     def explore_necessary_graphs(self) -> None:
         t0 = time.time()
+        explored: Dict[int, Any] = {}
         for g in self.worker_graphs:
             if g.need_explore or self.is_expolore_only:
                 self._say("[{}]Exploring graph {}".format(self.rank, g.cluster_id))
                 g.perturb_hparams()
                 g.need_explore = False
+                explored[g.cluster_id] = g.hparams
+        if self.mirror is not None:            # followers adopt the leader's draw instead of drawing their own
+            self.mirror(("HPARAMS", explored))
         self.explore_time += time.time() - t0
 
     def profiling_info(self) -> List[Any]:
@@ -162,3 +172,49 @@ class TrainingWorker:
             close = getattr(g, "close", None)
             if close is not None:
                 close()
+
+
+class FollowerWorker(TrainingWorker):
+    """A non-leader replica of a data-parallel member group.  It never talks to the master: the leader
+    mirrors ADD_GRAPHS / TRAIN / SET / EXIT plus two internal records — ("HPARAMS", {id: hparams}) after an
+    explore so every replica holds the same draw, and ("DROP", [ids]) after a round."""
+
+    def __init__(self, recv_from_leader: Callable[[], Any], target_model_class, **kw):
+        class _NoComm:
+            def Get_rank(self):
+                return -1
+        super().__init__(_NoComm(), 0, target_model_class, **kw)
+        self._recv = recv_from_leader
+
+    def main_loop(self) -> None:
+        import copy
+        while True:
+            data = self._recv()
+            tag = data[0]
+            if tag == WorkerInstruction.ADD_GRAPHS:
+                self.is_expolore_only = data[3]
+                self.add_graphs(data[1], data[2])
+            elif tag == WorkerInstruction.TRAIN:
+                for g in self.worker_graphs:
+                    try:
+                        g.train(data[1], data[2])
+                    except Exception:
+                        if self.verbose:
+                            traceback.print_exc()
+            elif tag == WorkerInstruction.SET:
+                self.set_values(data[1])
+            elif tag == "HPARAMS":
+                for g in self.worker_graphs:
+                    if g.cluster_id in data[1]:
+                        g.hparams = copy.deepcopy(data[1][g.cluster_id])
+                        g.need_explore = False
+                        if getattr(g, "_pending_exploit", None) is not None:
+                            g.flush_exploit()
+                        else:
+                            g.on_hparams_changed()
+            elif tag == "DROP":
+                for g in [g for g in self.worker_graphs if g.cluster_id in data[1]]:
+                    self.worker_graphs.remove(g)
+            elif tag == WorkerInstruction.EXIT:
+                self.shutdown()
+                break
