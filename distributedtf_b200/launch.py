@@ -181,6 +181,11 @@ def _tcp_worker_entry(cfg: RunConfig, rank: int, gpu: Optional[int], group_port:
     comm = TcpWorkerComm(cfg.master_addr, cfg.master_port, rank, cfg.workers + 1)
     try:
         run_worker(cfg, comm, dp_group=dp_group, mirror=mirror)
+    except BaseException:
+        import traceback
+        print(f"[worker {rank}] fatal:", flush=True)
+        traceback.print_exc()
+        raise
     finally:
         comm.close()
         try:

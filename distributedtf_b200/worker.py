@@ -89,7 +89,8 @@ class TrainingWorker:
     def _exchange_symmetric_directory(self) -> None:
         """Publish the CUDA IPC handles of this worker's members to the other workers (device
         exploit paths).  A collective over the worker process group; skipped without one."""
-        bufs = {g.cluster_id: g.symm.buf for g in self.worker_graphs if getattr(g, "symm", None) is not None}
+        bufs = {(g.directory_key(g.cluster_id) if hasattr(g, "directory_key") else g.cluster_id): g.symm.buf
+                for g in self.worker_graphs if getattr(g, "symm", None) is not None}
         try:
             import torch.distributed as dist
             if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:

@@ -78,3 +78,18 @@ def test_cifar_population_two_gpus_tcp_p2p(tmp_path):
     # bottom member and top member live on different workers for pop 4 / 2 workers at least once
     assert (tmp_path / "savedata" / "best_model.json").exists()
     assert out["profiling"]["device_exploit"] >= 0
+
+
+@pytest.mark.multigpu
+def test_cifar_dp2_member_group_two_gpus(tmp_path):
+    """BASELINE config 4 in miniature: one member sharded data-parallel over 2 GPUs, driven through the
+    real protocol (leader = worker endpoint, follower mirrors the leader's instructions); the gradient
+    exchange + update is the fused peer-memory kernel."""
+    from distributedtf_b200.launch import spawn_tcp
+    cfg = _cfg(tmp_path, workers=1, dp_size=2, transport="tcp", master_port=0, population_size=2, train_round=2,
+               exploit_path="p2p")
+    out = spawn_tcp(cfg, gpus=[0, 1])
+    assert out["pop_size"] == 2 and len(out["history"]) == 2
+    sd = tmp_path / "savedata"
+    assert (sd / "model_0" / "model.ckpt.data").exists() and (sd / "model_1" / "model.ckpt.data").exists()
+    assert 0 <= out["best"]["best_acc"] <= 1
