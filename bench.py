@@ -44,6 +44,8 @@ def parse():
     p.add_argument("--impl", choices=["native", "restated", "reference"], default="native")
     p.add_argument("--batch", type=int, default=BATCH)
     p.add_argument("--resnet-size", type=int, default=32)
+    p.add_argument("--dp-size", type=int, default=1, choices=[1, 2, 4],
+                   help="GPUs per member (BASELINE config 4: population N/D x data-parallel D)")
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--no-graphs", action="store_true")
     return p.parse_args()
@@ -166,7 +168,17 @@ def main():
 
     hp = default_cifar_hparam()
     hp["batch_size"] = args.batch
-    B = args.batch
+    D = args.dp_size
+    if world % D or args.batch % D:
+        raise SystemExit("--dp-size must divide both the GPU count and the batch")
+    members, member_id, dp_rank = world // D, rank // D, rank % D
+    B = args.batch // D                      # images per replica per step (global batch per member stays args.batch)
+    dp_group = None
+    if D > 1:
+        for m in range(members):
+            grp = dist.new_group(list(range(m * D, (m + 1) * D)))
+            if m == member_id:
+                dp_group = grp
 
     # ---- member under test ----
     from distributedtf_b200.models import resnet
@@ -182,7 +194,8 @@ def main():
             symm.DIRECTORY.register_local(rank, symm_buf.buf, rank)
             return symm_buf.alloc_state(n)
 
-        eng = NativeResNetEngine(cfg, hp, dev, seed=1234 + rank, use_graphs=not args.no_graphs, arena_alloc=alloc)
+        eng = NativeResNetEngine(cfg, hp, dev, seed=1234 + member_id, use_graphs=not args.no_graphs,
+                                 arena_alloc=alloc, dp_group=dp_group)
         if world > 1:
             symm.exchange_directory({rank: symm_buf.buf})
             for r in range(world):                       # map every peer's buffer now (cudaIpcOpenMemHandle is
@@ -190,6 +203,8 @@ def main():
     else:
         from distributedtf_b200.models.engine_eager import EagerEngine
         from distributedtf_b200.utils.data import cifar_preprocess_torch
+        if D > 1:
+            raise SystemExit("--dp-size > 1 is implemented for --impl native")
         init = resnet.init_params(cfg, hp["initializer"], 1234 + rank)
         eng = EagerEngine(resnet.param_specs(cfg), lambda p, x, t: resnet.forward(cfg, p, x, t), init, hp, dev,
                           compute_dtype=torch.bfloat16, lr_schedule=True)
@@ -240,15 +255,15 @@ def main():
 
     def pbt_event():
         nonlocal exploit_ms
-        if world == 1:
+        if members == 1:
             return
         loss = eng.last_loss.reshape(1).float().clone()
         allv = [torch.zeros_like(loss) for _ in range(world)]
         dist.all_gather(allv, loss)                                  # scores (device, NCCL plumbing)
-        scores = [-float(v.item()) for v in allv]                    # higher = better
-        order = sorted(range(world), key=lambda r: scores[r])
-        n = -(-world // 4)
-        pairs = [(order[world - n + i], order[i]) for i in range(n)]  # (winner, loser)
+        scores = [-float(allv[m * D].item()) for m in range(members)]   # higher = better; one score per member
+        order = sorted(range(members), key=lambda m: scores[m])
+        n = -(-members // 4)
+        pairs = [(order[members - n + i], order[i]) for i in range(n)]  # (winner, loser) member ids
         rnd = pbt_round[0]
         if args.impl == "native":
             exploit.copy_kernel(symm_buf.state_ptr + symm_buf.snapshot_offset(rnd), symm_buf.state_ptr,
@@ -260,11 +275,12 @@ def main():
             if winner == loser:
                 continue
             if args.impl == "native":
-                if rank == loser:
+                if member_id == loser:
+                    import random as _random
                     new_hp = dict(hp, opt_case=dict(hp["opt_case"]))
-                    explore.perturb_hparams(new_hp)
-                    new_hp["batch_size"] = B                          # keep the benchmark's batch fixed
-                    src = symm.DIRECTORY.pointer(winner) + symm_buf.snapshot_offset(rnd)
+                    explore.perturb_hparams(new_hp, _random.Random(1000 * rnd + loser))   # same draw on every replica
+                    new_hp["batch_size"] = args.batch                 # keep the benchmark's batch fixed
+                    src = symm.DIRECTORY.pointer(winner * D + dp_rank) + symm_buf.snapshot_offset(rnd)
                     exploit.copy_kernel(symm_buf.state_ptr, src, symm_buf.state_bytes,
                                         hp_offset=eng.hp_state_offset, new_hp=eng.hparams_struct(new_hp),
                                         zero=eng.round_cells, done_flag_ptr=symm_buf.control_ptr, epoch=rnd + 1,
@@ -273,7 +289,7 @@ def main():
                     eng.after_state_replaced()
             else:
                 flat = eng.flat.detach()
-                if rank == winner:
+                if rank == winner:     # (restated arm: D == 1, member id == rank)
                     for t in (flat, eng.slot0, eng.slot1):
                         dist.send(t, dst=loser)
                 elif rank == loser:
@@ -311,14 +327,14 @@ def main():
         return float(ms.item()), wall, sampler.stop()
 
     dev_ms, wall, clocks = timed(step_resident, args.steps, True)
-    value = world * B * args.steps / (dev_ms / 1e3)
+    value = members * args.batch * args.steps / (dev_ms / 1e3)
 
     e2e = None
     if not args.no_e2e:
         for i in range(3):
             step_e2e(i)
         e2e_ms, _, _ = timed(step_e2e, args.steps, False)
-        e2e = {"value": world * B * args.steps / (e2e_ms / 1e3), "unit": "images/s",
+        e2e = {"value": members * args.batch * args.steps / (e2e_ms / 1e3), "unit": "images/s",
                "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
                "ms_per_step": e2e_ms / args.steps}
 
@@ -331,10 +347,11 @@ def main():
             "data": "synthetic uint8 CIFAR-10-shaped images (random), random labels, random-init weights",
             "impl": args.impl,
             "config": {"model": f"CIFAR-10 ResNet-{args.resnet_size} v2 (resnet_model, 6n+2)",
-                       "global_batch": B * world, "per_gpu_batch": B, "seq_len": None,
-                       "parallelism": f"population {world} x 1 GPU (pbt{world})", "optimizer": "Momentum 0.9 + l2 2e-4",
+                       "global_batch": args.batch * members, "per_gpu_batch": B, "seq_len": None,
+                       "parallelism": f"population {members} x {D} GPU" + (f" (pbt{members})" if D == 1 else f" (pbt{members} x dp{D}, fused all-reduce+update)"),
+                       "optimizer": "Momentum 0.9 + l2 2e-4",
                        "l2": "inputs larger than L2: each step gathers a fresh batch from a 153.6 MB resident dataset",
-                       "pbt_event_in_timed_region": world > 1, "cuda_graphs": not args.no_graphs},
+                       "pbt_event_in_timed_region": members > 1, "cuda_graphs": not args.no_graphs},
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
             "launches_per_step": getattr(eng, "launches_per_step", 0), "exploit_ms": exploit_ms,
             "state_bytes": getattr(eng, "state_bytes", lambda: None)(), "wall_s": wall,
