@@ -135,12 +135,12 @@ DTF_DEVINL void gather_rows(const RowJob (&jobs)[NJ], int njobs, int cs, int mod
 // =========================================================================================
 // forward / dgrad
 // =========================================================================================
+// The body is a device function parameterised by (cta, ncta) so that the same code runs as a
+// stand-alone kernel and as one half of the fused backward launch (dgrad CTAs + wgrad CTAs).
 template <int C8>
-__global__ void __launch_bounds__(kHThreads, 1)
-conv3x3_kernel(const __grid_constant__ DtfConvGemm P, const __grid_constant__ HaloGeom G) {
+DTF_DEVINL void conv3x3_body(const DtfConvGemm& P, const HaloGeom& G, const int cta, const int ncta, uint8_t* smem) {
     constexpr int kPairs = C8 / 2;            // UMMA K steps (16 channels) per tap
     constexpr int kBatch = C8 == 8 ? 1 : 2;   // tiles whose loads are in flight together per gather thread
-    extern __shared__ __align__(1024) uint8_t smem[];
     HaloHeader* hdr = reinterpret_cast<HaloHeader*>(smem);
     SmemConsts* cst = reinterpret_cast<SmemConsts*>(smem + 1024);
     uint8_t* smem_b = smem + G.smem_b_off;
@@ -149,7 +149,7 @@ conv3x3_kernel(const __grid_constant__ DtfConvGemm P, const __grid_constant__ Ha
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int N = P.N;
     const uint32_t acc_cols = tmem_cols_pow2(2 * N);
-    const int my_tiles = (G.num_tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
+    const int my_tiles = (G.num_tiles - cta + ncta - 1) / ncta;
 
     if (tid == 0) {
         for (int i = 0; i < kHStages; ++i) {
@@ -169,7 +169,7 @@ conv3x3_kernel(const __grid_constant__ DtfConvGemm P, const __grid_constant__ Ha
             bn_fwd_consts(P.epi_bn, c, cst->e_scale[c], cst->e_shift[c], cst->e_mean[c], cst->e_invstd[c]);
     for (int c = tid; c < 2 * kMaxC; c += kHThreads) (&cst->bins[0][0])[c] = 0.f;
     if (warp == kMmaWarp) tmem_alloc(smem_u32(&hdr->tmem_base), acc_cols);
-    if (blockIdx.x == 0 && P.a.update_running && P.a.mode == DTF_PRO_BN_RELU && !P.a.bn.use_running)
+    if (cta == 0 && P.a.update_running && P.a.mode == DTF_PRO_BN_RELU && !P.a.bn.use_running)
         update_running(P.a.bn, tid, kHThreads);
     if (tid == 0) DTF_MARK(0);
     tc_fence_before_sync();
@@ -238,7 +238,7 @@ conv3x3_kernel(const __grid_constant__ DtfConvGemm P, const __grid_constant__ Ha
             for (int u = 0; u < kBatch; ++u) {
                 jobs[u].valid = false;
                 if (u < nt) {
-                    const int tile = blockIdx.x + (it + u) * gridDim.x;
+                    const int tile = cta + (it + u) * ncta;
                     uint32_t pix = 0;
                     const bool ok = has_row && decode_virtual(tile * kTileM - G.Wp - 1 + g, G, pix);
                     jobs[u].valid = ok;
@@ -271,7 +271,7 @@ conv3x3_kernel(const __grid_constant__ DtfConvGemm P, const __grid_constant__ Ha
         uint32_t pix_nxt = 0;
         bool valid_nxt = false;
         if (my_tiles > 0) {
-            valid_nxt = decode_virtual(static_cast<int>(blockIdx.x) * kTileM + warp * 32 + lane, G, pix_nxt);
+            valid_nxt = decode_virtual(cta * kTileM + warp * 32 + lane, G, pix_nxt);
             if (aux_src != nullptr && valid_nxt) {
 #pragma unroll
                 for (int j = 0; j < C8; ++j) aux_nxt[j] = ldg16(aux_src + static_cast<size_t>(pix_nxt) * N + j * 8);
@@ -285,7 +285,7 @@ conv3x3_kernel(const __grid_constant__ DtfConvGemm P, const __grid_constant__ Ha
 #pragma unroll
             for (int j = 0; j < C8; ++j) aux[j] = aux_nxt[j];
             if (it + 1 < my_tiles) {
-                const int tile_n = blockIdx.x + (it + 1) * gridDim.x;
+                const int tile_n = cta + (it + 1) * ncta;
                 valid_nxt = decode_virtual(tile_n * kTileM + warp * 32 + lane, G, pix_nxt);
                 if (aux_src != nullptr && valid_nxt) {
 #pragma unroll
@@ -328,6 +328,13 @@ conv3x3_kernel(const __grid_constant__ DtfConvGemm P, const __grid_constant__ Ha
     }
 }
 
+template <int C8>
+__global__ void __launch_bounds__(kHThreads, 1)
+conv3x3_kernel(const __grid_constant__ DtfConvGemm P, const __grid_constant__ HaloGeom G) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    conv3x3_body<C8>(P, G, static_cast<int>(blockIdx.x), static_cast<int>(gridDim.x), smem);
+}
+
 // =========================================================================================
 // wgrad:  dw[co][tap*Cin + ci] += sum_pixels gy'[p][co] * act(x)[p + shift(tap)][ci]
 //
@@ -349,22 +356,21 @@ DTF_DEVINL void red_add_v4(float* p, float a, float b, float c, float d) {
 }
 
 template <int C8>
-__global__ void __launch_bounds__(kHThreads, 1)
-conv3x3_wgrad_kernel(const __grid_constant__ DtfConvWgrad P, const __grid_constant__ HaloGeom G) {
-    extern __shared__ __align__(1024) uint8_t smem[];
+DTF_DEVINL void conv3x3_wgrad_body(const DtfConvWgrad& P, const HaloGeom& G, const int cta, const int ncta,
+                                   const int cta_y, uint8_t* smem) {
     HaloHeader* hdr = reinterpret_cast<HaloHeader*>(smem);
     SmemConsts* cst = reinterpret_cast<SmemConsts*>(smem + 1024);
     uint8_t* smem_a = smem + G.smem_a_off;   // per stage: [gy: gy_c8 chunks][im2col: ntaps*C8 chunks][halo: C8 x rows]
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     constexpr int Cin = C8 * 8;
-    const int tap_begin = blockIdx.y == 0 ? 0 : G.ntaps;
-    const int ntaps = blockIdx.y == 0 ? G.ntaps : 9 - G.ntaps;
+    const int tap_begin = cta_y == 0 ? 0 : G.ntaps;
+    const int ntaps = cta_y == 0 ? G.ntaps : 9 - G.ntaps;
     const int nchunks = ntaps * C8;                          // im2col chunks (8 columns each)
     const int ngroups = (nchunks + 31) / 32;                 // MMA column groups of <= 256
     const int gchunks = (((nchunks + ngroups - 1) / ngroups) + 1) & ~1;
     const uint32_t acc_cols = tmem_cols_pow2(nchunks * 8);
-    const int my_tiles = (G.num_tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
+    const int my_tiles = (G.num_tiles - cta + ncta - 1) / ncta;
     const int gy_bytes = G.gy_c8 * kChunkBytes;
     const int im_bytes = G.tap0;                             // byte size of the im2col area (set by the host)
     const int nstages = G.sign;                              // number of operand stages (set by the host)
@@ -415,7 +421,7 @@ conv3x3_wgrad_kernel(const __grid_constant__ DtfConvWgrad P, const __grid_consta
         const int g = tid - (kMmaWarp + 1) * 32;
         const bool has_row = g < G.rows;
         for (int it = 0; it < my_tiles; ++it) {
-            const int tile = blockIdx.x + it * gridDim.x;
+            const int tile = cta + it * ncta;
             const uint32_t st = it % nstages;
             const uint32_t gy_base = smem_u32(smem_a) + st * G.stage_bytes;
             const uint32_t im_base = gy_base + gy_bytes;
@@ -477,6 +483,32 @@ conv3x3_wgrad_kernel(const __grid_constant__ DtfConvWgrad P, const __grid_consta
     }
 }
 
+template <int C8>
+__global__ void __launch_bounds__(kHThreads, 1)
+conv3x3_wgrad_kernel(const __grid_constant__ DtfConvWgrad P, const __grid_constant__ HaloGeom G) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    conv3x3_wgrad_body<C8>(P, G, static_cast<int>(blockIdx.x), static_cast<int>(gridDim.x), static_cast<int>(blockIdx.y), smem);
+}
+
+// One launch for the two backward GEMMs of a 3x3 convolution: CTAs [0, n_dgrad) compute the input
+// gradient, the remaining CTAs the weight gradient (linear index -> (x, y) of the wgrad grid).  The two
+// are independent (both only read gy'), so sharing a launch removes one launch latency per layer and
+// lets the two halves fill the SMs that either alone would leave idle in the small-tile stages.
+template <int C8>
+__global__ void __launch_bounds__(kHThreads, 1)
+conv3x3_bwd_fused_kernel(const __grid_constant__ DtfConvGemm Pd, const __grid_constant__ HaloGeom Gd,
+                         const __grid_constant__ DtfConvWgrad Pw, const __grid_constant__ HaloGeom Gw,
+                         const int n_dgrad, const int wgrad_gx) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    const int b = static_cast<int>(blockIdx.x);
+    if (b < n_dgrad) {
+        conv3x3_body<C8>(Pd, Gd, b, n_dgrad, smem);
+    } else {
+        const int w = b - n_dgrad;
+        conv3x3_wgrad_body<C8>(Pw, Gw, w % wgrad_gx, wgrad_gx, w / wgrad_gx, smem);
+    }
+}
+
 }  // namespace dtf
 
 // =========================================================================================
@@ -527,8 +559,32 @@ static bool fill_geom(dtf::HaloGeom* G, int NB, int H, int W, int C) {
     return true;
 }
 
+static int prep_fwd(const DtfConvGemm* p, dtf::HaloGeom* Gout, int* smem_out);
+static int prep_wgrad(const DtfConvWgrad* p, dtf::HaloGeom* Gout, int* smem_out, int* ny_out);
+
 // returns 1 if launched, 0 if not eligible, <0 on error
 extern "C" int dtf_conv3x3_try(const DtfConvGemm* p, cudaStream_t stream) {
+    using namespace dtf;
+    HaloGeom G{};
+    int smem_bytes = 0;
+    const int ok = prep_fwd(p, &G, &smem_bytes);
+    if (ok != 1) return ok;
+    static int attr_set = 0;
+    if (!attr_set) {
+        if (cudaFuncSetAttribute(conv3x3_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess ||
+            cudaFuncSetAttribute(conv3x3_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess ||
+            cudaFuncSetAttribute(conv3x3_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess)
+            return DTF_ERR_CUDA;
+        attr_set = 1;
+    }
+    const int grid = G.num_tiles < halo_sms() ? G.num_tiles : halo_sms();
+    if (G.c8 == 2) conv3x3_kernel<2><<<grid, kHThreads, smem_bytes, stream>>>(*p, G);
+    else if (G.c8 == 4) conv3x3_kernel<4><<<grid, kHThreads, smem_bytes, stream>>>(*p, G);
+    else conv3x3_kernel<8><<<grid, kHThreads, smem_bytes, stream>>>(*p, G);
+    return cudaGetLastError() == cudaSuccess ? 1 : DTF_ERR_CUDA;
+}
+
+static int prep_fwd(const DtfConvGemm* p, dtf::HaloGeom* Gout, int* smem_out) {
     using namespace dtf;
     const DtfGather& a = p->a;
     if (halo_disabled()) return 0;
@@ -545,22 +601,36 @@ extern "C" int dtf_conv3x3_try(const DtfConvGemm* p, cudaStream_t stream) {
     const int smem_bytes = G.smem_a_off + kHStages * G.stage_bytes + 256;
     if (smem_bytes > 227 * 1024) return 0;
     if (G.c8 != 2 && G.c8 != 4 && G.c8 != 8) return 0;
-    static int attr_set = 0;
-    if (!attr_set) {
-        if (cudaFuncSetAttribute(conv3x3_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess ||
-            cudaFuncSetAttribute(conv3x3_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess ||
-            cudaFuncSetAttribute(conv3x3_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess)
-            return DTF_ERR_CUDA;
-        attr_set = 1;
-    }
-    const int grid = G.num_tiles < halo_sms() ? G.num_tiles : halo_sms();
-    if (G.c8 == 2) conv3x3_kernel<2><<<grid, kHThreads, smem_bytes, stream>>>(*p, G);
-    else if (G.c8 == 4) conv3x3_kernel<4><<<grid, kHThreads, smem_bytes, stream>>>(*p, G);
-    else conv3x3_kernel<8><<<grid, kHThreads, smem_bytes, stream>>>(*p, G);
-    return cudaGetLastError() == cudaSuccess ? 1 : DTF_ERR_CUDA;
+    *Gout = G;
+    *smem_out = smem_bytes;
+    return 1;
 }
 
 extern "C" int dtf_conv3x3_wgrad_try(const DtfConvWgrad* p, cudaStream_t stream) {
+    using namespace dtf;
+    HaloGeom G{};
+    int smem_bytes = 0, ny = 1;
+    const int ok = prep_wgrad(p, &G, &smem_bytes, &ny);
+    if (ok != 1) return ok;
+    static int attr_set = 0;
+    if (!attr_set) {
+        if (cudaFuncSetAttribute(conv3x3_wgrad_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess ||
+            cudaFuncSetAttribute(conv3x3_wgrad_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess ||
+            cudaFuncSetAttribute(conv3x3_wgrad_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess)
+            return DTF_ERR_CUDA;
+        attr_set = 1;
+    }
+    int gx = halo_sms() / ny;
+    if (gx > G.num_tiles) gx = G.num_tiles;
+    if (gx < 1) gx = 1;
+    dim3 grid(gx, ny);
+    if (G.c8 == 2) conv3x3_wgrad_kernel<2><<<grid, kHThreads, smem_bytes, stream>>>(*p, G);
+    else if (G.c8 == 4) conv3x3_wgrad_kernel<4><<<grid, kHThreads, smem_bytes, stream>>>(*p, G);
+    else conv3x3_wgrad_kernel<8><<<grid, kHThreads, smem_bytes, stream>>>(*p, G);
+    return cudaGetLastError() == cudaSuccess ? 1 : DTF_ERR_CUDA;
+}
+
+static int prep_wgrad(const DtfConvWgrad* p, dtf::HaloGeom* Gout, int* smem_out, int* ny_out) {
     using namespace dtf;
     const DtfGather& x = p->x;
     if (halo_disabled()) return 0;
@@ -592,29 +662,45 @@ extern "C" int dtf_conv3x3_wgrad_try(const DtfConvWgrad* p, cudaStream_t stream)
     const int smem_bytes = G.smem_a_off + stages * G.stage_bytes + slack;
     if (G.c8 != 2 && G.c8 != 4 && G.c8 != 8) return 0;
     if (G.gy_c8 != 2 && G.gy_c8 != 4 && G.gy_c8 != 8) return 0;
+    *Gout = G;
+    *smem_out = smem_bytes;
+    *ny_out = ny;
+    return 1;
+}
+
+// Fused backward launch (dgrad + wgrad of one 3x3 / stride-1 convolution).  Both parameter blocks must
+// already be prepared by dtf_conv_gemm / dtf_conv_wgrad's front halves (kchunks etc.), which is what
+// dtf_conv_bwd_fused in conv_sm100.cu does.  Returns 1 if launched, 0 if not eligible.
+extern "C" int dtf_conv3x3_bwd_fused_try(const DtfConvGemm* pd, const DtfConvWgrad* pw, cudaStream_t stream) {
+    using namespace dtf;
+    HaloGeom Gd{}, Gw{};
+    int smem_d = 0, smem_w = 0, ny = 1;
+    int ok = prep_fwd(pd, &Gd, &smem_d);
+    if (ok != 1) return ok;
+    ok = prep_wgrad(pw, &Gw, &smem_w, &ny);
+    if (ok != 1) return ok;
+    if (Gd.c8 != Gw.c8) return 0;
     static int attr_set = 0;
     if (!attr_set) {
-        if (cudaFuncSetAttribute(conv3x3_wgrad_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess ||
-            cudaFuncSetAttribute(conv3x3_wgrad_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess ||
-            cudaFuncSetAttribute(conv3x3_wgrad_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess)
+        if (cudaFuncSetAttribute(conv3x3_bwd_fused_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess ||
+            cudaFuncSetAttribute(conv3x3_bwd_fused_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess ||
+            cudaFuncSetAttribute(conv3x3_bwd_fused_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess)
             return DTF_ERR_CUDA;
         attr_set = 1;
     }
-    int gx = halo_sms() / ny;
-    if (gx > G.num_tiles) gx = G.num_tiles;
+    const int sms = halo_sms();
+    // split the SMs between the two halves in proportion to their MMA work (dgrad: 9*C8/2 small MMAs per
+    // tile, wgrad: 8 wide MMAs per tile per column group), never more CTAs than tiles
+    int n_d = (sms * 45) / 100;
+    if (n_d > Gd.num_tiles) n_d = Gd.num_tiles;
+    if (n_d < 1) n_d = 1;
+    int gx = (sms - n_d) / ny;
+    if (gx > Gw.num_tiles) gx = Gw.num_tiles;
     if (gx < 1) gx = 1;
-    dim3 grid(gx, ny);
-    if (G.c8 == 2) conv3x3_wgrad_kernel<2><<<grid, kHThreads, smem_bytes, stream>>>(*p, G);
-    else if (G.c8 == 4) conv3x3_wgrad_kernel<4><<<grid, kHThreads, smem_bytes, stream>>>(*p, G);
-    else conv3x3_wgrad_kernel<8><<<grid, kHThreads, smem_bytes, stream>>>(*p, G);
+    const int grid = n_d + gx * ny;
+    const int smem_bytes = smem_d > smem_w ? smem_d : smem_w;
+    if (Gd.c8 == 2) conv3x3_bwd_fused_kernel<2><<<grid, kHThreads, smem_bytes, stream>>>(*pd, Gd, *pw, Gw, n_d, gx);
+    else if (Gd.c8 == 4) conv3x3_bwd_fused_kernel<4><<<grid, kHThreads, smem_bytes, stream>>>(*pd, Gd, *pw, Gw, n_d, gx);
+    else conv3x3_bwd_fused_kernel<8><<<grid, kHThreads, smem_bytes, stream>>>(*pd, Gd, *pw, Gw, n_d, gx);
     return cudaGetLastError() == cudaSuccess ? 1 : DTF_ERR_CUDA;
-}
-
-extern "C" int dtf_debug_timeline(unsigned long long* out64) {
-#ifdef DTF_TIMING
-    return cudaMemcpyFromSymbol(out64, dtf::g_timeline, 64 * sizeof(unsigned long long)) == cudaSuccess ? DTF_OK : DTF_ERR_CUDA;
-#else
-    (void)out64;
-    return DTF_ERR_ARG;
-#endif
 }

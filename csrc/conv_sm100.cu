@@ -405,3 +405,27 @@ extern "C" int dtf_conv_wgrad(DtfConvWgrad* p, cudaStream_t stream) {
     conv_wgrad_kernel<<<grid, kThreads, smem_bytes, stream>>>(*p);
     return cudaGetLastError() == cudaSuccess ? DTF_OK : DTF_ERR_CUDA;
 }
+
+// Backward of one convolution in a single launch when both halves are 3x3 / stride 1 (see
+// conv3x3_bwd_fused_kernel); otherwise two launches (dgrad, then wgrad).
+extern "C" int dtf_conv3x3_bwd_fused_try(const DtfConvGemm* pd, const DtfConvWgrad* pw, cudaStream_t stream);
+
+extern "C" int dtf_conv_bwd(DtfConvGemm* dgrad, DtfConvWgrad* wgrad, cudaStream_t stream) {
+    using namespace dtf;
+    int rc = prep_gather(&dgrad->a);
+    if (rc != DTF_OK) return rc;
+    dgrad->kchunks = (dgrad->a.kchunks_real + 1) & ~1;
+    rc = prep_gather(&wgrad->x);
+    if (rc != DTF_OK) return rc;
+    wgrad->gy.KH = wgrad->gy.KW = 1; wgrad->gy.stride = 1; wgrad->gy.pad = 0; wgrad->gy.transposed = 0;
+    wgrad->gy.Hs = wgrad->Ho; wgrad->gy.Ws = wgrad->Wo; wgrad->gy.C = wgrad->Cout;
+    rc = prep_gather(&wgrad->gy);
+    if (rc != DTF_OK) return rc;
+    wgrad->kchunks_real = wgrad->x.kchunks_real;
+    wgrad->kchunks = (wgrad->kchunks_real + 1) & ~1;
+    rc = dtf_conv3x3_bwd_fused_try(dgrad, wgrad, stream);
+    if (rc != 0) return rc > 0 ? DTF_OK : rc;
+    rc = dtf_conv_wgrad(wgrad, stream);
+    if (rc != DTF_OK) return rc;
+    return dtf_conv_gemm(dgrad, stream);
+}

@@ -34,6 +34,7 @@ class RunConfig:
     dp_size: int = 1                      # GPUs per member (1 | 2 | 4)
     # --- data plane ---
     exploit_path: str = "file"            # file | p2p | nccl | host
+    scoreboard: bool = False              # eval scores reach the master through the device score board
     engine: str = "auto"                  # native (sm_100a kernels) | eager (torch oracle) | auto
     dtype: str = "bf16"                   # bf16 | fp32 | fp16 (compute dtype of the native engine)
     # --- model / data ---
@@ -97,6 +98,7 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--master-port", type=int, default=29611)
     p.add_argument("--dp-size", type=int, choices=[1, 2, 4], default=1)
     p.add_argument("--exploit-path", choices=["file", "p2p", "nccl", "host"], default="file")
+    p.add_argument("--scoreboard", action="store_true", help="rank by the device-side score board")
     p.add_argument("--engine", choices=["auto", "native", "eager"], default="auto")
     p.add_argument("--dtype", choices=["bf16", "fp32", "fp16"], default="bf16")
     p.add_argument("--resnet-size", type=int, default=32)

@@ -57,10 +57,24 @@ def model_kwargs(cfg: RunConfig, dp_group=None, dp_rank: int = 0) -> Dict[str, A
         kw.update(resnet_size=cfg.resnet_size, resnet_version=cfg.resnet_version)
     if cfg.dp_size > 1:
         kw.update(dp_group=dp_group, dp_rank=dp_rank, dp_size=cfg.dp_size)
+    if getattr(cfg, "_board_info", None):
+        kw["scoreboard"] = cfg._board_info
     return kw
 
 
-def run_master(cfg: RunConfig, comm) -> Dict[str, Any]:
+def make_scoreboard(cfg: RunConfig, same_process: bool):
+    """Device score board owned by the master.  Returns (board, info-for-members)."""
+    if not cfg.scoreboard or cfg.target_model == "toy":
+        return None, None
+    import torch
+    if not torch.cuda.is_available():
+        return None, None
+    from .parallel.scoreboard import ScoreBoard
+    board = ScoreBoard(max(cfg.population_size, 1), torch.device("cuda", 0))
+    return board, ({"ptr": board.ptr} if same_process else {"handle": board.handle()})
+
+
+def run_master(cfg: RunConfig, comm, board=None) -> Dict[str, Any]:
     if cfg.clean:
         shutil.rmtree(cfg.save_root, ignore_errors=True)
     os.makedirs(cfg.save_root, exist_ok=True)
@@ -74,7 +88,7 @@ def run_master(cfg: RunConfig, comm) -> Dict[str, Any]:
                          do_exploit=cfg.do_exploit, do_explore=cfg.do_explore,
                          save_root=cfg.save_root, exploit_path=cfg.exploit_path, rng=rng,
                          recv_timeout=cfg.recv_timeout, initial_hparams=initial,
-                         verbose=cfg.verbose)
+                         scoreboard=board, verbose=cfg.verbose)
     cluster.dump_all_models_to_json(os.path.join(cfg.save_root, "initial_hp.json"))
     elapsed = cluster.train(cfg.train_round)
     if cfg.results_file:
@@ -104,6 +118,8 @@ def run_worker(cfg: RunConfig, comm, dp_group=None, mirror=None) -> TrainingWork
 def run_local(cfg: RunConfig) -> Dict[str, Any]:
     """Master + workers as threads over the in-process fabric."""
     fabric = LocalFabric(cfg.workers + 1)
+    board, info = make_scoreboard(cfg, same_process=True)
+    object.__setattr__(cfg, "_board_info", info)
     errors: List[BaseException] = []
 
     def guard(fn, *a):
@@ -117,7 +133,7 @@ def run_local(cfg: RunConfig) -> Dict[str, Any]:
                for r in range(1, cfg.workers + 1)]
     for t in threads:
         t.start()
-    result = run_master(cfg, fabric.endpoint(0))
+    result = run_master(cfg, fabric.endpoint(0), board)
     for t in threads:
         t.join(timeout=60)
     if errors:
@@ -202,6 +218,8 @@ def spawn_tcp(cfg: RunConfig, gpus: Optional[List[int]] = None) -> Dict[str, Any
     ctx = mp.get_context("spawn")
     master = TcpMasterComm(cfg.master_addr, cfg.master_port, cfg.workers + 1)
     cfg = cfg.replace(master_port=master.port)
+    board, info = make_scoreboard(cfg, same_process=False)
+    object.__setattr__(cfg, "_board_info", info)
     import socket
     with socket.socket() as probe:                       # a free port for the workers' own process group
         probe.bind((cfg.master_addr, 0))
@@ -223,7 +241,7 @@ def spawn_tcp(cfg: RunConfig, gpus: Optional[List[int]] = None) -> Dict[str, Any
             procs.append(p)
     try:
         master.wait_for_workers()
-        result = run_master(cfg, master)
+        result = run_master(cfg, master, board)
     finally:
         for p in procs:
             p.join(timeout=60)

@@ -173,7 +173,9 @@ class PBTCluster:
         t0 = time.time()
         if self.scoreboard is not None:
             # Device-side scores win over the host copies when the board is live.
-            scores = self.scoreboard.read(self.rounds_done)
+            # every live member published (hits / seen, epoch = rounds trained) from its eval kernel stream
+            scores = self.scoreboard.read(self.rounds_done + 1, members=[rec[0] for rec in all_values])
+            self.board_scores = dict(scores)
             for rec in all_values:
                 if rec[0] in scores:
                     rec[1] = scores[rec[0]]

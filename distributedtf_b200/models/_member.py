@@ -51,7 +51,8 @@ class GpuMember(ModelBase):
                  data_dir: str = "./datasets", max_train_steps: Optional[int] = None,
                  eval_batches: Optional[int] = None, resume: bool = False,
                  synthetic_mode: str = "random", device: Optional[torch.device] = None,
-                 hooks: Optional[List[Any]] = None, dp_group=None, dp_rank: int = 0, dp_size: int = 1, **_):
+                 hooks: Optional[List[Any]] = None, dp_group=None, dp_rank: int = 0, dp_size: int = 1,
+                 scoreboard: Optional[Dict[str, Any]] = None, **_):
         super().__init__(cluster_id, hparams, save_base_dir)
         self.device = device or pick_device()
         self.dp_group, self.dp_rank, self.dp_size = dp_group, int(dp_rank), int(dp_size)
@@ -65,6 +66,8 @@ class GpuMember(ModelBase):
         self.eval_batches = eval_batches
         self.device_times: Dict[str, float] = {"train": 0.0, "eval": 0.0, "exploit": 0.0}
         self.hooks = list(hooks or [])          # utils.logs.hooks.Hook objects, called once per step
+        self._board = scoreboard                # {"ptr": local pointer} or {"handle": CUDA IPC handle of the board}
+        self._board_ptr: Optional[int] = None
         self.train_set, self.eval_set = self.build_datasets()
         self.symm = None                 # symmetric (peer-addressable) buffer, native engine on CUDA only
         self._pending_exploit: Optional[Dict[str, Any]] = None
@@ -156,7 +159,26 @@ class GpuMember(ModelBase):
         loss = self.engine.last_loss
         if loss is not None and not bool(torch.isfinite(loss)):
             return float("nan")
+        self._publish_score(correct, seen)
         return float(correct.item()) / max(seen, 1)
+
+    def _publish_score(self, correct: torch.Tensor, seen: int) -> None:
+        """Device path of the eval-score reduction: the hit counter goes to this member's slot of the
+        master-visible board (peer store + release of the round epoch), no host round trip involved."""
+        if self._board is None or self.device.type != "cuda" or self.dp_rank != 0:
+            return
+        from ..parallel import scoreboard as sb
+        if self._board_ptr is None:
+            if "ptr" in self._board:
+                self._board_ptr = int(self._board["ptr"])
+            else:
+                import ctypes as C
+                from ..ops import native
+                out = C.c_void_p()
+                native.check(native.lib().dtf_ipc_open_handle(self._board["handle"], C.byref(out)), "open score board")
+                self._board_ptr = int(out.value)
+        cell = correct.to(torch.int32).reshape(1).contiguous()
+        sb.publish(self._board_ptr, self.cluster_id, cell, seen, epoch=self.rounds_trained + 1, reset=False)
 
     def make_symmetric_alloc(self, state_bytes: int) -> torch.Tensor:
         """``arena_alloc`` callback for native engines: puts the member state in exportable memory

@@ -328,6 +328,29 @@ class NativeResNetEngine(NativeEngineBase):
                          epi_stats_out=self._bwd_stats(mask_bn), epi_accumulate=accumulate)
         self._count += 1
 
+    def _bwd_conv(self, c: ConvL, x_src, x_bn: Optional[BnL], gy_src, nb, out, *, mask_x, mask_bn: BnL,
+                  gy_bn: Optional[BnL] = None, gy_x=None) -> None:
+        """Weight gradient + input gradient of one conv.  3x3 / stride-1 layers go out as ONE launch
+        (dgrad CTAs and wgrad CTAs share the grid); the others as two."""
+        if not (c.k == 3 and c.stride == 1 and c.cin == c.cout):
+            self._wgrad(c, x_src, x_bn, gy_src, nb, gy_bn=gy_bn, gy_x=gy_x)
+            self._dgrad(c, gy_src, nb, out, mask_x=mask_x, mask_bn=mask_bn, gy_bn=gy_bn, gy_x=gy_x)
+            return
+        pro = native.PRO_BN_BWD if gy_bn else native.PRO_NONE
+        bn_gy = self._bn(gy_bn, nb, True) if gy_bn else None
+        bwd = self._bwd_stats(gy_bn) if gy_bn else None
+        gd = native.gather(gy_src, c.hout, c.hout, c.cout, KH=3, KW=3, stride=1, pad=1, transposed=True, mode=pro,
+                           bn=bn_gy, src2=gy_x, bwd_stats=bwd)
+        dgrad = native.conv_gemm_params(gd, self._wpk(c, dgrad=True), out, NB=nb, Ho=c.hin, Wo=c.hin, N=c.cin,
+                                        epi_mode=native.EPI_RELU_MASK, epi_x=mask_x,
+                                        epi_bn=self._bn(mask_bn, nb, True), epi_stats_out=self._bwd_stats(mask_bn))
+        gx = native.gather(x_src, c.hin, c.hin, c.cin, KH=3, KW=3, stride=1, pad=1,
+                           mode=native.PRO_BN_RELU if x_bn else native.PRO_NONE,
+                           bn=self._bn(x_bn, nb, True) if x_bn else None)
+        gg = native.gather(gy_src, c.hout, c.hout, c.cout, mode=pro, bn=bn_gy, src2=gy_x, bwd_stats=bwd)
+        native.conv_bwd(dgrad, gx, gg, self.grads[c.w_off:], NB=nb, Ho=c.hout, Wo=c.hout, Cout=c.cout)
+        self._count += 1
+
     def _backward(self, x_last, nb: int) -> None:
         t_f = self.tbuf[0]
         self._head(x_last, nb, True, t_out=t_f)
@@ -341,12 +364,10 @@ class NativeResNetEngine(NativeEngineBase):
             b, a = self.blocks[i], self.acts[i]
             x_in = self.acts[i - 1]["out"] if i > 0 else self.r0
             t2, t1 = self.tbuf[0], self.tbuf[1]
-            self._wgrad(b.conv2, a["c1"], b.bn2, g_out, nb)
-            self._dgrad(b.conv2, g_out, nb, t2, mask_x=a["c1"], mask_bn=b.bn2)
-            self._wgrad(b.conv1, x_in, b.bn1, t2, nb, gy_bn=b.bn2, gy_x=a["c1"])
+            self._bwd_conv(b.conv2, a["c1"], b.bn2, g_out, nb, t2, mask_x=a["c1"], mask_bn=b.bn2)
             if b.proj:
                 self._wgrad(b.proj, x_in, b.bn1, g_out, nb)
-            self._dgrad(b.conv1, t2, nb, t1, mask_x=x_in, mask_bn=b.bn1, gy_bn=b.bn2, gy_x=a["c1"])
+            self._bwd_conv(b.conv1, x_in, b.bn1, t2, nb, t1, mask_x=x_in, mask_bn=b.bn1, gy_bn=b.bn2, gy_x=a["c1"])
             if b.proj:
                 self._dgrad(b.proj, g_out, nb, t1, mask_x=x_in, mask_bn=b.bn1, accumulate=True)
             nxt = self.gbuf[cur ^ 1]

@@ -122,6 +122,8 @@ def _declare(l: C.CDLL) -> None:
     vp, i, ll, f = C.c_void_p, C.c_int, C.c_longlong, C.c_float
     l.dtf_conv_gemm.argtypes = [C.POINTER(ConvGemm), vp]
     l.dtf_conv_wgrad.argtypes = [C.POINTER(ConvWgrad), vp]
+    l.dtf_conv_bwd.argtypes = [C.POINTER(ConvGemm), C.POINTER(ConvWgrad), vp]
+    l.dtf_conv_bwd.restype = i
     l.dtf_bn_bwd_apply.argtypes = [vp, vp, vp, vp, C.POINTER(BnRef), vp, ll, i, vp]
     l.dtf_head.argtypes = [C.POINTER(Head), vp]
     l.dtf_pack_weights.argtypes = [vp, vp, vp, vp, i, vp]
@@ -195,6 +197,19 @@ def conv_gemm(a: Gather, wpk: torch.Tensor, out: torch.Tensor, *, NB: int, Ho: i
                  epi_bn if epi_bn is not None else BnRef(), ptr(epi_stats_out), epi_mode,
                  int(epi_accumulate), NB, Ho, Wo, N, 0, 0, 0, 0)
     check(lib().dtf_conv_gemm(C.byref(p), stream_ptr()), "dtf_conv_gemm")
+
+
+def conv_gemm_params(a: Gather, wpk, out, *, NB, Ho, Wo, N, epi_mode=EPI_STORE, epi_res=None, epi_bias=None, epi_x=None,
+                     epi_bn=None, epi_stats_out=None, epi_accumulate=False) -> ConvGemm:
+    return ConvGemm(a, ptr(wpk), ptr(out), ptr(epi_res), ptr(epi_bias), ptr(epi_x),
+                    epi_bn if epi_bn is not None else BnRef(), ptr(epi_stats_out), epi_mode,
+                    int(epi_accumulate), NB, Ho, Wo, N, 0, 0, 0, 0)
+
+
+def conv_bwd(dgrad: ConvGemm, x: Gather, gy: Gather, dw: torch.Tensor, *, NB: int, Ho: int, Wo: int, Cout: int) -> None:
+    """dgrad + wgrad of one convolution (one fused launch for 3x3 / stride-1 layers)."""
+    w = ConvWgrad(x, gy, ptr(dw), NB, Ho, Wo, Cout, 0, 0, 0, 0)
+    check(lib().dtf_conv_bwd(C.byref(dgrad), C.byref(w), stream_ptr()), "dtf_conv_bwd")
 
 
 def conv_wgrad(x: Gather, gy: Gather, dw: torch.Tensor, *, NB: int, Ho: int, Wo: int, Cout: int) -> None:

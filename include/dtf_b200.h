@@ -88,6 +88,9 @@ typedef struct {
 
 int dtf_conv_gemm(DtfConvGemm* p, cudaStream_t stream);
 int dtf_conv_wgrad(DtfConvWgrad* p, cudaStream_t stream);
+/* Backward of one convolution: input gradient + weight gradient.  One fused launch when the conv is
+ * 3x3 / stride 1 (the two GEMMs share the SMs of a single grid), otherwise wgrad then dgrad. */
+int dtf_conv_bwd(DtfConvGemm* dgrad, DtfConvWgrad* wgrad, cudaStream_t stream);
 
 /* ---- classifier head: final BN + ReLU + global average pool + dense + softmax-CE ----------
  * forward and backward in one launch, one CTA per image (resnet_model.py:537-552,

@@ -93,3 +93,26 @@ def test_cifar_dp2_member_group_two_gpus(tmp_path):
     sd = tmp_path / "savedata"
     assert (sd / "model_0" / "model.ckpt.data").exists() and (sd / "model_1" / "model.ckpt.data").exists()
     assert 0 <= out["best"]["best_acc"] <= 1
+
+
+def test_scoreboard_feeds_the_ranking(tmp_path):
+    """Eval hit counters reach the master through the device board; they equal the GET accuracies."""
+    from distributedtf_b200.config import RunConfig
+    from distributedtf_b200 import launch
+    cfg = _cfg(tmp_path, scoreboard=True, train_round=2)
+    seen = {}
+    orig = launch.run_master
+
+    def spy(cfg_, comm, board=None):
+        out = orig(cfg_, comm, board)
+        seen["board"] = board
+        return out
+    launch.run_master = spy
+    try:
+        out = launch.run_local(cfg)
+    finally:
+        launch.run_master = orig
+    assert seen["board"] is not None
+    scores = seen["board"].read(2, members=[0, 1, 2, 3], timeout=5)
+    assert set(scores) == {0, 1, 2, 3} and all(0 <= v <= 1 for v in scores.values())
+    assert out["pop_size"] == 4
