@@ -93,7 +93,7 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--exploit", dest="do_exploit", action=argparse.BooleanOptionalAction, default=True)
     p.add_argument("--explore", dest="do_explore", action=argparse.BooleanOptionalAction, default=True)
     p.add_argument("--workers", type=int, default=1)
-    p.add_argument("--transport", choices=["local", "tcp", "gloo", "mpi"], default="local")
+    p.add_argument("--transport", choices=["local", "tcp", "torchrun", "gloo", "mpi"], default="local")
     p.add_argument("--master-addr", default="127.0.0.1")
     p.add_argument("--master-port", type=int, default=29611)
     p.add_argument("--dp-size", type=int, choices=[1, 2, 4], default=1)

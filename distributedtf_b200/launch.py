@@ -59,6 +59,10 @@ def model_kwargs(cfg: RunConfig, dp_group=None, dp_rank: int = 0) -> Dict[str, A
         kw.update(dp_group=dp_group, dp_rank=dp_rank, dp_size=cfg.dp_size)
     if getattr(cfg, "_board_info", None):
         kw["scoreboard"] = cfg._board_info
+    if cfg.hooks and cfg.verbose:
+        from .utils.logs import hooks as _hooks
+        kw["hooks"] = _hooks.get_train_hooks(cfg.hooks, model_dir=cfg.save_root, batch_size=128)
+    kw["benchmark"] = (cfg.benchmark_logger_type, cfg.benchmark_log_dir)
     return kw
 
 
@@ -251,8 +255,50 @@ def spawn_tcp(cfg: RunConfig, gpus: Optional[List[int]] = None) -> Dict[str, Any
     return result
 
 
+def run_torchrun(cfg: RunConfig) -> Optional[Dict[str, Any]]:
+    """One process per GPU under ``python -m torch.distributed.run``: every rank is a worker endpoint
+    (rank + 1); rank 0 additionally hosts the master in a thread.  Control messages go over the TCP
+    star on MASTER_PORT + 1; the NCCL/gloo process group carries the symmetric-memory handles."""
+    import torch
+    import torch.distributed as dist
+    from .parallel.tcp import TcpMasterComm, TcpWorkerComm
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    local = int(os.environ.get("LOCAL_RANK", rank))
+    addr = os.environ.get("MASTER_ADDR", "127.0.0.1")
+    port = int(os.environ.get("MASTER_PORT", "29500")) + 1
+    os.environ["DTF_LOCAL_GPU"] = str(local)
+    if torch.cuda.is_available():
+        torch.cuda.set_device(local % torch.cuda.device_count())
+    if not dist.is_initialized():
+        dist.init_process_group("cpu:gloo,cuda:nccl" if torch.cuda.is_available() else "gloo")
+    cfg = cfg.replace(workers=world, master_addr=addr, master_port=port)
+    result: Dict[str, Any] = {}
+    master_thread = None
+    if rank == 0:
+        master = TcpMasterComm(addr, port, world + 1)
+        board, info = make_scoreboard(cfg, same_process=False)
+        object.__setattr__(cfg, "_board_info", info)
+
+        def _m():
+            master.wait_for_workers()
+            result.update(run_master(cfg, master, board))
+        master_thread = threading.Thread(target=_m, name="dtf-master", daemon=True)
+        master_thread.start()
+    comm = TcpWorkerComm(addr, port, rank + 1, world + 1)
+    try:
+        run_worker(cfg, comm)
+    finally:
+        comm.close()
+    if master_thread is not None:
+        master_thread.join(timeout=120)
+    dist.barrier()
+    return result if rank == 0 else None
+
+
 def run(cfg: RunConfig) -> Optional[Dict[str, Any]]:
     cfg.validate()
+    if "RANK" in os.environ and "WORLD_SIZE" in os.environ and cfg.transport in ("tcp", "torchrun"):
+        return run_torchrun(cfg)
     if cfg.transport == "local":
         return run_local(cfg)
     if cfg.transport == "tcp":

@@ -52,7 +52,7 @@ class GpuMember(ModelBase):
                  eval_batches: Optional[int] = None, resume: bool = False,
                  synthetic_mode: str = "random", device: Optional[torch.device] = None,
                  hooks: Optional[List[Any]] = None, dp_group=None, dp_rank: int = 0, dp_size: int = 1,
-                 scoreboard: Optional[Dict[str, Any]] = None, **_):
+                 scoreboard: Optional[Dict[str, Any]] = None, benchmark=None, **_):
         super().__init__(cluster_id, hparams, save_base_dir)
         self.device = device or pick_device()
         self.dp_group, self.dp_rank, self.dp_size = dp_group, int(dp_rank), int(dp_size)
@@ -66,6 +66,13 @@ class GpuMember(ModelBase):
         self.eval_batches = eval_batches
         self.device_times: Dict[str, float] = {"train": 0.0, "eval": 0.0, "exploit": 0.0}
         self.hooks = list(hooks or [])          # utils.logs.hooks.Hook objects, called once per step
+        self._bench_logger = None
+        if benchmark and benchmark[0] == "BenchmarkFileLogger" and benchmark[1]:
+            from ..utils.logs import logger as _logger
+            self._bench_logger = _logger.BenchmarkFileLogger(os.path.join(benchmark[1], f"model_{cluster_id}"))
+            self._bench_logger.log_run_info(type(self).__name__, "synthetic" if synthetic else "real",
+                                            {"batch_size": int(hparams["batch_size"]), "dtype": dtype,
+                                             "engine": engine, "synthetic_data": bool(synthetic)})
         self._board = scoreboard                # {"ptr": local pointer} or {"handle": CUDA IPC handle of the board}
         self._board_ptr: Optional[int] = None
         self.train_set, self.eval_set = self.build_datasets()
@@ -201,6 +208,8 @@ class GpuMember(ModelBase):
             self.train_one_epoch()
             self.accuracy = self.evaluate()
             rows.append(self.csv_row(self.epoch_index_for_csv(e), self.accuracy))
+            if self._bench_logger is not None:      # resnet_run_loop.py:466 log_evaluation_result
+                self._bench_logger.log_evaluation_result({"accuracy": self.accuracy, "global_step": self.engine.step})
         self.bump_epochs(num_epoch)
         if math.isnan(self.accuracy):
             return                      # the worker drops the member; nothing to persist

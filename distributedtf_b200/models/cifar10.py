@@ -45,15 +45,30 @@ class Cifar10Model(GpuMember):
         seed = 7919 * (self.cluster_id + 1)
         if self.engine_kind == "native":
             from .resnet_native import NativeResNetEngine
-            return NativeResNetEngine(self.net_cfg, self.hparams, self.device, seed=seed, dtype=self.dtype,
-                                      arena_alloc=self.make_symmetric_alloc,
-                                      dp_group=self.dp_group if self.dp_size > 1 else None)
+            try:
+                return NativeResNetEngine(self.net_cfg, self.hparams, self.device, seed=seed, dtype=self.dtype,
+                                          arena_alloc=self.make_symmetric_alloc,
+                                          dp_group=self.dp_group if self.dp_size > 1 else None)
+            except NotImplementedError:
+                # ResNet v1 / bottleneck / fp16 are served by the eager engine; an explicit request for
+                # the native engine is an error, `auto` degrades.
+                if self._engine_requested == "native":
+                    raise
+                self.engine_kind, self.symm = "eager", None
         from .engine_eager import EagerEngine
         cfg = self.net_cfg
         init = resnet.init_params(cfg, self.hparams.get("initializer", "None"), seed)
         return EagerEngine(resnet.param_specs(cfg), lambda p, x, t: resnet.forward(cfg, p, x, t), init,
                            self.hparams, self.device, compute_dtype=_DTYPES[self.dtype]
                            if self.device.type == "cuda" else torch.float32, lr_schedule=True)
+
+    def export(self, export_dir: str) -> str:
+        """Inference bundle (reference: ``classifier.export_savedmodel``, resnet_run_loop.py:510-514)."""
+        import dataclasses
+        from ..utils.export import export as _export
+        named = self.engine.export_named() if hasattr(self.engine, "export_named") else \
+            {k: v.detach() for k, v in self.engine.params.items()}
+        return _export.export_inference_bundle(export_dir, named, "resnet", dataclasses.asdict(self.net_cfg), [32, 32, 3])
 
     def preprocess(self, images_u8: torch.Tensor, training: bool) -> torch.Tensor:
         pre = getattr(self.engine, "preprocess", None)
