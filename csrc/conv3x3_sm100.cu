@@ -272,11 +272,11 @@ DTF_DEVINL void conv3x3_body(const DtfConvGemm& P, const HaloGeom& G, const int 
         bool valid_nxt = false;
         if (my_tiles > 0) {
             valid_nxt = decode_virtual(cta * kTileM + warp * 32 + lane, G, pix_nxt);
-            if (aux_src != nullptr && valid_nxt) {
-#pragma unroll
-                for (int j = 0; j < C8; ++j) aux_nxt[j] = ldg16(aux_src + static_cast<size_t>(pix_nxt) * N + j * 8);
-            }
         }
+#pragma unroll
+        for (int j = 0; j < C8; ++j)
+            aux_nxt[j] = (aux_src != nullptr && valid_nxt) ? ldg16(aux_src + static_cast<size_t>(pix_nxt) * N + j * 8)
+                                                           : make_uint4(0, 0, 0, 0);
         for (int it = 0; it < my_tiles; ++it) {
             const uint32_t a = it & 1;
             const bool valid = valid_nxt;
@@ -287,10 +287,11 @@ DTF_DEVINL void conv3x3_body(const DtfConvGemm& P, const HaloGeom& G, const int 
             if (it + 1 < my_tiles) {
                 const int tile_n = cta + (it + 1) * ncta;
                 valid_nxt = decode_virtual(tile_n * kTileM + warp * 32 + lane, G, pix_nxt);
-                if (aux_src != nullptr && valid_nxt) {
 #pragma unroll
-                    for (int j = 0; j < C8; ++j) aux_nxt[j] = ldg16(aux_src + static_cast<size_t>(pix_nxt) * N + j * 8);
-                }
+                for (int j = 0; j < C8; ++j)
+                    aux_nxt[j] = (aux_src != nullptr && valid_nxt)
+                                     ? ldg16(aux_src + static_cast<size_t>(pix_nxt) * N + j * 8)
+                                     : make_uint4(0, 0, 0, 0);
             }
             mbar_wait(smem_u32(&hdr->acc_full[a]), (it >> 1) & 1, 0x35);
             tc_fence_after_sync();
@@ -299,7 +300,7 @@ DTF_DEVINL void conv3x3_body(const DtfConvGemm& P, const HaloGeom& G, const int 
             for (int cgi = 0; cgi < kGroups; ++cgi) {
                 float v[16];
                 tmem_ld16(tmem_base + ((warp * 32u) << 16) + a * N + cgi * 16, v);
-                epilogue_group(P, cst, v, valid, obase, cgi * 16, lane, aux_src ? &aux[2 * cgi] : nullptr,
+                epilogue_group(P, cst, v, valid, obase, cgi * 16, lane, &aux[2 * cgi],
                                kRegStats ? &acc1[cgi * 16] : nullptr, kRegStats ? &acc2[cgi * 16] : nullptr);
             }
             tc_fence_before_sync();

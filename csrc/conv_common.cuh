@@ -98,12 +98,22 @@ DTF_DEVINL RowCoord row_coord(int m, int M, int Ho, int Wo) {
     return r;
 }
 
-// Returns the 16-byte chunk (8 consecutive channels) of the im2col row for global chunk jg.
-DTF_DEVINL uint4 gather16(const DtfGather& g, const int8_t* tap_dy, const int8_t* tap_dx,
-                          const float* p0, const float* p1, const float* p2,
-                          const RowCoord& rc, int jg) {
-    const uint4 zero = make_uint4(0, 0, 0, 0);
-    if (!rc.valid || jg >= g.kchunks_real) return zero;
+// The gather of one 16-byte chunk (8 consecutive channels) of an im2col row is split in two so that a
+// thread can put the loads of several chunks in flight before it consumes the first one.
+struct GatherLoad {
+    uint4 raw, x;     // source chunk; second source (BN backward) when the mode needs it
+    int cb;           // first channel of the chunk
+    bool ok;          // false: padding / out-of-range chunk, stays zero
+};
+
+template <bool TWO>
+DTF_DEVINL void gather_issue(const DtfGather& g, const int8_t* tap_dy, const int8_t* tap_dx,
+                             const RowCoord& rc, int jg, GatherLoad& L) {
+    L.raw = make_uint4(0, 0, 0, 0);
+    L.x = L.raw;
+    L.ok = false;
+    L.cb = 0;
+    if (!rc.valid || jg >= g.kchunks_real) return;
     const int tap = jg >> g.cpt_shift;
     const int c8 = jg & ((1 << g.cpt_shift) - 1);
     int sy, sx;
@@ -114,27 +124,73 @@ DTF_DEVINL uint4 gather16(const DtfGather& g, const int8_t* tap_dy, const int8_t
         // gradient gather of a strided conv: source = (o + pad - r) / stride when divisible
         const int ty = rc.oy - tap_dy[tap];
         const int tx = rc.ox - tap_dx[tap];
-        if ((ty % g.stride) != 0 || (tx % g.stride) != 0 || ty < 0 || tx < 0) return zero;
+        if ((ty % g.stride) != 0 || (tx % g.stride) != 0 || ty < 0 || tx < 0) return;
         sy = ty / g.stride;
         sx = tx / g.stride;
     }
-    if (sy < 0 || sy >= g.Hs || sx < 0 || sx >= g.Ws) return zero;
+    if (sy < 0 || sy >= g.Hs || sx < 0 || sx >= g.Ws) return;
     const size_t off = ((static_cast<size_t>(rc.n) * g.Hs + sy) * g.Ws + sx) * g.C + c8 * 8;
-    const uint4 raw = ldg16(g.src + off);
-    if (g.mode == DTF_PRO_NONE) return raw;
+    L.raw = ldg16(g.src + off);
+    if (TWO) L.x = ldg16(g.src2 + off);
+    L.cb = c8 * 8;
+    L.ok = true;
+}
+
+DTF_DEVINL uint4 gather_finish(const DtfGather& g, const float* p0, const float* p1, const float* p2,
+                               const GatherLoad& L) {
+    if (!L.ok || g.mode == DTF_PRO_NONE) return L.raw;
     float f[8];
-    unpack8(raw, f);
-    const int cb = c8 * 8;
+    unpack8(L.raw, f);
+    const int cb = L.cb;
     if (g.mode == DTF_PRO_BN_RELU) {
 #pragma unroll
         for (int i = 0; i < 8; ++i) f[i] = fmaxf(fmaf(f[i], p0[cb + i], p1[cb + i]), 0.f);
     } else {
         float x[8];
-        unpack8(ldg16(g.src2 + off), x);
+        unpack8(L.x, x);
 #pragma unroll
         for (int i = 0; i < 8; ++i) f[i] = fmaf(f[i], p0[cb + i], fmaf(x[i], p1[cb + i], p2[cb + i]));
     }
     return pack8(f);
+}
+
+DTF_DEVINL uint4 gather16(const DtfGather& g, const int8_t* tap_dy, const int8_t* tap_dx,
+                          const float* p0, const float* p1, const float* p2,
+                          const RowCoord& rc, int jg) {
+    GatherLoad L;
+    if (g.mode == DTF_PRO_BN_BWD) gather_issue<true>(g, tap_dy, tap_dx, rc, jg, L);
+    else gather_issue<false>(g, tap_dy, tap_dx, rc, jg, L);
+    return gather_finish(g, p0, p1, p2, L);
+}
+
+// Chunks jbeg, jbeg + 2, ... < jend of one row (global chunk index = jglobal0 + j), written to
+// dst + j * kChunkBytes; BATCH loads per source are in flight per thread.
+template <int BATCH, bool TWO>
+DTF_DEVINL void gather_row_chunks_t(const DtfGather& g, const int8_t* tap_dy, const int8_t* tap_dx,
+                                    const float* p0, const float* p1, const float* p2, const RowCoord& rc,
+                                    int jbeg, int jend, int jglobal0, uint32_t dst) {
+    for (int j0 = jbeg; j0 < jend; j0 += 2 * BATCH) {
+        GatherLoad L[BATCH];
+#pragma unroll
+        for (int u = 0; u < BATCH; ++u) {
+            const int j = j0 + 2 * u;     // past-the-end chunks resolve to "not ok" inside gather_issue
+            gather_issue<TWO>(g, tap_dy, tap_dx, rc, j < jend ? jglobal0 + j : 0x7fffffff, L[u]);
+        }
+#pragma unroll
+        for (int u = 0; u < BATCH; ++u) {
+            const int j = j0 + 2 * u;
+            const uint4 r = gather_finish(g, p0, p1, p2, L[u]);
+            if (j < jend) sts16(dst + j * (kTileM * 16), r);
+        }
+    }
+}
+DTF_DEVINL void gather_row_chunks(const DtfGather& g, const int8_t* tap_dy, const int8_t* tap_dx,
+                                  const float* p0, const float* p1, const float* p2, const RowCoord& rc,
+                                  int jbeg, int jend, int jglobal0, uint32_t dst) {
+    if (g.mode == DTF_PRO_BN_BWD)
+        gather_row_chunks_t<4, true>(g, tap_dy, tap_dx, p0, p1, p2, rc, jbeg, jend, jglobal0, dst);
+    else
+        gather_row_chunks_t<8, false>(g, tap_dy, tap_dx, p0, p1, p2, rc, jbeg, jend, jglobal0, dst);
 }
 
 DTF_DEVINL void fill_taps(SmemHeader* h, const DtfGather& g, int tid) {

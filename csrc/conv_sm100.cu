@@ -122,19 +122,8 @@ conv_gemm_kernel(const __grid_constant__ DtfConvGemm P) {
                 mbar_wait(smem_u32(&hdr->empty[buf]), ((it >> 1) & 1) ^ 1, 4);
                 const int nch = min(kb_chunks, P.kchunks - kb * kb_chunks);
                 const uint32_t dst = smem_u32(smem_a) + buf * kb_chunks * kChunkBytes + row * 16;
-                int j = half;
-                for (; j + 6 < nch; j += 8) {   // 4 chunks in flight per thread
-                    uint4 v[4];
-#pragma unroll
-                    for (int u = 0; u < 4; ++u)
-                        v[u] = gather16(P.a, hdr->tap_dy, hdr->tap_dx, cst->p0, cst->p1, cst->p2, rc,
-                                        kb * kb_chunks + j + 2 * u);
-#pragma unroll
-                    for (int u = 0; u < 4; ++u) sts16(dst + (j + 2 * u) * kChunkBytes, v[u]);
-                }
-                for (; j < nch; j += 2)
-                    sts16(dst + j * kChunkBytes,
-                          gather16(P.a, hdr->tap_dy, hdr->tap_dx, cst->p0, cst->p1, cst->p2, rc, kb * kb_chunks + j));
+                gather_row_chunks(P.a, hdr->tap_dy, hdr->tap_dx, cst->p0, cst->p1, cst->p2, rc, half, nch,
+                                  kb * kb_chunks, dst);
                 fence_proxy_async_smem();
                 mbar_arrive(smem_u32(&hdr->full[buf]));
             }
@@ -249,21 +238,9 @@ conv_wgrad_kernel(const __grid_constant__ DtfConvWgrad P) {
             const uint32_t a_dst = smem_u32(smem_ab) + buf * buf_bytes + row * 16;
             const uint32_t b_dst = a_dst + gy_chunks * kChunkBytes;
             // gy' chunks: a 1x1 "gather" at the output pixel itself
-            for (int j = half; j < gy_chunks; j += 2)
-                sts16(a_dst + j * kChunkBytes,
-                      gather16(P.gy, hdr->tap_dy + 31, hdr->tap_dx + 31, cst->q0, cst->q1, cst->q2, rc, j));
-            int j = half;
-            for (; j + 6 < nj; j += 8) {
-                uint4 v[4];
-#pragma unroll
-                for (int u = 0; u < 4; ++u)
-                    v[u] = gather16(P.x, hdr->tap_dy, hdr->tap_dx, cst->p0, cst->p1, cst->p2, rc, j0 + j + 2 * u);
-#pragma unroll
-                for (int u = 0; u < 4; ++u) sts16(b_dst + (j + 2 * u) * kChunkBytes, v[u]);
-            }
-            for (; j < nj; j += 2)
-                sts16(b_dst + j * kChunkBytes,
-                      gather16(P.x, hdr->tap_dy, hdr->tap_dx, cst->p0, cst->p1, cst->p2, rc, j0 + j));
+            gather_row_chunks(P.gy, hdr->tap_dy + 31, hdr->tap_dx + 31, cst->q0, cst->q1, cst->q2, rc, half,
+                              gy_chunks, 0, a_dst);
+            gather_row_chunks(P.x, hdr->tap_dy, hdr->tap_dx, cst->p0, cst->p1, cst->p2, rc, half, nj, j0, b_dst);
             fence_proxy_async_smem();
             mbar_arrive(smem_u32(&hdr->full[buf]));
         }
@@ -326,6 +303,7 @@ static int prep_gather(DtfGather* g) {
 
 extern "C" int dtf_conv3x3_try(const DtfConvGemm* p, cudaStream_t stream);
 extern "C" int dtf_conv3x3_wgrad_try(const DtfConvWgrad* p, cudaStream_t stream);
+extern "C" int dtf_conv_s2_dgrad_try(const DtfConvGemm* p, cudaStream_t stream);
 
 extern "C" int dtf_conv_gemm(DtfConvGemm* p, cudaStream_t stream) {
     using namespace dtf;
@@ -335,6 +313,9 @@ extern "C" int dtf_conv_gemm(DtfConvGemm* p, cudaStream_t stream) {
     p->kchunks = (p->a.kchunks_real + 1) & ~1;
     // 3x3 / stride 1: halo-tile kernel with shifted descriptor views (conv3x3_sm100.cu)
     rc = dtf_conv3x3_try(p, stream);
+    if (rc != 0) return rc > 0 ? DTF_OK : rc;
+    // stride-2 input gradient: parity-class kernel (conv_s2_sm100.cu)
+    rc = dtf_conv_s2_dgrad_try(p, stream);
     if (rc != 0) return rc > 0 ? DTF_OK : rc;
     // operand buffer: as many chunks as fit next to the weights, even, <= kchunks
     const int header = 1024 + static_cast<int>(sizeof(SmemConsts));

@@ -150,6 +150,8 @@ DGRAD_CASES = [
     (4, 32, 16, 32, 3, 2),
     (4, 32, 16, 32, 1, 2),
     (3, 16, 32, 64, 3, 2),
+    (5, 8, 32, 64, 3, 2),        # fewer pixels per parity class than one tile
+    (5, 8, 32, 64, 1, 2),
     (3, 8, 64, 64, 3, 1),
 ]
 
