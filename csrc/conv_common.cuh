@@ -10,6 +10,7 @@ constexpr int kEpiWarps = 4;
 constexpr int kGatherWarps = 8;
 constexpr int kThreads = (kEpiWarps + 1 + kGatherWarps) * 32;   // 416
 constexpr int kGatherThreads = kGatherWarps * 32;               // 256
+constexpr int kGatherGroup = kGatherThreads / 2;                // one thread per tile row; two groups alternate
 constexpr int kMmaWarp = kEpiWarps;
 constexpr int kTileM = 128;
 constexpr int kChunkBytes = kTileM * 16;                         // one [128 rows][8 bf16] chunk
@@ -91,6 +92,14 @@ DTF_DEVINL RowCoord row_coord(int m, int M, int Ho, int Wo) {
     r.valid = m < M;
     const int mm = r.valid ? m : 0;
     const int hw = Ho * Wo;
+    if (((hw & (hw - 1)) | (Wo & (Wo - 1))) == 0) {      // powers of two (every CIFAR layer): shifts only
+        const int shw = 31 - __clz(hw), sw = 31 - __clz(Wo);
+        r.n = mm >> shw;
+        const int rem = mm & (hw - 1);
+        r.oy = rem >> sw;
+        r.ox = rem & (Wo - 1);
+        return r;
+    }
     r.n = mm / hw;
     const int rem = mm - r.n * hw;
     r.oy = rem / Wo;
@@ -163,34 +172,151 @@ DTF_DEVINL uint4 gather16(const DtfGather& g, const int8_t* tap_dy, const int8_t
     return gather_finish(g, p0, p1, p2, L);
 }
 
-// Chunks jbeg, jbeg + 2, ... < jend of one row (global chunk index = jglobal0 + j), written to
-// dst + j * kChunkBytes; BATCH loads per source are in flight per thread.
-template <int BATCH, bool TWO>
-DTF_DEVINL void gather_row_chunks_t(const DtfGather& g, const int8_t* tap_dy, const int8_t* tap_dx,
-                                    const float* p0, const float* p1, const float* p2, const RowCoord& rc,
-                                    int jbeg, int jend, int jglobal0, uint32_t dst) {
-    for (int j0 = jbeg; j0 < jend; j0 += 2 * BATCH) {
-        GatherLoad L[BATCH];
+// ---- row gather, tap-major ---------------------------------------------------------------
+// Chunks j in [jbeg, jend) of one im2col row, written to dst + (j - jbeg) * 2 KB.  One thread owns the
+// whole row of a tile; the two gather groups (4 warps each) work on alternate tiles so that two tiles'
+// loads are in flight per CTA.
+// The source pixel of a tap is resolved ONCE per tap (not per chunk), all address arithmetic is 32-bit,
+// strides are powers of two, and the loads of a batch of taps are issued before any is consumed.
+//   L = log2(chunks per tap); TWO = second source (BN backward) is read as well.
+struct RowPre {
+    int base;        // n * Hs * Ws
+    int oy, ox;      // output pixel (already multiplied by the stride for a forward gather)
+    bool valid;
+};
+DTF_DEVINL RowPre row_pre(const DtfGather& g, const RowCoord& rc) {
+    RowPre r;
+    r.base = rc.n * g.Hs * g.Ws;
+    r.oy = g.transposed ? rc.oy : rc.oy * g.stride;
+    r.ox = g.transposed ? rc.ox : rc.ox * g.stride;
+    r.valid = rc.valid;
+    return r;
+}
+
+// One batch of TPB taps starting at t0 (taps beyond t_end are dead).  Gather warps share an issue port
+// with one other warp only, so the serial instruction stream per tile is what bounds small-K layers:
+// the caller picks TPB to match the live tap count instead of predicating a fixed-size batch.
+template <int L, bool TWO, int TPB>
+DTF_DEVINL void gather_batch_t(const DtfGather& g, const int8_t* tap_dy, const int8_t* tap_dx,
+                               const float* p0, const float* p1, const float* p2, const RowPre& rp,
+                               int jbeg, int jend, uint32_t dst, int t0, int t_end) {
+    constexpr int CPT = 1 << L;
+    constexpr int PER = CPT;                                  // chunks per tap
+    constexpr int TSTEP = 1;
+    const int smask = g.stride - 1;
+    const int sshift = g.stride >> 1;                         // stride in {1, 2}
+    uint4 v[TPB * PER], x[TPB * PER];
+    uint32_t okmask = 0;
 #pragma unroll
-        for (int u = 0; u < BATCH; ++u) {
-            const int j = j0 + 2 * u;     // past-the-end chunks resolve to "not ok" inside gather_issue
-            gather_issue<TWO>(g, tap_dy, tap_dx, rc, j < jend ? jglobal0 + j : 0x7fffffff, L[u]);
+    for (int u = 0; u < TPB; ++u) {
+        const int t = t0 + u * TSTEP;
+        bool ok = rp.valid && t < t_end;
+        int sy, sx;
+        const int tt = t < 32 ? t : 31;
+        if (!g.transposed) {
+            sy = rp.oy + tap_dy[tt];
+            sx = rp.ox + tap_dx[tt];
+        } else {
+            const int ty = rp.oy - tap_dy[tt], tx = rp.ox - tap_dx[tt];
+            ok = ok && ((ty | tx) & smask) == 0;
+            sy = ty >> sshift;
+            sx = tx >> sshift;
         }
+        ok = ok && static_cast<unsigned>(sy) < static_cast<unsigned>(g.Hs) &&
+             static_cast<unsigned>(sx) < static_cast<unsigned>(g.Ws);
+        const int off = (rp.base + sy * g.Ws + sx) * g.C;
 #pragma unroll
-        for (int u = 0; u < BATCH; ++u) {
-            const int j = j0 + 2 * u;
-            const uint4 r = gather_finish(g, p0, p1, p2, L[u]);
-            if (j < jend) sts16(dst + j * (kTileM * 16), r);
+        for (int c = 0; c < PER; ++c) {
+            const int c8 = c;
+            const int j = (t << L) + c8;
+            const bool live = ok && j >= jbeg && j < jend && j < g.kchunks_real;
+            v[u * PER + c] = live ? ldg16(g.src + off + c8 * 8) : make_uint4(0, 0, 0, 0);
+            if (TWO) x[u * PER + c] = live ? ldg16(g.src2 + off + c8 * 8) : make_uint4(0, 0, 0, 0);
+            okmask |= (live ? 1u : 0u) << (u * PER + c);
+        }
+    }
+#pragma unroll
+    for (int u = 0; u < TPB; ++u) {
+        const int t = t0 + u * TSTEP;
+#pragma unroll
+        for (int c = 0; c < PER; ++c) {
+            const int c8 = c;
+            const int j = (t << L) + c8;
+            uint4 r = v[u * PER + c];
+            if (g.mode != DTF_PRO_NONE && ((okmask >> (u * PER + c)) & 1)) {
+                float f[8];
+                unpack8(r, f);
+                const int cb = c8 * 8;
+                if (!TWO) {
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) f[i] = fmaxf(fmaf(f[i], p0[cb + i], p1[cb + i]), 0.f);
+                } else {
+                    float xx[8];
+                    unpack8(x[u * PER + c], xx);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) f[i] = fmaf(f[i], p0[cb + i], fmaf(xx[i], p1[cb + i], p2[cb + i]));
+                }
+                r = pack8(f);
+            }
+            if (t < t_end && j >= jbeg && j < jend) sts16(dst + (j - jbeg) * (kTileM * 16), r);
         }
     }
 }
-DTF_DEVINL void gather_row_chunks(const DtfGather& g, const int8_t* tap_dy, const int8_t* tap_dx,
-                                  const float* p0, const float* p1, const float* p2, const RowCoord& rc,
-                                  int jbeg, int jend, int jglobal0, uint32_t dst) {
-    if (g.mode == DTF_PRO_BN_BWD)
-        gather_row_chunks_t<4, true>(g, tap_dy, tap_dx, p0, p1, p2, rc, jbeg, jend, jglobal0, dst);
-    else
-        gather_row_chunks_t<8, false>(g, tap_dy, tap_dx, p0, p1, p2, rc, jbeg, jend, jglobal0, dst);
+
+template <int L, bool TWO>
+DTF_DEVINL void gather_taps_t(const DtfGather& g, const int8_t* tap_dy, const int8_t* tap_dx,
+                              const float* p0, const float* p1, const float* p2, const RowPre& rp,
+                              int jbeg, int jend, uint32_t dst) {
+    constexpr int PER = 1 << L;
+    constexpr int BUDGET = TWO ? 4 : 8;                       // 16-byte loads in flight per source
+    constexpr int TMAX = BUDGET / PER > 0 ? BUDGET / PER : 1; // taps per full batch
+    constexpr int TSTEP = 1;
+    int t = jbeg >> L;
+    const int t_end = ((jend - 1) >> L) + 1;
+#define DTF_BATCH(N)                                                                                       \
+    {                                                                                                      \
+        gather_batch_t<L, TWO, N>(g, tap_dy, tap_dx, p0, p1, p2, rp, jbeg, jend, dst, t, t_end);           \
+        t += N * TSTEP;                                                                                    \
+    }
+    while (t < t_end) {
+        const int rem = (t_end - t + TSTEP - 1) / TSTEP;
+        if (TMAX >= 8 && rem >= 5) DTF_BATCH(TMAX >= 8 ? 8 : 1)
+        else if (TMAX >= 4 && rem >= 3) DTF_BATCH(TMAX >= 4 ? 4 : 1)
+        else if (TMAX >= 2 && rem >= 2) DTF_BATCH(TMAX >= 2 ? 2 : 1)
+        else DTF_BATCH(1)
+    }
+#undef DTF_BATCH
+}
+
+// Fallback for wide channel counts (> 64): one chunk at a time.
+DTF_DEVINL void gather_chunks_slow(const DtfGather& g, const int8_t* tap_dy, const int8_t* tap_dx,
+                                   const float* p0, const float* p1, const float* p2, const RowCoord& rc,
+                                   int jbeg, int jend, uint32_t dst) {
+    for (int j = jbeg; j < jend; ++j)
+        sts16(dst + (j - jbeg) * (kTileM * 16), gather16(g, tap_dy, tap_dx, p0, p1, p2, rc, j));
+}
+
+DTF_DEVINL void gather_row(const DtfGather& g, const int8_t* tap_dy, const int8_t* tap_dx,
+                           const float* p0, const float* p1, const float* p2, const RowCoord& rc,
+                           int jbeg, int jend, uint32_t dst) {
+    if (g.cpt_shift > 3 || g.stride > 2) {
+        gather_chunks_slow(g, tap_dy, tap_dx, p0, p1, p2, rc, jbeg, jend, dst);
+        return;
+    }
+    const RowPre rp = row_pre(g, rc);
+    const bool two = g.mode == DTF_PRO_BN_BWD;
+#define DTF_GATHER_CASE(LL)                                                                             \
+    case LL:                                                                                            \
+        if (two) gather_taps_t<LL, true>(g, tap_dy, tap_dx, p0, p1, p2, rp, jbeg, jend, dst);            \
+        else gather_taps_t<LL, false>(g, tap_dy, tap_dx, p0, p1, p2, rp, jbeg, jend, dst);               \
+        break;
+    switch (g.cpt_shift) {
+        DTF_GATHER_CASE(0)
+        DTF_GATHER_CASE(1)
+        DTF_GATHER_CASE(2)
+        DTF_GATHER_CASE(3)
+    }
+#undef DTF_GATHER_CASE
 }
 
 DTF_DEVINL void fill_taps(SmemHeader* h, const DtfGather& g, int tid) {

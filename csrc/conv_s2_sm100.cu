@@ -38,18 +38,85 @@ struct __align__(16) S2Header {
 struct S2Row { int n, a, b; bool valid; };
 
 DTF_DEVINL S2Row s2_row(int m, int Mc, int Hh, int Wh) {
+    const RowCoord c = row_coord(m, Mc, Hh, Wh);
     S2Row r;
-    r.valid = m < Mc;
-    const int mm = r.valid ? m : 0;
-    const int hw = Hh * Wh;
-    r.n = mm / hw;
-    const int rem = mm - r.n * hw;
-    r.a = rem / Wh;
-    r.b = rem - r.a * Wh;
+    r.n = c.n; r.a = c.oy; r.b = c.ox; r.valid = c.valid;
     return r;
 }
 
-constexpr int kS2Batch = 8;     // 16-byte loads in flight per thread and source
+// One row of the operand tile: for every tap of the parity class, all chunks of the row.
+// All loads of up to `BUDGET` chunks are issued before the first is consumed.
+template <int L, bool TWO, int TPB>
+DTF_DEVINL void s2_batch_t(const DtfGather& G, const S2Header* hdr, const SmemConsts* cst, int cls, const S2Row& rc,
+                           int rowbase, uint32_t dst, int t0) {
+    constexpr int PER = 1 << L;
+    uint4 v[TPB * PER], x[TPB * PER];
+    uint32_t okmask = 0;
+#pragma unroll
+    for (int u = 0; u < TPB; ++u) {
+        const int ti = cls * 4 + t0 + u;
+        const int sy = rc.a + hdr->dy[ti], sx = rc.b + hdr->dx[ti];
+        const bool ok = rc.valid && sy < G.Hs && sx < G.Ws;
+        const int off = (rowbase + sy * G.Ws + sx) * G.C;
+#pragma unroll
+        for (int c = 0; c < PER; ++c) {
+            const int c8 = c;
+            v[u * PER + c] = ok ? ldg16(G.src + off + c8 * 8) : make_uint4(0, 0, 0, 0);
+            if (TWO) x[u * PER + c] = ok ? ldg16(G.src2 + off + c8 * 8) : make_uint4(0, 0, 0, 0);
+        }
+        okmask |= (ok ? 1u : 0u) << u;
+    }
+#pragma unroll
+    for (int u = 0; u < TPB; ++u) {
+#pragma unroll
+        for (int c = 0; c < PER; ++c) {
+            const int c8 = c;
+            uint4 r = v[u * PER + c];
+            if (TWO && ((okmask >> u) & 1)) {
+                const int cb = c8 * 8;
+                float f[8], xx[8];
+                unpack8(r, f);
+                unpack8(x[u * PER + c], xx);
+#pragma unroll
+                for (int i = 0; i < 8; ++i)
+                    f[i] = fmaf(f[i], cst->p0[cb + i], fmaf(xx[i], cst->p1[cb + i], cst->p2[cb + i]));
+                r = pack8(f);
+            }
+            sts16(dst + (((t0 + u) << L) + c8) * kChunkBytes, r);
+        }
+    }
+}
+
+// One row of the operand tile: for every tap of the parity class (1, 2 or 4), this thread's chunks
+// The loads of a batch are issued before the first is consumed; batches are
+// sized to the class so that no dead tap costs instructions.
+template <int L, bool TWO>
+DTF_DEVINL void s2_gather_t(const DtfGather& G, const S2Header* hdr, const SmemConsts* cst, int cls, const S2Row& rc,
+                            int rowbase, uint32_t dst) {
+    constexpr int PER = 1 << L;
+    constexpr int BUDGET = TWO ? 4 : 8;
+    const int nt = hdr->ntaps[cls];
+    if (nt == 1) {
+        s2_batch_t<L, TWO, 1>(G, hdr, cst, cls, rc, rowbase, dst, 0);
+    } else if (nt == 2) {
+        if (2 * PER <= BUDGET) {
+            s2_batch_t<L, TWO, (2 * PER <= BUDGET ? 2 : 1)>(G, hdr, cst, cls, rc, rowbase, dst, 0);
+        } else {
+            s2_batch_t<L, TWO, 1>(G, hdr, cst, cls, rc, rowbase, dst, 0);
+            s2_batch_t<L, TWO, 1>(G, hdr, cst, cls, rc, rowbase, dst, 1);
+        }
+    } else {
+        if (4 * PER <= BUDGET) {
+            s2_batch_t<L, TWO, (4 * PER <= BUDGET ? 4 : 1)>(G, hdr, cst, cls, rc, rowbase, dst, 0);
+        } else if (2 * PER <= BUDGET) {
+            s2_batch_t<L, TWO, (2 * PER <= BUDGET ? 2 : 1)>(G, hdr, cst, cls, rc, rowbase, dst, 0);
+            s2_batch_t<L, TWO, (2 * PER <= BUDGET ? 2 : 1)>(G, hdr, cst, cls, rc, rowbase, dst, 2);
+        } else {
+#pragma unroll
+            for (int t = 0; t < 4; ++t) s2_batch_t<L, TWO, 1>(G, hdr, cst, cls, rc, rowbase, dst, t);
+        }
+    }
+}
 
 __global__ void __launch_bounds__(kThreads, 1)
 conv_dgrad_s2_kernel(const __grid_constant__ DtfConvGemm P) {
@@ -75,7 +142,7 @@ conv_dgrad_s2_kernel(const __grid_constant__ DtfConvGemm P) {
 
     if (tid == 0) {
         for (int i = 0; i < 2; ++i) {
-            mbar_init(smem_u32(&hdr->full[i]), kGatherThreads);
+            mbar_init(smem_u32(&hdr->full[i]), kGatherGroup);
             mbar_init(smem_u32(&hdr->empty[i]), 1);
             mbar_init(smem_u32(&hdr->acc_full[i]), 1);
             mbar_init(smem_u32(&hdr->acc_empty[i]), kEpiWarps * 32);
@@ -155,59 +222,37 @@ conv_dgrad_s2_kernel(const __grid_constant__ DtfConvGemm P) {
         // ================= gather producers =================
         const int g = tid - (kMmaWarp + 1) * 32;
         const int row = g & (kTileM - 1);
-        const int half = g >> 7;
+        const uint32_t group = g >> 7;                       // two groups work on alternate tiles
         const bool two = G.mode == DTF_PRO_BN_BWD;
         uint32_t it = 0;
         for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+            if ((it & 1) != group) continue;
             const int cls = tile / tiles_per_class;
             const S2Row rc = s2_row((tile - cls * tiles_per_class) * kTileM + row, Mc, Hh, Wh);
-            const int nch = hdr->ntaps[cls] * cpt;
-            const uint32_t buf = it & 1;
-            mbar_wait(smem_u32(&hdr->empty[buf]), ((it >> 1) & 1) ^ 1, 24);
-            const uint32_t dst = smem_u32(smem_a) + buf * cap * kChunkBytes + row * 16;
-            for (int j0 = half; j0 < nch; j0 += 2 * kS2Batch) {
-                uint4 v[kS2Batch], x[kS2Batch];
-                uint32_t okmask = 0;
-#pragma unroll
-                for (int u = 0; u < kS2Batch; ++u) {
-                    const int j = j0 + 2 * u;
-                    v[u] = make_uint4(0, 0, 0, 0);
-                    x[u] = v[u];
-                    if (j < nch && rc.valid) {
-                        const int t = j >> G.cpt_shift;
-                        const int sy = rc.a + hdr->dy[cls * 4 + t], sx = rc.b + hdr->dx[cls * 4 + t];
-                        if (sy < G.Hs && sx < G.Ws) {
-                            const size_t off = ((static_cast<size_t>(rc.n) * G.Hs + sy) * G.Ws + sx) * G.C +
-                                               (j & (cpt - 1)) * 8;
-                            v[u] = ldg16(G.src + off);
-                            if (two) x[u] = ldg16(G.src2 + off);
-                            okmask |= 1u << u;
-                        }
-                    }
-                }
-#pragma unroll
-                for (int u = 0; u < kS2Batch; ++u) {
-                    const int j = j0 + 2 * u;
-                    if (j >= nch) break;
-                    if (two && ((okmask >> u) & 1)) {
-                        const int cb = (j & (cpt - 1)) * 8;
-                        float f[8], xx[8];
-                        unpack8(v[u], f);
-                        unpack8(x[u], xx);
-#pragma unroll
-                        for (int i = 0; i < 8; ++i)
-                            f[i] = fmaf(f[i], cst->p0[cb + i], fmaf(xx[i], cst->p1[cb + i], cst->p2[cb + i]));
-                        v[u] = pack8(f);
-                    }
-                    sts16(dst + j * kChunkBytes, v[u]);
-                }
+            mbar_wait(smem_u32(&hdr->empty[group]), ((it >> 1) & 1) ^ 1, 24);
+            const uint32_t dst = smem_u32(smem_a) + group * cap * kChunkBytes + row * 16;
+            const int rowbase = rc.n * G.Hs * G.Ws;
+#define DTF_S2_CASE(LL)                                                                                   \
+    case LL:                                                                                              \
+        if (two) s2_gather_t<LL, true>(G, hdr, cst, cls, rc, rowbase, dst);                         \
+        else s2_gather_t<LL, false>(G, hdr, cst, cls, rc, rowbase, dst);                            \
+        break;
+            switch (G.cpt_shift) {
+                DTF_S2_CASE(1)
+                DTF_S2_CASE(2)
+                DTF_S2_CASE(3)
             }
+#undef DTF_S2_CASE
             fence_proxy_async_smem();
-            mbar_arrive(smem_u32(&hdr->full[buf]));
+            mbar_arrive(smem_u32(&hdr->full[group]));
         }
     } else {
         // ================= epilogue =================
         const dtf_bf16* auxp = epilogue_aux_ptr(P);
+        const bool reg_stats = P.epi_stats_out != nullptr && N <= 16;   // see conv_sm100.cu
+        float acc1[16], acc2[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) { acc1[i] = 0.f; acc2[i] = 0.f; }
         uint32_t it = 0;
         for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
             const int cls = tile / tiles_per_class;
@@ -222,18 +267,25 @@ conv_dgrad_s2_kernel(const __grid_constant__ DtfConvGemm P) {
             const uint32_t a = it & 1;
             mbar_wait(smem_u32(&hdr->acc_full[a]), (it >> 1) & 1, 25);
             tc_fence_after_sync();
+            if (reg_stats) {
+                float v[16];
+                tmem_ld16(tmem_base + ((warp * 32u) << 16) + a * N, v);
+                epilogue_group(P, cst, v, rc.valid, obase, 0, lane, aux, acc1, acc2);
+            } else {
 #pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                const int cg = q * 16;
-                if (cg < N) {
-                    float v[16];
-                    tmem_ld16(tmem_base + ((warp * 32u) << 16) + a * N + cg, v);
-                    epilogue_group(P, cst, v, rc.valid, obase, cg, lane, aux + 2 * q);
+                for (int q = 0; q < 4; ++q) {
+                    const int cg = q * 16;
+                    if (cg < N) {
+                        float v[16];
+                        tmem_ld16(tmem_base + ((warp * 32u) << 16) + a * N + cg, v);
+                        epilogue_group(P, cst, v, rc.valid, obase, cg, lane, aux + 2 * q);
+                    }
                 }
             }
             tc_fence_before_sync();
             mbar_arrive(smem_u32(&hdr->acc_empty[a]));
         }
+        if (reg_stats) flush_stats16(cst, acc1, acc2, 0, lane);
         if (P.epi_stats_out) {
             named_bar_sync(1, kEpiWarps * 32);
             for (int c = tid; c < N; c += kEpiWarps * 32) {
@@ -265,7 +317,7 @@ extern "C" int dtf_conv_s2_dgrad_try(const DtfConvGemm* p, cudaStream_t stream) 
     if (!k3 && !k1) return 0;
     if (k1 && !(p->epi_mode == DTF_EPI_RELU_MASK && p->epi_accumulate)) return 0;   // 3/4 of `out` is not written
     if ((p->Ho & 1) || (p->Wo & 1) || g.Hs * 2 != p->Ho || g.Ws * 2 != p->Wo) return 0;
-    if (g.cpt_shift < 1 || p->N > 64 || g.mode == DTF_PRO_BN_RELU) return 0;
+    if (g.cpt_shift < 1 || g.cpt_shift > 3 || p->N > 64 || g.mode == DTF_PRO_BN_RELU) return 0;
     const int cpt = 1 << g.cpt_shift;
     DtfConvGemm q = *p;
     q.kb_chunks = (k3 ? 4 : 1) * cpt;

@@ -51,7 +51,7 @@ conv_gemm_kernel(const __grid_constant__ DtfConvGemm P) {
     // ---- one-time setup ----
     if (tid == 0) {
         for (int i = 0; i < 2; ++i) {
-            mbar_init(smem_u32(&hdr->full[i]), kGatherThreads);
+            mbar_init(smem_u32(&hdr->full[i]), kGatherGroup);
             mbar_init(smem_u32(&hdr->empty[i]), 1);
             mbar_init(smem_u32(&hdr->acc_full[i]), 1);
             mbar_init(smem_u32(&hdr->acc_empty[i]), kEpiWarps * 32);
@@ -113,23 +113,30 @@ conv_gemm_kernel(const __grid_constant__ DtfConvGemm P) {
         // ================= gather producers =================
         const int g = tid - (kMmaWarp + 1) * 32;
         const int row = g & (kTileM - 1);
-        const int half = g >> 7;
+        const uint32_t group = g >> 7;                       // operand buffer this thread's group fills
         uint32_t it = 0;
         for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
             const RowCoord rc = row_coord(tile * kTileM + row, M, P.Ho, P.Wo);
             for (int kb = 0; kb < num_kb; ++kb, ++it) {
-                const uint32_t buf = it & 1;
-                mbar_wait(smem_u32(&hdr->empty[buf]), ((it >> 1) & 1) ^ 1, 4);
+                if ((it & 1) != group) continue;
+                mbar_wait(smem_u32(&hdr->empty[group]), ((it >> 1) & 1) ^ 1, 4);
                 const int nch = min(kb_chunks, P.kchunks - kb * kb_chunks);
-                const uint32_t dst = smem_u32(smem_a) + buf * kb_chunks * kChunkBytes + row * 16;
-                gather_row_chunks(P.a, hdr->tap_dy, hdr->tap_dx, cst->p0, cst->p1, cst->p2, rc, half, nch,
-                                  kb * kb_chunks, dst);
+                const uint32_t dst = smem_u32(smem_a) + group * kb_chunks * kChunkBytes + row * 16;
+                gather_row(P.a, hdr->tap_dy, hdr->tap_dx, cst->p0, cst->p1, cst->p2, rc, kb * kb_chunks,
+                           kb * kb_chunks + nch, dst);
                 fence_proxy_async_smem();
-                mbar_arrive(smem_u32(&hdr->full[buf]));
+                mbar_arrive(smem_u32(&hdr->full[group]));
             }
         }
     } else {
         // ================= epilogue =================
+        // N <= 16: the per-channel statistics stay in registers across the CTA's tiles (one warp
+        // butterfly per CTA instead of one per tile -- the epilogue warp's instruction stream is what
+        // bounds the small-K layers).
+        const bool reg_stats = P.epi_stats_out != nullptr && N <= 16;
+        float acc1[16], acc2[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) { acc1[i] = 0.f; acc2[i] = 0.f; }
         uint32_t local_tile = 0;
         for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local_tile) {
             const uint32_t a = local_tile & 1;
@@ -138,14 +145,21 @@ conv_gemm_kernel(const __grid_constant__ DtfConvGemm P) {
             const int m = tile * kTileM + warp * 32 + lane;
             const bool valid = m < M;
             const size_t obase = static_cast<size_t>(valid ? m : 0) * N;
-            for (int cg = 0; cg < N; cg += 16) {
+            if (reg_stats) {
                 float v[16];
-                tmem_ld16(tmem_base + ((warp * 32u) << 16) + a * N + cg, v);
-                epilogue_group(P, cst, v, valid, obase, cg, lane);
+                tmem_ld16(tmem_base + ((warp * 32u) << 16) + a * N, v);
+                epilogue_group(P, cst, v, valid, obase, 0, lane, nullptr, acc1, acc2);
+            } else {
+                for (int cg = 0; cg < N; cg += 16) {
+                    float v[16];
+                    tmem_ld16(tmem_base + ((warp * 32u) << 16) + a * N + cg, v);
+                    epilogue_group(P, cst, v, valid, obase, cg, lane);
+                }
             }
             tc_fence_before_sync();
             mbar_arrive(smem_u32(&hdr->acc_empty[a]));
         }
+        if (reg_stats) flush_stats16(cst, acc1, acc2, 0, lane);
         if (P.epi_stats_out) {
             named_bar_sync(1, kEpiWarps * 32);
             for (int c = tid; c < N; c += kEpiWarps * 32) {
@@ -187,7 +201,7 @@ conv_wgrad_kernel(const __grid_constant__ DtfConvWgrad P) {
 
     if (tid == 0) {
         for (int i = 0; i < 2; ++i) {
-            mbar_init(smem_u32(&hdr->full[i]), kGatherThreads);
+            mbar_init(smem_u32(&hdr->full[i]), kGatherGroup);
             mbar_init(smem_u32(&hdr->empty[i]), 1);
         }
         mbar_init(smem_u32(&hdr->acc_full[0]), 1);
@@ -229,20 +243,19 @@ conv_wgrad_kernel(const __grid_constant__ DtfConvWgrad P) {
     } else if (warp > kMmaWarp) {
         const int g = tid - (kMmaWarp + 1) * 32;
         const int row = g & (kTileM - 1);
-        const int half = g >> 7;
+        const uint32_t group = g >> 7;
         uint32_t it = 0;
         for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
-            const uint32_t buf = it & 1;
+            if ((it & 1) != group) continue;
             const RowCoord rc = row_coord(tile * kTileM + row, M, P.Ho, P.Wo);
-            mbar_wait(smem_u32(&hdr->empty[buf]), ((it >> 1) & 1) ^ 1, 7);
-            const uint32_t a_dst = smem_u32(smem_ab) + buf * buf_bytes + row * 16;
+            mbar_wait(smem_u32(&hdr->empty[group]), ((it >> 1) & 1) ^ 1, 7);
+            const uint32_t a_dst = smem_u32(smem_ab) + group * buf_bytes + row * 16;
             const uint32_t b_dst = a_dst + gy_chunks * kChunkBytes;
             // gy' chunks: a 1x1 "gather" at the output pixel itself
-            gather_row_chunks(P.gy, hdr->tap_dy + 31, hdr->tap_dx + 31, cst->q0, cst->q1, cst->q2, rc, half,
-                              gy_chunks, 0, a_dst);
-            gather_row_chunks(P.x, hdr->tap_dy, hdr->tap_dx, cst->p0, cst->p1, cst->p2, rc, half, nj, j0, b_dst);
+            gather_row(P.gy, hdr->tap_dy + 31, hdr->tap_dx + 31, cst->q0, cst->q1, cst->q2, rc, 0, gy_chunks, a_dst);
+            gather_row(P.x, hdr->tap_dy, hdr->tap_dx, cst->p0, cst->p1, cst->p2, rc, j0, j0 + nj, b_dst);
             fence_proxy_async_smem();
-            mbar_arrive(smem_u32(&hdr->full[buf]));
+            mbar_arrive(smem_u32(&hdr->full[group]));
         }
     } else if (has_work) {
         mbar_wait(smem_u32(&hdr->acc_full[0]), 0, 8);

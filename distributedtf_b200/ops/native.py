@@ -13,7 +13,7 @@ from typing import Any, Optional, Sequence
 
 import torch
 
-LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "lib", "libdtf_b200.so")
+LIB_PATH = os.environ.get("DTF_LIB") or os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "lib", "libdtf_b200.so")
 _lib: Optional[C.CDLL] = None
 
 OK = 0
