@@ -215,9 +215,42 @@ DTF_DEVINL bool elect_one() {
     return pred != 0;
 }
 
+// ---- programmatic dependent launch ------------------------------------------------------
+// Every kernel of the training step is launched with the programmatic-stream-serialization
+// attribute (dtf_launch below): its CTAs may be scheduled while the previous kernel is still
+// draining, run their private set-up (barriers, TMEM allocation, shared tables), and block in
+// griddep_wait() until the previous grid has completed and its writes are visible.  Rules kept by
+// all kernels: nothing in global memory is read or written before griddep_wait(); every kernel
+// executes griddep_wait() (completion is then transitive along the stream).
+DTF_DEVINL void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+DTF_DEVINL void griddep_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // named barrier among a subset of warps
 DTF_DEVINL void named_bar_sync(uint32_t id, uint32_t nthreads) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
 
 }  // namespace dtf
+
+// Host side: launch with the programmatic-dependent-launch attribute (DTF_NO_PDL=1 turns it off).
+#include <stdlib.h>
+inline bool dtf_pdl_enabled() {
+    static int on = -1;
+    if (on < 0) on = getenv("DTF_NO_PDL") != nullptr ? 0 : 1;
+    return on != 0;
+}
+template <typename... KArgs, typename... Args>
+inline cudaError_t dtf_launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                              Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = dtf_pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}

@@ -163,12 +163,14 @@ DTF_DEVINL void conv3x3_body(const DtfConvGemm& P, const HaloGeom& G, const int 
         mbar_init(smem_u32(&hdr->bfull), 1);
         mbar_fence_init();
     }
+    for (int c = tid; c < 2 * kMaxC; c += kHThreads) (&cst->bins[0][0])[c] = 0.f;
+    if (warp == kMmaWarp) tmem_alloc(smem_u32(&hdr->tmem_base), acc_cols);
+    griddep_launch_dependents();
+    griddep_wait();
     fill_prologue(P.a, cst->p0, cst->p1, cst->p2, tid, kHThreads);
     if (P.epi_mode == DTF_EPI_RELU_MASK)
         for (int c = tid; c < N; c += kHThreads)
             bn_fwd_consts(P.epi_bn, c, cst->e_scale[c], cst->e_shift[c], cst->e_mean[c], cst->e_invstd[c]);
-    for (int c = tid; c < 2 * kMaxC; c += kHThreads) (&cst->bins[0][0])[c] = 0.f;
-    if (warp == kMmaWarp) tmem_alloc(smem_u32(&hdr->tmem_base), acc_cols);
     if (cta == 0 && P.a.update_running && P.a.mode == DTF_PRO_BN_RELU && !P.a.bn.use_running)
         update_running(P.a.bn, tid, kHThreads);
     if (tid == 0) DTF_MARK(0);
@@ -384,9 +386,11 @@ DTF_DEVINL void conv3x3_wgrad_body(const DtfConvWgrad& P, const HaloGeom& G, con
         mbar_init(smem_u32(&hdr->acc_full[0]), 1);
         mbar_fence_init();
     }
+    if (warp == kMmaWarp) tmem_alloc(smem_u32(&hdr->tmem_base), acc_cols);
+    griddep_launch_dependents();
+    griddep_wait();
     fill_prologue(P.x, cst->p0, cst->p1, cst->p2, tid, kHThreads);
     fill_prologue(P.gy, cst->q0, cst->q1, cst->q2, tid, kHThreads);
-    if (warp == kMmaWarp) tmem_alloc(smem_u32(&hdr->tmem_base), acc_cols);
     tc_fence_before_sync();
     __syncthreads();
     tc_fence_after_sync();
@@ -579,9 +583,9 @@ extern "C" int dtf_conv3x3_try(const DtfConvGemm* p, cudaStream_t stream) {
         attr_set = 1;
     }
     const int grid = G.num_tiles < halo_sms() ? G.num_tiles : halo_sms();
-    if (G.c8 == 2) conv3x3_kernel<2><<<grid, kHThreads, smem_bytes, stream>>>(*p, G);
-    else if (G.c8 == 4) conv3x3_kernel<4><<<grid, kHThreads, smem_bytes, stream>>>(*p, G);
-    else conv3x3_kernel<8><<<grid, kHThreads, smem_bytes, stream>>>(*p, G);
+    if (G.c8 == 2) dtf_launch(conv3x3_kernel<2>, dim3(grid), dim3(kHThreads), smem_bytes, stream, *p, G);
+    else if (G.c8 == 4) dtf_launch(conv3x3_kernel<4>, dim3(grid), dim3(kHThreads), smem_bytes, stream, *p, G);
+    else dtf_launch(conv3x3_kernel<8>, dim3(grid), dim3(kHThreads), smem_bytes, stream, *p, G);
     return cudaGetLastError() == cudaSuccess ? 1 : DTF_ERR_CUDA;
 }
 
@@ -625,9 +629,9 @@ extern "C" int dtf_conv3x3_wgrad_try(const DtfConvWgrad* p, cudaStream_t stream)
     if (gx > G.num_tiles) gx = G.num_tiles;
     if (gx < 1) gx = 1;
     dim3 grid(gx, ny);
-    if (G.c8 == 2) conv3x3_wgrad_kernel<2><<<grid, kHThreads, smem_bytes, stream>>>(*p, G);
-    else if (G.c8 == 4) conv3x3_wgrad_kernel<4><<<grid, kHThreads, smem_bytes, stream>>>(*p, G);
-    else conv3x3_wgrad_kernel<8><<<grid, kHThreads, smem_bytes, stream>>>(*p, G);
+    if (G.c8 == 2) dtf_launch(conv3x3_wgrad_kernel<2>, dim3(grid), dim3(kHThreads), smem_bytes, stream, *p, G);
+    else if (G.c8 == 4) dtf_launch(conv3x3_wgrad_kernel<4>, dim3(grid), dim3(kHThreads), smem_bytes, stream, *p, G);
+    else dtf_launch(conv3x3_wgrad_kernel<8>, dim3(grid), dim3(kHThreads), smem_bytes, stream, *p, G);
     return cudaGetLastError() == cudaSuccess ? 1 : DTF_ERR_CUDA;
 }
 
@@ -700,8 +704,8 @@ extern "C" int dtf_conv3x3_bwd_fused_try(const DtfConvGemm* pd, const DtfConvWgr
     if (gx < 1) gx = 1;
     const int grid = n_d + gx * ny;
     const int smem_bytes = smem_d > smem_w ? smem_d : smem_w;
-    if (Gd.c8 == 2) conv3x3_bwd_fused_kernel<2><<<grid, kHThreads, smem_bytes, stream>>>(*pd, Gd, *pw, Gw, n_d, gx);
-    else if (Gd.c8 == 4) conv3x3_bwd_fused_kernel<4><<<grid, kHThreads, smem_bytes, stream>>>(*pd, Gd, *pw, Gw, n_d, gx);
-    else conv3x3_bwd_fused_kernel<8><<<grid, kHThreads, smem_bytes, stream>>>(*pd, Gd, *pw, Gw, n_d, gx);
+    if (Gd.c8 == 2) dtf_launch(conv3x3_bwd_fused_kernel<2>, dim3(grid), dim3(kHThreads), smem_bytes, stream, *pd, Gd, *pw, Gw, n_d, gx);
+    else if (Gd.c8 == 4) dtf_launch(conv3x3_bwd_fused_kernel<4>, dim3(grid), dim3(kHThreads), smem_bytes, stream, *pd, Gd, *pw, Gw, n_d, gx);
+    else dtf_launch(conv3x3_bwd_fused_kernel<8>, dim3(grid), dim3(kHThreads), smem_bytes, stream, *pd, Gd, *pw, Gw, n_d, gx);
     return cudaGetLastError() == cudaSuccess ? 1 : DTF_ERR_CUDA;
 }

@@ -171,13 +171,15 @@ conv_dgrad_s2_kernel(const __grid_constant__ DtfConvGemm P) {
             hdr->dy[0] = hdr->dx[0] = hdr->widx[0] = 0;
         }
     }
+    for (int c = tid; c < 2 * kMaxC; c += kThreads) (&cst->bins[0][0])[c] = 0.f;
+    if (warp == kMmaWarp) tmem_alloc(smem_u32(&hdr->tmem_base), acc_cols);
+    griddep_launch_dependents();
+    griddep_wait();
     fill_prologue(G, cst->p0, cst->p1, cst->p2, tid, kThreads);
     if (P.epi_mode == DTF_EPI_RELU_MASK) {
         for (int c = tid; c < N; c += kThreads)
             bn_fwd_consts(P.epi_bn, c, cst->e_scale[c], cst->e_shift[c], cst->e_mean[c], cst->e_invstd[c]);
     }
-    for (int c = tid; c < 2 * kMaxC; c += kThreads) (&cst->bins[0][0])[c] = 0.f;
-    if (warp == kMmaWarp) tmem_alloc(smem_u32(&hdr->tmem_base), acc_cols);
     tc_fence_before_sync();
     __syncthreads();
     tc_fence_after_sync();
@@ -346,7 +348,7 @@ extern "C" int dtf_conv_s2_dgrad_try(const DtfConvGemm* p, cudaStream_t stream) 
     const int Mc = q.NB * (q.Ho / 2) * (q.Wo / 2);
     const int tiles = (k3 ? 4 : 1) * ((Mc + kTileM - 1) / kTileM);
     const int grid = tiles < sms ? tiles : sms;
-    conv_dgrad_s2_kernel<<<grid, kThreads, smem_bytes, stream>>>(q);
+    dtf_launch(conv_dgrad_s2_kernel, dim3(grid), dim3(kThreads), smem_bytes, stream, q);
     const cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) {
         fprintf(stderr, "[dtf] conv_dgrad_s2 launch (grid %d, smem %d): %s\n", grid, smem_bytes, cudaGetErrorString(e));

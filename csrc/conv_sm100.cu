@@ -60,13 +60,15 @@ conv_gemm_kernel(const __grid_constant__ DtfConvGemm P) {
         mbar_fence_init();
     }
     fill_taps(hdr, P.a, tid);
+    for (int c = tid; c < 2 * kMaxC; c += kThreads) (&cst->bins[0][0])[c] = 0.f;
+    if (warp == kMmaWarp) tmem_alloc(smem_u32(&hdr->tmem_base), acc_cols);
+    griddep_launch_dependents();
+    griddep_wait();
     fill_prologue(P.a, cst->p0, cst->p1, cst->p2, tid, kThreads);
     if (P.epi_mode == DTF_EPI_RELU_MASK) {
         for (int c = tid; c < N; c += kThreads)
             bn_fwd_consts(P.epi_bn, c, cst->e_scale[c], cst->e_shift[c], cst->e_mean[c], cst->e_invstd[c]);
     }
-    for (int c = tid; c < 2 * kMaxC; c += kThreads) (&cst->bins[0][0])[c] = 0.f;
-    if (warp == kMmaWarp) tmem_alloc(smem_u32(&hdr->tmem_base), acc_cols);
     if (blockIdx.x == 0 && P.a.update_running && P.a.mode == DTF_PRO_BN_RELU && !P.a.bn.use_running)
         update_running(P.a.bn, tid, kThreads);
     tc_fence_before_sync();
@@ -208,9 +210,11 @@ conv_wgrad_kernel(const __grid_constant__ DtfConvWgrad P) {
         mbar_fence_init();
     }
     fill_taps(hdr, P.x, tid);
+    if (warp == kMmaWarp) tmem_alloc(smem_u32(&hdr->tmem_base), acc_cols);
+    griddep_launch_dependents();
+    griddep_wait();
     fill_prologue(P.x, cst->p0, cst->p1, cst->p2, tid, kThreads);
     fill_prologue(P.gy, cst->q0, cst->q1, cst->q2, tid, kThreads);
-    if (warp == kMmaWarp) tmem_alloc(smem_u32(&hdr->tmem_base), acc_cols);
     tc_fence_before_sync();
     __syncthreads();
     tc_fence_after_sync();
@@ -353,7 +357,7 @@ extern "C" int dtf_conv_gemm(DtfConvGemm* p, cudaStream_t stream) {
         if (e != cudaSuccess) return DTF_ERR_CUDA;
         max_set = 227 * 1024;
     }
-    conv_gemm_kernel<<<grid, kThreads, smem_bytes, stream>>>(*p);
+    dtf_launch(conv_gemm_kernel, dim3(grid), dim3(kThreads), smem_bytes, stream, *p);
     return cudaGetLastError() == cudaSuccess ? DTF_OK : DTF_ERR_CUDA;
 }
 
@@ -396,7 +400,7 @@ extern "C" int dtf_conv_wgrad(DtfConvWgrad* p, cudaStream_t stream) {
         set = 1;
     }
     dim3 grid(gx, ny);
-    conv_wgrad_kernel<<<grid, kThreads, smem_bytes, stream>>>(*p);
+    dtf_launch(conv_wgrad_kernel, grid, dim3(kThreads), smem_bytes, stream, *p);
     return cudaGetLastError() == cudaSuccess ? DTF_OK : DTF_ERR_CUDA;
 }
 

@@ -34,6 +34,8 @@ __global__ void __launch_bounds__(256)
 bn_bwd_apply_kernel(const dtf_bf16* __restrict__ t, const dtf_bf16* __restrict__ x,
                     const dtf_bf16* __restrict__ res, dtf_bf16* __restrict__ out,
                     DtfBnRef bn, const float* __restrict__ bwd_stats, long long total_vec, int C) {
+    griddep_launch_dependents();
+    griddep_wait();
     __shared__ float p0[256], p1[256], p2[256];
     for (int c = threadIdx.x; c < C; c += blockDim.x) {
         float scale, shift, mean, invstd;
@@ -72,6 +74,8 @@ constexpr int kMaxClasses = 16;
 
 __global__ void __launch_bounds__(kHeadThreads)
 head_kernel(const __grid_constant__ DtfHead P) {
+    griddep_launch_dependents();
+    griddep_wait();
     constexpr int kMaxHeadC = 1024;
     __shared__ float s_scale[kMaxHeadC], s_shift[kMaxHeadC], s_mean[kMaxHeadC], s_invstd[kMaxHeadC];
     __shared__ float pooled[kMaxHeadC], gpool[kMaxHeadC], st1[kMaxHeadC], st2[kMaxHeadC];
@@ -259,6 +263,8 @@ optimizer_kernel(float* __restrict__ params, const float* __restrict__ grads,
                  const DtfOptSegment* __restrict__ segs, const int2* __restrict__ chunks,
                  const DtfHparams* __restrict__ hp_ptr, const long long* __restrict__ step_ptr,
                  float grad_scale) {
+    griddep_launch_dependents();
+    griddep_wait();
     __shared__ DtfHparams hp;
     if (threadIdx.x == 0) hp = *hp_ptr;
     __syncthreads();
@@ -296,6 +302,8 @@ optimizer_kernel(float* __restrict__ params, const float* __restrict__ grads,
 // the device-resident step counter — one launch at the start of every step
 __global__ void __launch_bounds__(256)
 step_begin_kernel(float4* __restrict__ zero, long long n_vec, long long* __restrict__ step_ptr, int bump) {
+    griddep_launch_dependents();
+    griddep_wait();
     const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n_vec;
          i += (long long)gridDim.x * blockDim.x)
@@ -326,6 +334,8 @@ __global__ void __launch_bounds__(256)
 preprocess_kernel(const uint8_t* __restrict__ images, const int* __restrict__ indices,
                   dtf_bf16* __restrict__ out, const int* __restrict__ crop_flip,
                   int H, int W, int C, int mode, unsigned long long seed, unsigned long long counter) {
+    griddep_launch_dependents();
+    griddep_wait();
     __shared__ float red[2][8];
     __shared__ float s_mean, s_inv;
     const int n = blockIdx.x;
@@ -396,13 +406,13 @@ extern "C" int dtf_bn_bwd_apply(const dtf_bf16* t, const dtf_bf16* x, const dtf_
     const long long total_vec = pixels * (C / 8);
     long long blocks = (total_vec + 255) / 256;
     if (blocks > 148 * 8) blocks = 148 * 8;
-    dtf::bn_bwd_apply_kernel<<<static_cast<int>(blocks), 256, 0, stream>>>(t, x, res, out, *bn, bwd_stats, total_vec, C);
+    dtf_launch(dtf::bn_bwd_apply_kernel, dim3(static_cast<int>(blocks)), dim3(256), 0, stream, t, x, res, out, *bn, bwd_stats, total_vec, C);
     return DTF_CHECK_LAUNCH();
 }
 
 extern "C" int dtf_head(const DtfHead* p, cudaStream_t stream) {
     if (p->C > 1024 || p->classes > dtf::kMaxClasses) return DTF_ERR_SHAPE;
-    dtf::head_kernel<<<p->batch, dtf::kHeadThreads, 0, stream>>>(*p);
+    dtf_launch(dtf::head_kernel, dim3(p->batch), dim3(dtf::kHeadThreads), 0, stream, *p);
     return DTF_CHECK_LAUNCH();
 }
 
@@ -416,8 +426,8 @@ extern "C" int dtf_optimizer_step(float* params, const float* grads, float* slot
                                   const DtfOptSegment* segs, const int* chunks, int n_chunks,
                                   const DtfHparams* hp, const long long* step, float grad_scale,
                                   cudaStream_t stream) {
-    dtf::optimizer_kernel<<<n_chunks, 256, 0, stream>>>(params, grads, slot0, slot1, pack, segs,
-                                                        reinterpret_cast<const int2*>(chunks), hp, step, grad_scale);
+    dtf_launch(dtf::optimizer_kernel, dim3(n_chunks), dim3(256), 0, stream, params, grads, slot0, slot1, pack, segs,
+               reinterpret_cast<const int2*>(chunks), hp, step, grad_scale);
     return DTF_CHECK_LAUNCH();
 }
 
@@ -427,7 +437,7 @@ extern "C" int dtf_step_begin(float* zero_base, long long zero_floats, long long
     long long blocks = (n_vec + 255) / 256;
     if (blocks > 148 * 4) blocks = 148 * 4;
     if (blocks < 1) blocks = 1;
-    dtf::step_begin_kernel<<<static_cast<int>(blocks), 256, 0, stream>>>(reinterpret_cast<float4*>(zero_base), n_vec, step, bump);
+    dtf_launch(dtf::step_begin_kernel, dim3(static_cast<int>(blocks)), dim3(256), 0, stream, reinterpret_cast<float4*>(zero_base), n_vec, step, bump);
     return DTF_CHECK_LAUNCH();
 }
 
@@ -443,6 +453,6 @@ extern "C" int dtf_preprocess(const uint8_t* images, const int* indices, dtf_bf1
                               int n, int H, int W, int C, int mode, unsigned long long seed,
                               unsigned long long counter, cudaStream_t stream) {
     if (C > 8 || n < 1) return DTF_ERR_SHAPE;
-    dtf::preprocess_kernel<<<n, 256, 0, stream>>>(images, indices, out, crop_flip, H, W, C, mode, seed, counter);
+    dtf_launch(dtf::preprocess_kernel, dim3(n), dim3(256), 0, stream, images, indices, out, crop_flip, H, W, C, mode, seed, counter);
     return DTF_CHECK_LAUNCH();
 }

@@ -74,6 +74,8 @@ gemm_kernel(const __grid_constant__ DtfGemm P) {
         mbar_fence_init();
     }
     if (warp == 4) tmem_alloc(smem_u32(&hdr->tmem_base), 128);
+    griddep_launch_dependents();
+    griddep_wait();
     tc_fence_before_sync();
     __syncthreads();
     tc_fence_after_sync();
@@ -161,6 +163,8 @@ gemm_kernel(const __grid_constant__ DtfGemm P) {
 // ---------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
 maxpool_fwd_kernel(const dtf_bf16* __restrict__ x, dtf_bf16* __restrict__ y, int NB, int H, int W, int C) {
+    griddep_launch_dependents();
+    griddep_wait();
     const int Ho = H / 2, Wo = W / 2, cv = C / 8;
     const long long total = static_cast<long long>(NB) * Ho * Wo * cv;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
@@ -190,6 +194,8 @@ maxpool_fwd_kernel(const dtf_bf16* __restrict__ x, dtf_bf16* __restrict__ y, int
 __global__ void __launch_bounds__(256)
 maxpool_bwd_kernel(const dtf_bf16* __restrict__ x, const dtf_bf16* __restrict__ y, const dtf_bf16* __restrict__ gy,
                    dtf_bf16* __restrict__ gx, float* __restrict__ db, int NB, int H, int W, int C) {
+    griddep_launch_dependents();
+    griddep_wait();
     extern __shared__ float s_db[];
     for (int c = threadIdx.x; c < C; c += blockDim.x) s_db[c] = 0.f;
     __syncthreads();
@@ -237,6 +243,8 @@ maxpool_bwd_kernel(const dtf_bf16* __restrict__ x, const dtf_bf16* __restrict__ 
 __global__ void __launch_bounds__(256)
 act_mask_kernel(const dtf_bf16* __restrict__ g_in, const dtf_bf16* __restrict__ act, dtf_bf16* __restrict__ g_out,
                 float* __restrict__ db, float scale, long long rows, int C) {
+    griddep_launch_dependents();
+    griddep_wait();
     const int cv = C / 8;
     const int c8 = blockIdx.x * blockDim.x + threadIdx.x;          // one thread = one 8-channel column strip
     if (c8 >= cv) return;
@@ -275,7 +283,7 @@ extern "C" int dtf_gemm(const DtfGemm* p, cudaStream_t stream) {
         set = 1;
     }
     dim3 grid((p->M + kBM - 1) / kBM, (p->N + kBN - 1) / kBN);
-    gemm_kernel<<<grid, kGThreads, smem_bytes, stream>>>(*p);
+    dtf_launch(gemm_kernel, grid, dim3(kGThreads), smem_bytes, stream, *p);
     return DTF_CHECK_LAUNCH();
 }
 
@@ -284,7 +292,7 @@ extern "C" int dtf_maxpool_fwd(const dtf_bf16* x, dtf_bf16* y, int NB, int H, in
     const long long total = static_cast<long long>(NB) * (H / 2) * (W / 2) * (C / 8);
     long long blocks = (total + 255) / 256;
     if (blocks > 148 * 8) blocks = 148 * 8;
-    dtf::maxpool_fwd_kernel<<<static_cast<int>(blocks < 1 ? 1 : blocks), 256, 0, stream>>>(x, y, NB, H, W, C);
+    dtf_launch(dtf::maxpool_fwd_kernel, dim3(static_cast<int>(blocks < 1 ? 1 : blocks)), dim3(256), 0, stream, x, y, NB, H, W, C);
     return DTF_CHECK_LAUNCH();
 }
 
@@ -294,7 +302,7 @@ extern "C" int dtf_maxpool_bwd(const dtf_bf16* x, const dtf_bf16* y, const dtf_b
     const long long total = static_cast<long long>(NB) * (H / 2) * (W / 2) * (C / 8);
     long long blocks = (total + 255) / 256;
     if (blocks > 148 * 4) blocks = 148 * 4;
-    dtf::maxpool_bwd_kernel<<<static_cast<int>(blocks < 1 ? 1 : blocks), 256, C * sizeof(float), stream>>>(x, y, gy, gx, db, NB, H, W, C);
+    dtf_launch(dtf::maxpool_bwd_kernel, dim3(static_cast<int>(blocks < 1 ? 1 : blocks)), dim3(256), C * sizeof(float), stream, x, y, gy, gx, db, NB, H, W, C);
     return DTF_CHECK_LAUNCH();
 }
 
@@ -303,6 +311,6 @@ extern "C" int dtf_act_mask(const dtf_bf16* g_in, const dtf_bf16* act, dtf_bf16*
     if (C & 7) return DTF_ERR_SHAPE;
     const int cv = C / 8;
     dim3 grid((cv + 127) / 128, static_cast<unsigned>(rows < 64 ? (rows < 1 ? 1 : rows) : 64));
-    dtf::act_mask_kernel<<<grid, 128, 0, stream>>>(g_in, act, g_out, db, scale, rows, C);
+    dtf_launch(dtf::act_mask_kernel, grid, dim3(128), 0, stream, g_in, act, g_out, db, scale, rows, C);
     return DTF_CHECK_LAUNCH();
 }

@@ -44,6 +44,7 @@ class NativeEngineBase:
         self._pp_counter = 0
         self._seed = seed
         self._count = 0
+        self._side = None                       # side stream for independent kernels (engine-specific use)
 
     # ------------------------------------------------------------------ memory
     def _finish_segments(self) -> None:

@@ -268,6 +268,22 @@ class NativeResNetEngine(NativeEngineBase):
                          epi_stats_out=self._stats_out(stats_for) if training else None)
         self._count += 1
 
+    # -- independent kernels (projection shortcut, strided-conv weight gradient) run on a side stream: every
+    #    kernel here is a latency chain (launch -> BN constants -> first tile -> tail), so a second chain in
+    #    flight hides a good part of it.  Inside CUDA-graph capture the fork/join become graph branches.
+    def _fork(self):
+        if self._side is None:
+            self._side = torch.cuda.Stream(device=self.device)
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream())
+        self._side.wait_event(ev)
+        return torch.cuda.stream(self._side)
+
+    def _join(self) -> None:
+        ev = torch.cuda.Event()
+        ev.record(self._side)
+        torch.cuda.current_stream().wait_event(ev)
+
     def _forward(self, nb: int, training: bool) -> torch.Tensor:
         """Runs the trunk; returns the tensor feeding the final BN."""
         self._fwd_conv(self.conv0, self.image, self.r0, nb, bn=None, training=training, update=False,
@@ -276,8 +292,11 @@ class NativeResNetEngine(NativeEngineBase):
         for i, (b, a) in enumerate(zip(self.blocks, self.acts)):
             nxt = self.blocks[i + 1].bn1 if i + 1 < len(self.blocks) else self.bn_final
             if b.proj:
-                self._fwd_conv(b.proj, x, a["sc"], nb, bn=b.bn1, training=training, update=False)
+                with self._fork():
+                    self._fwd_conv(b.proj, x, a["sc"], nb, bn=b.bn1, training=training, update=False)
             self._fwd_conv(b.conv1, x, a["c1"], nb, bn=b.bn1, training=training, update=True, stats_for=b.bn2)
+            if b.proj:
+                self._join()
             self._fwd_conv(b.conv2, a["c1"], a["out"], nb, bn=b.bn2, training=training, update=True,
                            res=a["sc"] if b.proj else x, stats_for=nxt)
             x = a["out"]
@@ -333,8 +352,10 @@ class NativeResNetEngine(NativeEngineBase):
         """Weight gradient + input gradient of one conv.  3x3 / stride-1 layers go out as ONE launch
         (dgrad CTAs and wgrad CTAs share the grid); the others as two."""
         if not (c.k == 3 and c.stride == 1 and c.cin == c.cout):
-            self._wgrad(c, x_src, x_bn, gy_src, nb, gy_bn=gy_bn, gy_x=gy_x)
+            with self._fork():
+                self._wgrad(c, x_src, x_bn, gy_src, nb, gy_bn=gy_bn, gy_x=gy_x)
             self._dgrad(c, gy_src, nb, out, mask_x=mask_x, mask_bn=mask_bn, gy_bn=gy_bn, gy_x=gy_x)
+            self._join()
             return
         pro = native.PRO_BN_BWD if gy_bn else native.PRO_NONE
         bn_gy = self._bn(gy_bn, nb, True) if gy_bn else None
@@ -364,9 +385,12 @@ class NativeResNetEngine(NativeEngineBase):
             b, a = self.blocks[i], self.acts[i]
             x_in = self.acts[i - 1]["out"] if i > 0 else self.r0
             t2, t1 = self.tbuf[0], self.tbuf[1]
+            if b.proj:
+                with self._fork():
+                    self._wgrad(b.proj, x_in, b.bn1, g_out, nb)
             self._bwd_conv(b.conv2, a["c1"], b.bn2, g_out, nb, t2, mask_x=a["c1"], mask_bn=b.bn2)
             if b.proj:
-                self._wgrad(b.proj, x_in, b.bn1, g_out, nb)
+                self._join()
             self._bwd_conv(b.conv1, x_in, b.bn1, t2, nb, t1, mask_x=x_in, mask_bn=b.bn1, gy_bn=b.bn2, gy_x=a["c1"])
             if b.proj:
                 self._dgrad(b.proj, g_out, nb, t1, mask_x=x_in, mask_bn=b.bn1, accumulate=True)
