@@ -529,16 +529,8 @@ static dtf::FastDiv make_fastdiv(uint32_t d) {
     return f;
 }
 
-static int halo_sms() {
-    static int n = 0;
-    if (n == 0) {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
-        if (n <= 0) n = 148;
-    }
-    return n;
-}
+extern "C" int dtf_sm_count();
+static int halo_sms() { return dtf_sm_count(); }
 
 static bool halo_disabled() {
     static int v = -1;

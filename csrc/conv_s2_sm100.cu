@@ -306,6 +306,8 @@ conv_dgrad_s2_kernel(const __grid_constant__ DtfConvGemm P) {
 
 }  // namespace dtf
 
+extern "C" int dtf_sm_count();
+
 // Returns 1 = launched, 0 = not applicable (caller falls back to the dense transposed gather), < 0 = error.
 // `p->a` has been through prep_gather and p->kchunks is set.
 extern "C" int dtf_conv_s2_dgrad_try(const DtfConvGemm* p, cudaStream_t stream) {
@@ -338,13 +340,7 @@ extern "C" int dtf_conv_s2_dgrad_try(const DtfConvGemm* p, cudaStream_t stream) 
         }
         set = 1;
     }
-    static int sms = 0;
-    if (sms == 0) {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        if (sms <= 0) sms = 148;
-    }
+    const int sms = dtf_sm_count();
     const int Mc = q.NB * (q.Ho / 2) * (q.Wo / 2);
     const int tiles = (k3 ? 4 : 1) * ((Mc + kTileM - 1) / kTileM);
     const int grid = tiles < sms ? tiles : sms;

@@ -290,16 +290,24 @@ conv_wgrad_kernel(const __grid_constant__ DtfConvWgrad P) {
 // =========================================================================================
 // host launchers (C ABI)
 // =========================================================================================
-static int g_num_sms = 0;
-static int num_sms() {
+// SMs the persistent kernels may occupy.  Default: all of them.  A worker that trains several members at
+// once on one GPU lowers it (dtf_set_sm_limit) so that the members' kernels run side by side instead of
+// queueing CTA by CTA; the value in force when a CUDA graph is captured is baked into that graph.
+static int g_num_sms = 0, g_sm_limit = 0;
+extern "C" int dtf_sm_count() {
     if (g_num_sms == 0) {
         int dev = 0;
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
         if (g_num_sms <= 0) g_num_sms = 148;
     }
-    return g_num_sms;
+    return (g_sm_limit > 0 && g_sm_limit < g_num_sms) ? g_sm_limit : g_num_sms;
 }
+extern "C" int dtf_set_sm_limit(int n) {
+    g_sm_limit = n > 0 ? n : 0;
+    return dtf_sm_count();
+}
+static int num_sms() { return dtf_sm_count(); }
 
 static int ilog2_exact(int v) {
     int s = 0;

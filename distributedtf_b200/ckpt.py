@@ -162,3 +162,94 @@ def load_checkpoint(save_dir: str) -> Optional[Tuple[Dict[str, np.ndarray], Dict
         seg = raw[e["offset"]: e["offset"] + e["nbytes"]]
         out[name] = seg.view(dt).reshape(e["shape"]).copy()
     return out, index
+
+
+# ----------------------------------------------------------------------------------------------
+# Asynchronous save of a native engine's state arena (csrc/host_io.cpp)
+# ----------------------------------------------------------------------------------------------
+class AsyncCheckpointWriter:
+    """Round-end checkpoints that do not stall training: one async device->host copy of the member's state
+    region into a pinned staging slot, then a job for the native writer threads (data file, index, pointer, each
+    via temp file + rename).  Same on-disk format as ``save_checkpoint``; ``wait`` / ``wait_all`` are the
+    barriers restore, the file-exploit path and shutdown use.  (Reference: synchronous ``saver.save`` after
+    every train call, mnist_model.py / resnet_run_loop.py.)"""
+
+    def __init__(self, threads: int = 4, staging_slots: int = 4):
+        import threading
+        from .ops import native
+        self._lib = native.lib()
+        self._h = self._lib.dtf_io_create(int(threads))
+        self._slots = [{"buf": None, "ticket": 0} for _ in range(max(1, staging_slots))]
+        self._next = 0
+        self._lock = threading.Lock()
+
+    def save_state(self, save_dir: str, state, views: Mapping[str, Any], *, step: int, optimizer: str = "",
+                   meta: Optional[Dict[str, Any]] = None) -> int:
+        """``state``: contiguous uint8 CUDA tensor; ``views``: name -> tensor view inside it."""
+        import torch
+        os.makedirs(save_dir, exist_ok=True)
+        base, total = state.data_ptr(), state.numel()
+        entries: Dict[str, Dict[str, Any]] = {}
+        for name, t in views.items():
+            nbytes = t.numel() * t.element_size()
+            off = t.data_ptr() - base if nbytes else 0       # empty views (e.g. no BN statistics) carry no pointer
+            if off < 0 or off + nbytes > total or not t.is_contiguous():
+                raise ValueError(f"{name} is not a contiguous view of the state region")
+            entries[name] = {"offset": int(off), "shape": list(t.shape), "dtype": str(t.dtype).replace("torch.", ""),
+                             "nbytes": int(nbytes)}
+        index = {"version": FORMAT_VERSION, "step": int(step), "optimizer": optimizer, "total_bytes": int(total),
+                 "entries": entries, "meta": meta or {}}
+        with self._lock:
+            slot = self._slots[self._next]
+            self._next = (self._next + 1) % len(self._slots)
+            if slot["ticket"]:
+                self._lib.dtf_io_wait(self._h, slot["ticket"])          # the slot's previous job is on disk
+            if slot["buf"] is None or slot["buf"].numel() < total:
+                slot["buf"] = torch.empty(total, dtype=torch.uint8, pin_memory=state.is_cuda)
+            host = slot["buf"][:total]
+            host.copy_(state, non_blocking=True)
+            pointer = (f'model_checkpoint_path: "{CKPT_PREFIX}"\n'
+                       f'all_model_checkpoint_paths: "{CKPT_PREFIX}"\n')
+            ticket = self._lib.dtf_io_submit(
+                self._h, os.path.join(save_dir, CKPT_PREFIX + ".data").encode(), host.data_ptr(), total,
+                torch.cuda.current_stream(state.device).cuda_stream if state.is_cuda else None,
+                (state.device.index or 0) if state.is_cuda else -1,
+                os.path.join(save_dir, CKPT_PREFIX + ".index").encode(),
+                json.dumps(index, indent=1, sort_keys=True).encode(),
+                os.path.join(save_dir, POINTER_FILE).encode(), pointer.encode())
+            if ticket <= 0:
+                raise RuntimeError(f"dtf_io_submit failed: {ticket}")
+            slot["ticket"] = ticket
+            return int(ticket)
+
+    def wait(self, ticket: int) -> None:
+        if ticket and self._lib.dtf_io_wait(self._h, int(ticket)) != 0:
+            raise RuntimeError("checkpoint writer reported a failed write (see stderr)")
+
+    def wait_all(self) -> None:
+        if self._lib.dtf_io_wait_all(self._h) != 0:
+            raise RuntimeError("checkpoint writer reported a failed write (see stderr)")
+
+    def pending(self) -> int:
+        return int(self._lib.dtf_io_pending(self._h))
+
+    def bytes_written(self) -> int:
+        return int(self._lib.dtf_io_bytes_written(self._h))
+
+    def close(self) -> None:
+        if self._h:
+            self._lib.dtf_io_destroy(self._h)
+            self._h = None
+
+
+_WRITER: Optional[AsyncCheckpointWriter] = None
+
+
+def async_writer() -> AsyncCheckpointWriter:
+    """Process-wide writer (created on first use; drained at interpreter exit)."""
+    global _WRITER
+    if _WRITER is None:
+        import atexit
+        _WRITER = AsyncCheckpointWriter()
+        atexit.register(lambda: _WRITER is not None and _WRITER._h and _WRITER.wait_all())
+    return _WRITER

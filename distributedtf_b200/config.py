@@ -32,6 +32,9 @@ class RunConfig:
     master_addr: str = "127.0.0.1"
     master_port: int = 29611
     dp_size: int = 1                      # GPUs per member (1 | 2 | 4)
+    members_in_flight: int = 1            # members of one worker trained concurrently (own stream + host thread)
+    sm_limit: int = 0                     # > 0: SMs a member's persistent kernels occupy (0 = all)
+    async_checkpoint: Optional[bool] = None   # None: on unless exploit_path == 'file' (native engines only)
     # --- data plane ---
     exploit_path: str = "file"            # file | p2p | nccl | host
     scoreboard: bool = False              # eval scores reach the master through the device score board
@@ -97,6 +100,10 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--master-addr", default="127.0.0.1")
     p.add_argument("--master-port", type=int, default=29611)
     p.add_argument("--dp-size", type=int, choices=[1, 2, 4], default=1)
+    p.add_argument("--members-in-flight", type=int, default=1,
+                   help="members of one worker trained at once (own stream + host thread each)")
+    p.add_argument("--async-checkpoint", action=argparse.BooleanOptionalAction, default=None)
+    p.add_argument("--sm-limit", type=int, default=0, help="SMs a member's persistent kernels occupy (0 = all)")
     p.add_argument("--exploit-path", choices=["file", "p2p", "nccl", "host"], default="file")
     p.add_argument("--scoreboard", action="store_true", help="rank by the device-side score board")
     p.add_argument("--engine", choices=["auto", "native", "eager"], default="auto")

@@ -63,6 +63,8 @@ def model_kwargs(cfg: RunConfig, dp_group=None, dp_rank: int = 0) -> Dict[str, A
         from .utils.logs import hooks as _hooks
         kw["hooks"] = _hooks.get_train_hooks(cfg.hooks, model_dir=cfg.save_root, batch_size=128)
     kw["benchmark"] = (cfg.benchmark_logger_type, cfg.benchmark_log_dir)
+    # the file-exploit path copies checkpoint files right after GET: keep those saves synchronous
+    kw["async_checkpoint"] = cfg.async_checkpoint if cfg.async_checkpoint is not None else cfg.exploit_path != "file"
     return kw
 
 
@@ -112,7 +114,8 @@ def run_worker(cfg: RunConfig, comm, dp_group=None, mirror=None) -> TrainingWork
     worker = TrainingWorker(comm, cfg.master_rank, get_model_class(cfg.target_model),
                             save_base_dir=os.path.join(cfg.save_root, "model_"),
                             verbose=cfg.verbose, model_kwargs=model_kwargs(cfg, dp_group, 0),
-                            fault_hook=_fault_hook(cfg), mirror=mirror)
+                            fault_hook=_fault_hook(cfg), mirror=mirror,
+                            members_in_flight=cfg.members_in_flight, sm_limit=cfg.sm_limit)
     if cfg.seed is not None:
         random.seed(cfg.seed * 1000003 + comm.Get_rank())
     worker.main_loop()
@@ -129,15 +132,21 @@ def run_local(cfg: RunConfig) -> Dict[str, Any]:
     def guard(fn, *a):
         try:
             fn(*a)
-        except BaseException as e:  # surfaced after join
+        except BaseException as e:  # surfaced after join; unblocks the master's recv
             errors.append(e)
+            fabric.abort(e)
 
     threads = [threading.Thread(target=guard, args=(run_worker, cfg, fabric.endpoint(r)),
                                 name=f"dtf-worker{r}", daemon=True)
                for r in range(1, cfg.workers + 1)]
     for t in threads:
         t.start()
-    result = run_master(cfg, fabric.endpoint(0), board)
+    try:
+        result = run_master(cfg, fabric.endpoint(0), board)
+    except RuntimeError:
+        if errors:
+            raise errors[0]
+        raise
     for t in threads:
         t.join(timeout=60)
     if errors:

@@ -52,7 +52,7 @@ class GpuMember(ModelBase):
                  eval_batches: Optional[int] = None, resume: bool = False,
                  synthetic_mode: str = "random", device: Optional[torch.device] = None,
                  hooks: Optional[List[Any]] = None, dp_group=None, dp_rank: int = 0, dp_size: int = 1,
-                 scoreboard: Optional[Dict[str, Any]] = None, benchmark=None, **_):
+                 scoreboard: Optional[Dict[str, Any]] = None, benchmark=None, async_checkpoint: bool = False, **_):
         super().__init__(cluster_id, hparams, save_base_dir)
         self.device = device or pick_device()
         self.dp_group, self.dp_rank, self.dp_size = dp_group, int(dp_rank), int(dp_size)
@@ -67,6 +67,8 @@ class GpuMember(ModelBase):
         self.device_times: Dict[str, float] = {"train": 0.0, "eval": 0.0, "exploit": 0.0}
         self.hooks = list(hooks or [])          # utils.logs.hooks.Hook objects, called once per step
         self._bench_logger = None
+        self.async_checkpoint = bool(async_checkpoint)   # native engines: save through the background writer
+        self._ckpt_ticket = 0
         if benchmark and benchmark[0] == "BenchmarkFileLogger" and benchmark[1]:
             from ..utils.logs import logger as _logger
             self._bench_logger = _logger.BenchmarkFileLogger(os.path.join(benchmark[1], f"model_{cluster_id}"))
@@ -266,8 +268,21 @@ class GpuMember(ModelBase):
                 self.engine.set_hparams(self.hparams, keep_slots=True) if hasattr(self.engine, "adopt_hparams") \
                     else self.engine.set_hparams(self.hparams)
 
+    def flush_io(self) -> None:
+        """Barrier for a checkpoint handed to the background writer."""
+        t, self._ckpt_ticket = self._ckpt_ticket, 0
+        if t:
+            ckpt.async_writer().wait(t)
+
     def save(self) -> None:
         self.flush_exploit()
+        meta = {"model": type(self).__name__, "engine": self.engine_kind, "epoches_trained": self.epoches_trained}
+        if self.async_checkpoint and self.device.type == "cuda" and hasattr(self.engine, "state"):
+            self.flush_io()
+            self._ckpt_ticket = ckpt.async_writer().save_state(
+                self.ensure_dir(), self.engine.state, self.engine.state_tensors(), step=self.engine.step,
+                optimizer=self.hparams["opt_case"]["optimizer"], meta=meta)
+            return
         self.engine.synchronize()
         ckpt.save_checkpoint(self.ensure_dir(), self.engine.state_tensors(), step=self.engine.step,
                              optimizer=self.hparams["opt_case"]["optimizer"],
@@ -275,6 +290,7 @@ class GpuMember(ModelBase):
                                    "epoches_trained": self.epoches_trained})
 
     def restore(self) -> bool:
+        self.flush_io()
         loaded = ckpt.load_checkpoint(self.save_dir)
         if loaded is None:
             return False
@@ -299,7 +315,12 @@ class GpuMember(ModelBase):
         with self._timed("exploit"):
             exploit.donate(self, extras)
 
+    def drop(self) -> None:
+        self.flush_io()
+        super().drop()
+
     def close(self) -> None:
+        self.flush_io()
         closer = getattr(self.engine, "close", None)
         if closer:
             closer()

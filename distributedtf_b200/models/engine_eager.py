@@ -124,4 +124,4 @@ class EagerEngine:
 
     def synchronize(self) -> None:
         if self.device.type == "cuda":
-            torch.cuda.synchronize(self.device)
+            torch.cuda.current_stream(self.device).synchronize()

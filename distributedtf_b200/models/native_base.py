@@ -13,6 +13,7 @@ its activations, and implements ``_train_kernels`` / ``_eval_kernels`` as a sequ
 from __future__ import annotations
 
 import ctypes as C
+import threading
 from typing import Any, Dict, List, Optional, Tuple
 
 import torch
@@ -22,6 +23,43 @@ from ..ops import native, reference
 
 def _align(n: int, a: int = 256) -> int:
     return (n + a - 1) // a * a
+
+
+class _StepGate:
+    """Steps of different members (threads) run concurrently; a CUDA-graph capture runs alone."""
+
+    def __init__(self):
+        self._cv = threading.Condition()
+        self._active = 0
+        self._capturing = False
+
+    def enter_step(self) -> None:
+        with self._cv:
+            while self._capturing:
+                self._cv.wait()
+            self._active += 1
+
+    def exit_step(self) -> None:
+        with self._cv:
+            self._active -= 1
+            if self._active == 0:
+                self._cv.notify_all()
+
+    def enter_capture(self) -> None:
+        with self._cv:
+            while self._capturing:
+                self._cv.wait()
+            self._capturing = True
+            while self._active > 0:
+                self._cv.wait()
+
+    def exit_capture(self) -> None:
+        with self._cv:
+            self._capturing = False
+            self._cv.notify_all()
+
+
+_GATE = _StepGate()
 
 
 class NativeEngineBase:
@@ -191,16 +229,26 @@ class NativeEngineBase:
         key = (kind, nb)
         g = self._graphs.get(key)
         if g is None:
-            fn()                                   # first use: a plain run (sets kernel attributes) ...
-            torch.cuda.synchronize(self.device)
-            g = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(g):              # ... then capture for every later step of this batch size
-                fn()
+            # One capture at a time per process, with no other member's step in flight, in thread-local error
+            # mode (other members may still be evaluating / saving on their own streams and threads).
+            _GATE.enter_capture()
+            try:
+                fn()                               # first use: a plain run (sets kernel attributes) ...
+                torch.cuda.current_stream(self.device).synchronize()
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, capture_error_mode="thread_local"):   # ... then capture
+                    fn()
+            finally:
+                _GATE.exit_capture()
             self._graphs[key] = g
             if len(self._graphs) > 16:
                 self._graphs.pop(next(iter(self._graphs)))
             return                                 # the plain run already performed this step
-        g.replay()
+        _GATE.enter_step()
+        try:
+            g.replay()
+        finally:
+            _GATE.exit_step()
 
     def load_batch(self, images_u8: torch.Tensor, labels: torch.Tensor) -> int:
         nb = int(images_u8.shape[0])
@@ -261,7 +309,11 @@ class NativeEngineBase:
         self.repack()
 
     def synchronize(self) -> None:
-        torch.cuda.synchronize(self.device)
+        # stream-scoped on purpose: a device-wide synchronize is illegal while another member's thread is
+        # capturing a CUDA graph (worker.members_in_flight) and would invalidate that capture
+        torch.cuda.current_stream(self.device).synchronize()
+        if self._side is not None:
+            self._side.synchronize()
 
     def close(self) -> None:
         self._graphs.clear()

@@ -9,6 +9,7 @@ from __future__ import annotations
 
 import ctypes as C
 import os
+import threading
 from typing import Any, Optional, Sequence
 
 import torch
@@ -35,14 +36,22 @@ def available() -> bool:
     return os.path.isfile(LIB_PATH)
 
 
+_lib_lock = threading.Lock()
+
+
 def lib() -> C.CDLL:
     global _lib
     if _lib is None:
-        if not available():
-            raise NativeError(f"{LIB_PATH} is missing: run `python build_native.py` "
-                              "(or __graft_entry__.build()) before using the native engine")
-        _lib = C.CDLL(os.path.abspath(LIB_PATH))
-        _declare(_lib)
+        with _lib_lock:                      # published only after its signatures are declared
+            if _lib is None:
+                if not available():
+                    raise NativeError(f"{LIB_PATH} is missing: run `python build_native.py` "
+                                      "(or __graft_entry__.build()) before using the native engine")
+                l = C.CDLL(os.path.abspath(LIB_PATH))
+                _declare(l)
+                if os.environ.get("DTF_CRASH_BT"):
+                    l.dtf_install_crash_handler()
+                _lib = l
     return _lib
 
 
@@ -135,6 +144,19 @@ def _declare(l: C.CDLL) -> None:
     l.dtf_maxpool_fwd.argtypes = [vp, vp, i, i, i, i, vp]
     l.dtf_maxpool_bwd.argtypes = [vp, vp, vp, vp, vp, i, i, i, i, vp]
     l.dtf_act_mask.argtypes = [vp, vp, vp, vp, f, ll, i, vp]
+    l.dtf_set_sm_limit.argtypes = [i]
+    l.dtf_io_create.argtypes = [i]
+    l.dtf_io_create.restype = vp
+    l.dtf_io_submit.argtypes = [vp, C.c_char_p, vp, C.c_ulonglong, vp, i, C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p]
+    l.dtf_io_submit.restype = ll
+    l.dtf_io_wait.argtypes = [vp, ll]
+    l.dtf_io_wait_all.argtypes = [vp]
+    l.dtf_io_pending.argtypes = [vp]
+    l.dtf_io_bytes_written.argtypes = [vp]
+    l.dtf_io_bytes_written.restype = ll
+    l.dtf_io_destroy.argtypes = [vp]
+    l.dtf_io_destroy.restype = None
+    l.dtf_sm_count.argtypes = []
     for name in ("dtf_gemm", "dtf_maxpool_fwd", "dtf_maxpool_bwd", "dtf_act_mask"):
         getattr(l, name).restype = i
     for name in ("dtf_conv_gemm", "dtf_conv_wgrad", "dtf_bn_bwd_apply", "dtf_head", "dtf_pack_weights",
@@ -241,6 +263,15 @@ def optimizer_step(params, grads, slot0, slot1, pack, segs_dev, chunks_dev, n_ch
 def step_begin(zero_region: torch.Tensor, step_dev: torch.Tensor, bump: bool = True) -> None:
     n = zero_region.numel() * zero_region.element_size() // 4
     check(lib().dtf_step_begin(ptr(zero_region), n, ptr(step_dev), int(bump), stream_ptr()), "dtf_step_begin")
+
+
+def set_sm_limit(n: int) -> int:
+    """SMs the persistent kernels occupy from now on (0 = all); baked into CUDA graphs captured afterwards."""
+    return int(lib().dtf_set_sm_limit(int(n)))
+
+
+def sm_count() -> int:
+    return int(lib().dtf_sm_count())
 
 
 def fill(t: torch.Tensor, value: float) -> None:

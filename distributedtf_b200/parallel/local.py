@@ -26,6 +26,11 @@ class LocalFabric:
         self._delay_fn = delay_fn  # optional fault/latency injection: f(src, dst) -> seconds
         self.sent = 0
         self._lock = threading.Lock()
+        self._aborted: Optional[BaseException] = None
+
+    def abort(self, exc: BaseException) -> None:
+        """An endpoint's thread died: every blocked or future ``recv`` raises instead of waiting forever."""
+        self._aborted = exc
 
     def endpoint(self, rank: int) -> "LocalComm":
         if not 0 <= rank < self.size:
@@ -42,10 +47,18 @@ class LocalFabric:
         self._queues[(src, dst)].put(payload)
 
     def _get(self, src: int, dst: int, timeout: Optional[float]) -> bytes:
-        try:
-            return self._queues[(src, dst)].get(timeout=timeout)
-        except queue.Empty:
-            raise CommTimeout(f"endpoint {dst}: no message from {src} within {timeout}s") from None
+        deadline = None if timeout is None else time.monotonic() + timeout
+        q = self._queues[(src, dst)]
+        while True:                                # short polls so that abort() is noticed
+            if self._aborted is not None:
+                raise RuntimeError(f"fabric aborted: {self._aborted!r}") from self._aborted
+            left = 0.25 if deadline is None else min(0.25, deadline - time.monotonic())
+            if left <= 0:
+                raise CommTimeout(f"endpoint {dst}: no message from {src} within {timeout}s")
+            try:
+                return q.get(timeout=left)
+            except queue.Empty:
+                continue
 
 
 class LocalComm(Comm):

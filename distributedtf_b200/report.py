@@ -46,6 +46,11 @@ def dump_population(path: str, all_values: List[List[Any]]) -> None:
 
 
 def dump_best(path: str, all_values: List[List[Any]]) -> Dict[str, Any]:
+    if not all_values:                     # every member was dropped (NaN / exception)
+        doc = {"best_model_id": None, "best_acc": float("nan"), "best_hparams": None}
+        with open(path, "w") as f:
+            json.dump(doc, f, indent=4, sort_keys=True)
+        return doc
     best = sorted(all_values, key=lambda v: v[1])[-1]
     doc = {"best_model_id": best[0], "best_acc": float(best[1]), "best_hparams": best[2]}
     with open(path, "w") as f:

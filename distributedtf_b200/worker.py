@@ -26,7 +26,8 @@ class TrainingWorker:
     def __init__(self, comm, master_rank: int, target_model_class: Callable[..., Any], *,
                  save_base_dir: str = "./savedata/model_", verbose: bool = True,
                  model_kwargs: Optional[Dict[str, Any]] = None,
-                 fault_hook: Optional[Callable[[Any, int], None]] = None, mirror=None):
+                 fault_hook: Optional[Callable[[Any, int], None]] = None, mirror=None,
+                 members_in_flight: int = 1, sm_limit: int = 0):
         self.worker_graphs: List[Any] = []
         self.is_expolore_only = False          # (sic) reference attribute name
         self.rank = comm.Get_rank()
@@ -38,6 +39,11 @@ class TrainingWorker:
         self.model_kwargs = dict(model_kwargs or {})
         self.fault_hook = fault_hook           # test hook: f(member, round) may raise / poison
         self.mirror = mirror                   # DP group leader: callable(msg) that forwards to the followers
+        # > 1: that many members of this worker train at once, each on its own CUDA stream and host thread,
+        # (The reference trains them one after the other, training_worker.py:60-75.)
+        self.members_in_flight = max(1, int(members_in_flight))
+        self._member_streams: Dict[int, Any] = {}
+        self.sm_limit = int(sm_limit)          # > 0: SMs each member's persistent kernels occupy (default: all)
         self.train_time = 0.0
         self.explore_time = 0.0
         self.exploit_time = 0.0
@@ -80,6 +86,12 @@ class TrainingWorker:
     # ------------------------------------------------------------------ handlers
     def add_graphs(self, hparam_list: List[dict], id_begin: int) -> None:
         self._say("[{}]Got {} hparams".format(self.rank, len(hparam_list)))
+        if self.sm_limit > 0:       # baked into the members' CUDA graphs at capture
+            try:
+                from .ops import native
+                native.set_sm_limit(self.sm_limit)
+            except Exception:
+                pass
         for offset, hparam in enumerate(hparam_list):
             member = self.target_model_class(id_begin + offset, hparam, self.save_base_dir,
                                              **self.model_kwargs)
@@ -99,23 +111,52 @@ class TrainingWorker:
         except ImportError:
             pass
 
+    def _train_member(self, g, num_epoches: int, total_epochs: int) -> bool:
+        """Trains one member; returns False when it has to be dropped (exception or NaN score)."""
+        try:
+            if self.fault_hook is not None:
+                self.fault_hook(g, self.rounds_seen)
+            g.train(num_epoches, total_epochs)
+            self._say("Model {} epoch = {},  acc = {}".format(
+                g.cluster_id, g.epoches_trained, g.get_accuracy()))
+            acc = g.get_accuracy()
+            return not (isinstance(acc, float) and math.isnan(acc))
+        except Exception:  # member-level failure: drop it, keep the worker alive
+            if self.verbose:
+                traceback.print_exc()
+            return False
+
+    def _train_member_on_stream(self, g, num_epoches: int, total_epochs: int) -> bool:
+        import torch
+        dev = getattr(g, "device", None)
+        if dev is None or getattr(dev, "type", "cpu") != "cuda":
+            return self._train_member(g, num_epoches, total_epochs)
+        try:
+            torch.cuda.set_device(dev)
+            st = self._member_streams.get(g.cluster_id)
+            if st is None:
+                st = self._member_streams[g.cluster_id] = torch.cuda.Stream(device=dev)
+            st.wait_stream(torch.cuda.default_stream(dev))       # exploit / explore writes of the main thread
+            with torch.cuda.stream(st):
+                ok = self._train_member(g, num_epoches, total_epochs)
+            st.synchronize()
+            return ok
+        except Exception:
+            if self.verbose:
+                traceback.print_exc()
+            return False
+
     def train(self, num_epoches: int, total_epochs: int) -> None:
         t0 = time.time()
-        failed = []
-        for g in self.worker_graphs:
-            try:
-                if self.fault_hook is not None:
-                    self.fault_hook(g, self.rounds_seen)
-                g.train(num_epoches, total_epochs)
-                self._say("Model {} epoch = {},  acc = {}".format(
-                    g.cluster_id, g.epoches_trained, g.get_accuracy()))
-                acc = g.get_accuracy()
-                if isinstance(acc, float) and math.isnan(acc):
-                    failed.append(g)
-            except Exception:  # member-level failure: drop it, keep the worker alive
-                if self.verbose:
-                    traceback.print_exc()
-                failed.append(g)
+        k = min(self.members_in_flight, len(self.worker_graphs))
+        if k > 1:
+            from concurrent.futures import ThreadPoolExecutor
+            with ThreadPoolExecutor(max_workers=k, thread_name_prefix="dtf-member") as pool:
+                oks = list(pool.map(lambda g: self._train_member_on_stream(g, num_epoches, total_epochs),
+                                    list(self.worker_graphs)))
+        else:
+            oks = [self._train_member(g, num_epoches, total_epochs) for g in list(self.worker_graphs)]
+        failed = [g for g, ok in zip(list(self.worker_graphs), oks) if not ok]
         for g in failed:
             self._say("Error occured , graph {} removed".format(g.cluster_id))
             self.dropped.append(g.cluster_id)

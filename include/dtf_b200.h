@@ -256,6 +256,32 @@ int dtf_maxpool_bwd(const dtf_bf16* x, const dtf_bf16* y, const dtf_bf16* gy, dt
 int dtf_act_mask(const dtf_bf16* g_in, const dtf_bf16* act, dtf_bf16* g_out, float* db, float scale,
                  long long rows, int C, cudaStream_t stream);
 
+/* SMs the persistent kernels occupy (default: all).  Lower it when several members train at once on one GPU
+ * so that their kernels run side by side; the value in force at CUDA-graph capture is baked into the graph.
+ * Returns the effective count.  (No reference counterpart: the reference trains a worker's members one by one,
+ * training_worker.py:60-75.) */
+int dtf_set_sm_limit(int n);
+int dtf_sm_count(void);
+
+/* ---- host runtime: background checkpoint writer (csrc/host_io.cpp) -------------------------------------
+ * Replaces the synchronous `saver.save(sess, ...)` the reference runs after every train call
+ * (mnist_model.py / cifar10 model, via TensorFlow's C++ Saver).  A job = wait until everything queued on
+ * `cuda_stream` of `device` at submit time has run (the caller's device->host copy into `host_ptr`; pass
+ * device = -1 for a host-only job), write `data_path`, then `index_path`, then
+ * `pointer_path`, each through a temp file + rename.  Strings are copied at submit; `host_ptr` must stay valid
+ * and unmodified until the ticket has been waited for.  Returns a ticket > 0 or a DTF_ERR_* code. */
+void* dtf_io_create(int threads);
+long long dtf_io_submit(void* writer, const char* data_path, const void* host_ptr, unsigned long long nbytes,
+                        void* cuda_stream, int device, const char* index_path, const char* index_text,
+                        const char* pointer_path, const char* pointer_text);
+int dtf_io_wait(void* writer, long long ticket);
+int dtf_io_wait_all(void* writer);
+int dtf_io_pending(void* writer);
+long long dtf_io_bytes_written(void* writer);
+void dtf_io_destroy(void* writer);
+/* debugging aid: native backtrace of the faulting thread on SIGSEGV, then the previous handler */
+void dtf_install_crash_handler(void);
+
 #ifdef __cplusplus
 }
 #endif

@@ -141,3 +141,33 @@ def test_cli_parsing():
         RunConfig(resnet_size=33).validate()
     with pytest.raises(ValueError):
         RunConfig(resnet_version=1, dtype="fp16").validate()
+
+
+def test_async_checkpoint_writer_roundtrip(tmp_path):
+    """Native background writer (csrc/host_io.cpp): same on-disk format as the synchronous path, ordered
+    data -> index -> pointer, many jobs in flight, reusable staging slots.  Host tensors here (no GPU)."""
+    import numpy as np
+    import torch
+    from distributedtf_b200 import ckpt
+    from distributedtf_b200.ops import native
+    if not native.available():
+        pytest.skip("native library not built")
+    w = ckpt.AsyncCheckpointWriter(threads=3, staging_slots=2)
+    states = []
+    for m in range(7):                                        # more jobs than staging slots
+        state = torch.arange(4096 + 256 * m, dtype=torch.int32).view(torch.uint8).clone()
+        f = state.view(torch.float32)
+        views = {"params": f[:1000].view(10, 100), "slot0": f[1000:2000], "step": state[8000:8008].view(torch.int64)}
+        t = w.save_state(str(tmp_path / f"model_{m}"), state, views, step=m + 5, optimizer="Momentum", meta={"m": m})
+        assert t > 0
+        states.append((state, views))
+    w.wait_all()
+    assert w.pending() == 0 and w.bytes_written() == sum(s.numel() for s, _ in states)
+    for m, (state, views) in enumerate(states):
+        d = tmp_path / f"model_{m}"
+        assert sorted(os.listdir(d)) == ["checkpoint", "model.ckpt.data", "model.ckpt.index"]      # no temp files left
+        tensors, index = ckpt.load_checkpoint(str(d))
+        assert index["step"] == m + 5 and index["optimizer"] == "Momentum" and index["meta"] == {"m": m}
+        for k, v in views.items():
+            assert np.array_equal(tensors[k], v.numpy()), k
+    w.close()

@@ -114,3 +114,23 @@ def test_toy_pbt_over_tcp_processes(tmp_path):
     assert out["pop_size"] == 2
     assert (tmp_path / "sd" / "best_model.json").exists()
     assert "n = 2, pop_size = 2, time = " in (tmp_path / "res.txt").read_text()
+
+
+def test_local_fabric_abort_unblocks_recv():
+    """A dead endpoint must not leave its peers blocked forever (run_local aborts the fabric on a worker error)."""
+    import threading
+    from distributedtf_b200.parallel.local import LocalFabric
+    fabric = LocalFabric(2)
+    got = []
+
+    def waiter():
+        try:
+            fabric.endpoint(0).recv(source=1)
+        except RuntimeError as e:
+            got.append(e)
+
+    t = threading.Thread(target=waiter, daemon=True)
+    t.start()
+    fabric.abort(ValueError("worker died"))
+    t.join(5)
+    assert not t.is_alive() and got and "worker died" in str(got[0])

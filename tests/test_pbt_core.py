@@ -34,7 +34,7 @@ class ScoreModel(ModelBase):
 
 
 def _hp(i):
-    return {"opt_case": {"optimizer": "gd", "lr": 0.1}, "batch_size": 100, "decay_rate": 0.1 + 0.02 * i}
+    return {"opt_case": {"optimizer": "gd", "lr": 0.1}, "batch_size": 100, "decay_rate": round(0.33 + 0.05 * i, 2)}   # never equal to a 1-digit perturbed value
 
 
 def start_cluster(pop, workers, tmp_path, model=ScoreModel, **kw):
@@ -221,3 +221,17 @@ def test_recv_timeout_detects_dead_worker(tmp_path):
         c = PBTCluster(2, fabric.endpoint(0), 0, 1, save_root=str(tmp_path), verbose=False,
                        recv_timeout=0.2, initial_hparams=[_hp(0), _hp(1)])
         c.get_all_values()
+
+
+def test_members_in_flight_matches_sequential_on_toy(tmp_path):
+    """Thread-pool schedule of a worker's members (host members: no streams involved) gives the same run."""
+    from distributedtf_b200.config import RunConfig
+    from distributedtf_b200.launch import run_local
+    outs = []
+    for k in (1, 3):
+        cfg = RunConfig(target_model="toy", population_size=6, train_round=4, epochs_per_round=2, workers=2,
+                        transport="local", save_root=str(tmp_path / f"sd{k}"), results_file=str(tmp_path / f"r{k}.txt"),
+                        verbose=False, seed=11, members_in_flight=k).validate()
+        outs.append(run_local(cfg))
+    assert outs[0]["best"] == outs[1]["best"]
+    assert [h["pairs"] for h in outs[0]["history"]] == [h["pairs"] for h in outs[1]["history"]]

@@ -116,3 +116,53 @@ def test_scoreboard_feeds_the_ranking(tmp_path):
     scores = seen["board"].read(2, members=[0, 1, 2, 3], timeout=5)
     assert set(scores) == {0, 1, 2, 3} and all(0 <= v <= 1 for v in scores.values())
     assert out["pop_size"] == 4
+
+
+@pytest.mark.parametrize("model", ["cifar10", "mnist"])
+def test_members_in_flight(tmp_path, model):
+    """Four members of one worker trained at once (own stream + thread each, half the SMs per member) through
+    the protocol: same artefacts as the sequential schedule, P2P exploit between rounds still consistent."""
+    from distributedtf_b200.launch import run_local
+    from distributedtf_b200.ops import native
+    try:
+        out = run_local(_cfg(tmp_path, target_model=model, members_in_flight=4, train_round=3, sm_limit=74))
+        assert native.sm_count() == 74
+    finally:
+        native.set_sm_limit(0)
+    # random MNIST hyper-parameters on 0..255 pixels diverge to NaN for some members (dropped, as in the
+    # sequential schedule); the ResNet population survives whole
+    assert (out["pop_size"] == 4 if model == "cifar10" else 1 <= out["pop_size"] <= 4) and len(out["history"]) == 3
+    alive = 0
+    for i in range(4):
+        path = tmp_path / "savedata" / f"model_{i}" / "learning_curve.csv"
+        if not path.exists():
+            continue
+        rows = open(path).read().strip().splitlines()
+        if len(rows) == 4 and all(0.0 <= float(r.split(",")[1]) <= 1.0 for r in rows[1:]):
+            alive += 1
+    assert alive >= out["pop_size"]
+
+
+def test_async_checkpoint_equals_device_state(tmp_path):
+    """Round-end save through the background writer (pinned staging + native writer threads): after the barrier
+    the files hold exactly the device state, and a second member restores bit-identically from them."""
+    from distributedtf_b200 import ckpt
+    from distributedtf_b200.hpspace import default_cifar_hparam
+    from distributedtf_b200.models.cifar10 import Cifar10Model
+    base = str(tmp_path / "model_")
+    kw = dict(engine="native", resnet_size=8, max_train_steps=3, eval_batches=1)
+    a = Cifar10Model(0, default_cifar_hparam(), base, async_checkpoint=True, **kw)
+    b = Cifar10Model(1, default_cifar_hparam(), base, **kw)
+    a.train(1, 1)
+    a.train(1, 1)                      # second save reuses the member's ticket / a staging slot
+    assert a._ckpt_ticket > 0
+    a.flush_io()
+    tensors, index = ckpt.load_checkpoint(a.save_dir)
+    assert index["step"] == a.engine.step == 6
+    for k, t in a.engine.state_tensors().items():
+        assert torch.equal(torch.from_numpy(tensors[k]).to(t.device).view_as(t), t), k
+    ckpt.copy_member_files(a.save_dir, b.save_dir)
+    assert b.restore() and b.engine.step == 6
+    for k, t in a.engine.state_tensors().items():
+        assert torch.equal(t, b.engine.state_tensors()[k]), k
+    a.close(); b.close()

@@ -44,6 +44,9 @@ def test_noalloc_matches_regular_entry_point_twice_in_a_row():
     native, l = _lib()
     dev = torch.device("cuda", 0)
     torch.cuda.set_device(dev)
+    import gc
+    gc.collect()                                             # members of earlier tests: let them go now, not mid-test
+    torch.cuda.synchronize(dev)
     stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
     nbytes, hp_off = 5 * 1024 * 1024 + 4096, 1024
     for call in range(2):                                    # back to back: the scratch carries over
