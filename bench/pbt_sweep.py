@@ -21,13 +21,14 @@ from distributedtf_b200.config import RunConfig  # noqa: E402
 from distributedtf_b200.launch import run_local  # noqa: E402
 
 
-def one(arm, n, pop, rounds, k):
+def one(arm, n, pop, rounds, k, ckpt_every=1):
     d = tempfile.mkdtemp(prefix="dtf_sweep_")
     cfg = RunConfig(target_model="mnist", population_size=pop, train_round=rounds, epochs_per_round=1,
                     workers=n - 1, transport="local", max_train_steps=10, eval_batches=4,
                     engine="eager" if arm == "restated" else "native",
                     exploit_path="file" if arm == "restated" else "p2p",
                     members_in_flight=k if arm == "native-mf" else 1,
+                    checkpoint_every=1 if arm == "restated" else ckpt_every,
                     save_root=d + "/savedata", results_file=d + "/test_results.txt", verbose=False, seed=7).validate()
     t0 = time.time()
     out = run_local(cfg)
@@ -41,6 +42,7 @@ if __name__ == "__main__":
     ap.add_argument("--pop", type=int, nargs="+", default=[10, 20, 30, 40, 50])
     ap.add_argument("--rounds", type=int, default=20)
     ap.add_argument("--members-in-flight", type=int, default=4)
+    ap.add_argument("--checkpoint-every", type=int, default=1, help="native arms: rounds between checkpoints (0 = last only)")
     a = ap.parse_args()
     import faulthandler
     faulthandler.enable()
@@ -50,8 +52,9 @@ if __name__ == "__main__":
     one(a.arm, 2, 2, 1, a.members_in_flight)          # warm-up: library load, kernel attributes
     for n in a.n:
         for pop in a.pop:
-            secs, alive = one(a.arm, n, pop, a.rounds, a.members_in_flight)
+            secs, alive = one(a.arm, n, pop, a.rounds, a.members_in_flight, a.checkpoint_every)
             print("n = {}, pop_size = {}, time = {}s".format(n, pop, secs), flush=True)
             grid.append({"n": n, "pop_size": pop, "time_s": round(secs, 3), "alive_at_end": alive})
     print(json.dumps({"bench": "pbt_sweep", "arm": a.arm, "rounds": a.rounds, "model": "mnist (10 train steps/epoch)",
-                      "members_in_flight": a.members_in_flight if a.arm == "native-mf" else 1, "grid": grid}))
+                      "members_in_flight": a.members_in_flight if a.arm == "native-mf" else 1,
+                      "checkpoint_every": 1 if a.arm == "restated" else a.checkpoint_every, "grid": grid}))

@@ -34,6 +34,7 @@ class RunConfig:
     dp_size: int = 1                      # GPUs per member (1 | 2 | 4)
     members_in_flight: int = 1            # members of one worker trained concurrently (own stream + host thread)
     sm_limit: int = 0                     # > 0: SMs a member's persistent kernels occupy (0 = all)
+    checkpoint_every: int = 1             # rounds between member checkpoints (0 = last round only); 'file' exploit needs 1
     async_checkpoint: Optional[bool] = None   # None: on unless exploit_path == 'file' (native engines only)
     # --- data plane ---
     exploit_path: str = "file"            # file | p2p | nccl | host
@@ -64,6 +65,8 @@ class RunConfig:
     def validate(self) -> "RunConfig":
         if self.workers < 1:
             raise ValueError("need at least one worker (the reference needs mpirun -n >= 2)")
+        if self.checkpoint_every != 1 and self.exploit_path == "file" and self.do_exploit:
+            raise ValueError("exploit_path='file' copies checkpoint files every round: checkpoint_every must be 1")
         if self.dp_size not in (1, 2, 4):
             raise ValueError("dp_size must be 1, 2 or 4")
         if self.target_model not in ("toy", "mnist", "cifar10"):
@@ -102,6 +105,8 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--dp-size", type=int, choices=[1, 2, 4], default=1)
     p.add_argument("--members-in-flight", type=int, default=1,
                    help="members of one worker trained at once (own stream + host thread each)")
+    p.add_argument("--checkpoint-every", type=int, default=1,
+                   help="rounds between member checkpoints (0 = only after the last round)")
     p.add_argument("--async-checkpoint", action=argparse.BooleanOptionalAction, default=None)
     p.add_argument("--sm-limit", type=int, default=0, help="SMs a member's persistent kernels occupy (0 = all)")
     p.add_argument("--exploit-path", choices=["file", "p2p", "nccl", "host"], default="file")

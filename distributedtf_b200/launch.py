@@ -64,6 +64,7 @@ def model_kwargs(cfg: RunConfig, dp_group=None, dp_rank: int = 0) -> Dict[str, A
         kw["hooks"] = _hooks.get_train_hooks(cfg.hooks, model_dir=cfg.save_root, batch_size=128)
     kw["benchmark"] = (cfg.benchmark_logger_type, cfg.benchmark_log_dir)
     # the file-exploit path copies checkpoint files right after GET: keep those saves synchronous
+    kw["checkpoint_every"] = cfg.checkpoint_every
     kw["async_checkpoint"] = cfg.async_checkpoint if cfg.async_checkpoint is not None else cfg.exploit_path != "file"
     return kw
 

@@ -52,7 +52,8 @@ class GpuMember(ModelBase):
                  eval_batches: Optional[int] = None, resume: bool = False,
                  synthetic_mode: str = "random", device: Optional[torch.device] = None,
                  hooks: Optional[List[Any]] = None, dp_group=None, dp_rank: int = 0, dp_size: int = 1,
-                 scoreboard: Optional[Dict[str, Any]] = None, benchmark=None, async_checkpoint: bool = False, **_):
+                 scoreboard: Optional[Dict[str, Any]] = None, benchmark=None, async_checkpoint: bool = False,
+                 checkpoint_every: int = 1, **_):
         super().__init__(cluster_id, hparams, save_base_dir)
         self.device = device or pick_device()
         self.dp_group, self.dp_rank, self.dp_size = dp_group, int(dp_rank), int(dp_size)
@@ -69,6 +70,9 @@ class GpuMember(ModelBase):
         self._bench_logger = None
         self.async_checkpoint = bool(async_checkpoint)   # native engines: save through the background writer
         self._ckpt_ticket = 0
+        # 1 = every round (the reference's behaviour); k > 1 = every k-th round and the last; 0 = the last only.
+        # The state lives on the GPU between rounds, so with a device exploit path files are only for resume.
+        self.checkpoint_every = int(checkpoint_every)
         if benchmark and benchmark[0] == "BenchmarkFileLogger" and benchmark[1]:
             from ..utils.logs import logger as _logger
             self._bench_logger = _logger.BenchmarkFileLogger(os.path.join(benchmark[1], f"model_{cluster_id}"))
@@ -219,7 +223,10 @@ class GpuMember(ModelBase):
             from ..parallel import exploit
             exploit.publish(self, self.rounds_trained)
         self.rounds_trained += 1
-        self.save()
+        last = self.epoches_trained >= total_epochs
+        k = self.checkpoint_every
+        if last or k == 1 or (k > 1 and self.rounds_trained % k == 0):
+            self.save()
         report.append_csv(os.path.join(self.ensure_dir(), "learning_curve.csv"), self.csv_fields_now(), rows)
 
     def epoch_index_for_csv(self, e: int) -> int:

@@ -99,3 +99,20 @@ def test_eager_fallback_for_resnet_v1(tmp_path):
     from distributedtf_b200.utils.export import export
     out = export.load_inference_bundle(bundle)(torch.randn(2, 32, 32, 3))
     assert out["probabilities"].shape == (2, 10)
+
+
+def test_checkpoint_every(tmp_path):
+    """`checkpoint_every=0`: the member state stays in memory between rounds; files appear after the last round."""
+    from distributedtf_b200.hpspace import default_cifar_hparam
+    from distributedtf_b200.models.cifar10 import Cifar10Model
+    hp = default_cifar_hparam(); hp["batch_size"] = 65
+    m = Cifar10Model(0, hp, str(tmp_path / "model_"), engine="eager", resnet_size=8, max_train_steps=1,
+                     eval_batches=1, device=torch.device("cpu"), checkpoint_every=0)
+    m.train(1, 2)
+    assert not os.path.exists(os.path.join(m.save_dir, "checkpoint"))
+    assert os.path.exists(os.path.join(m.save_dir, "learning_curve.csv"))       # curves are still appended
+    m.train(1, 2)
+    assert os.path.exists(os.path.join(m.save_dir, "checkpoint"))
+    from distributedtf_b200.config import RunConfig
+    with pytest.raises(ValueError):
+        RunConfig(exploit_path="file", checkpoint_every=3).validate()
