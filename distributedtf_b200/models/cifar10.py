@@ -9,7 +9,7 @@ Hyper-parameters arrive in the constructor / ``set_values`` — no flag globals.
 """
 from __future__ import annotations
 
-from typing import Any, Dict, List
+from typing import Optional, Any, Dict, List
 
 import torch
 
@@ -28,8 +28,9 @@ class Cifar10Model(GpuMember):
                   "initializer", "regularizer", "weight_decay", "batch_size", "model_id"]
 
     def __init__(self, cluster_id: int, hparams: Dict[str, Any], save_base_dir: str, *,
-                 resnet_size: int = 32, resnet_version: int = 2, **kw):
+                 resnet_size: int = 32, resnet_version: int = 2, loss_scale: Optional[float] = None, **kw):
         self.net_cfg = resnet.cifar10_config(resnet_size, resnet_version)
+        self.loss_scale = loss_scale            # None: 128 for fp16, 1 otherwise (flags.get_loss_scale)
         super().__init__(cluster_id, hparams, save_base_dir, **kw)
 
     def build_datasets(self):
@@ -60,7 +61,8 @@ class Cifar10Model(GpuMember):
         init = resnet.init_params(cfg, self.hparams.get("initializer", "None"), seed)
         return EagerEngine(resnet.param_specs(cfg), lambda p, x, t: resnet.forward(cfg, p, x, t), init,
                            self.hparams, self.device, compute_dtype=_DTYPES[self.dtype]
-                           if self.device.type == "cuda" else torch.float32, lr_schedule=True)
+                           if self.device.type == "cuda" else torch.float32, lr_schedule=True,
+                           loss_scale=self.loss_scale)
 
     def export(self, export_dir: str) -> str:
         """Inference bundle (reference: ``classifier.export_savedmodel``, resnet_run_loop.py:510-514)."""

@@ -26,11 +26,14 @@ class EagerEngine:
     def __init__(self, specs: Sequence[ParamSpec], forward: Callable[..., torch.Tensor],
                  init: Dict[str, torch.Tensor], hparams: Dict[str, Any], device, *,
                  compute_dtype: torch.dtype = torch.float32, lr_schedule: bool = False,
-                 channels_last: bool = True):
+                 channels_last: bool = True, loss_scale: Optional[float] = None):
         self.specs = list(specs)
         self.device = torch.device(device)
         self.forward_fn = forward
         self.compute_dtype = compute_dtype
+        # static loss scale: loss x S before backward, gradients / S before the update; default 128 for fp16,
+        # 1 otherwise (reference: _performance.py:30-33, resnet_run_loop.py:284-294)
+        self.loss_scale = float(loss_scale) if loss_scale else (128.0 if compute_dtype == torch.float16 else 1.0)
         self.lr_schedule = lr_schedule
         self.channels_last = channels_last and self.device.type == "cuda"
         self.train_specs = [s for s in self.specs if s.trainable]
@@ -83,9 +86,13 @@ class EagerEngine:
         """One optimizer step; returns the (device) mean cross-entropy."""
         self.flat.grad = None
         logits = self.forward_fn(self.params, self._prep(images_nhwc), True)
-        ce = F.cross_entropy(logits, labels.long())
-        ce.backward()
-        g = self.flat.grad
+        ce = F.cross_entropy(logits.float(), labels.long())
+        if self.loss_scale != 1.0:
+            (ce * self.loss_scale).backward()
+            g = self.flat.grad / self.loss_scale
+        else:
+            ce.backward()
+            g = self.flat.grad
         oc = self.hp["opt_case"]
         reg, wd = self.hp.get("regularizer", "None"), float(self.hp.get("weight_decay", 0.0))
         with torch.no_grad():

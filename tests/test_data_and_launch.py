@@ -116,3 +116,24 @@ def test_checkpoint_every(tmp_path):
     from distributedtf_b200.config import RunConfig
     with pytest.raises(ValueError):
         RunConfig(exploit_path="file", checkpoint_every=3).validate()
+
+
+def test_static_loss_scale_leaves_the_update_unchanged():
+    """K12: loss x S before backward, gradients / S before the optimizer -- same step in fp32 arithmetic."""
+    from distributedtf_b200.hpspace import default_cifar_hparam
+    from distributedtf_b200.models import resnet
+    from distributedtf_b200.models.engine_eager import EagerEngine
+    cfg = resnet.cifar10_config(8, 2)
+    hp = default_cifar_hparam()
+    x = torch.randn(8, 32, 32, 3)
+    y = torch.randint(0, 10, (8,))
+    flats = []
+    for scale in (None, 128.0):
+        e = EagerEngine(resnet.param_specs(cfg), lambda p, a, t: resnet.forward(cfg, p, a, t),
+                        resnet.init_params(cfg, "he_normal", 0), hp, "cpu", lr_schedule=True, loss_scale=scale)
+        assert e.loss_scale == (scale or 1.0)
+        e.train_step(x, y)
+        flats.append(e.flat.detach().clone())
+    assert torch.allclose(flats[0], flats[1], rtol=1e-4, atol=1e-6)
+    assert EagerEngine(resnet.param_specs(cfg), None, resnet.init_params(cfg, "None", 0), hp, "cpu",
+                       compute_dtype=torch.float16).loss_scale == 128.0

@@ -82,8 +82,6 @@ def test_benchmark_loggers(tmp_path):
     assert params["synthetic_data"]["bool_value"] == "True" and params["lr"]["float_value"] == 0.1
     assert run["machine_config"]["cpu_info"]["num_cores"] >= 1 and "framework_version" in run
     with pytest.raises(ValueError):
-        logger.config_benchmark_logger(type("F", (), {"benchmark_logger_type": "BenchmarkBigQueryLogger"})())
-    with pytest.raises(ValueError):
         logger.config_benchmark_logger(type("F", (), {"benchmark_logger_type": "nope"})())
     with pytest.raises(RuntimeError):
         with logger.benchmark_context(None):
@@ -269,3 +267,29 @@ def test_embedding_matmul():
         tpu.embedding_matmul(table, values[0], mask[0])
     with pytest.raises(NotImplementedError):
         tpu.construct_scalar_host_call({}, "/tmp")
+
+
+def test_bigquery_logger_uploads_from_threads(tmp_path):
+    """C12: BenchmarkBigQueryLogger — run info, RUNNING status, metrics, final status, through the uploader API;
+    offline the uploader spools JSON lines per table."""
+    import json
+    import types
+    from distributedtf_b200.utils.logs import logger
+    flags = types.SimpleNamespace(benchmark_logger_type="BenchmarkBigQueryLogger", benchmark_log_dir=str(tmp_path),
+                                  gcp_project=None, bigquery_data_set="ds", bigquery_run_table="run",
+                                  bigquery_run_status_table="status", bigquery_metric_table="metric")
+    with logger.benchmark_context(flags):
+        lg = logger.get_benchmark_logger()
+        assert isinstance(lg, logger.BenchmarkBigQueryLogger)
+        lg.log_run_info("resnet", "cifar10", {"batch_size": 128}, test_id="t1")
+        lg.log_metric("accuracy", 0.5, global_step=10)
+        lg.log_metric("bad", "not a number")                 # dropped, as in the reference
+        lg.log_evaluation_result({"loss": 1.25, "global_step": 20})
+    spool = tmp_path / "bigquery_spool"
+    rows = {f: [json.loads(l) for l in open(spool / f)] for f in sorted(os.listdir(spool))}
+    assert sorted(rows) == ["ds.metric.jsonl", "ds.run.jsonl", "ds.status.jsonl"]
+    assert [r["status"] for r in rows["ds.status.jsonl"]] == ["running", "success"]
+    assert {r["name"] for r in rows["ds.metric.jsonl"]} == {"accuracy", "loss"}
+    assert len({r["run_id"] for r in rows["ds.metric.jsonl"]}) == 1
+    assert rows["ds.run.jsonl"][0]["model_name"] == "resnet" and rows["ds.run.jsonl"][0]["test_id"] == "t1"
+    logger.config_benchmark_logger()                          # back to the default for later tests
