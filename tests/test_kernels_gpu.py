@@ -278,3 +278,61 @@ def test_conv_wgrad(nat, NB, H, Cin, Cout, k, stride, pro):
     nat.conv_wgrad(gx, gg, dw, NB=NB, Ho=Ho, Wo=Ho, Cout=Cout)
     torch.cuda.synchronize()
     assert_close(dw, 2 * want, rtol=2e-2, atol=2e-2 * scale_ref + 2e-3, what="wgrad x2")
+
+
+GUARD = 4096            # elements of sentinel on each side of every output
+
+
+def _guarded(shape, dtype, fill):
+    """A tensor of `shape` embedded in a larger buffer whose margins hold a sentinel (compute-sanitizer is not
+    available on the GPU pool: out-of-bounds writes are caught by canaries instead)."""
+    n = 1
+    for s in shape:
+        n *= s
+    buf = torch.full((n + 2 * GUARD,), fill, dtype=dtype, device="cuda")
+    return buf, buf[GUARD: GUARD + n].view(*shape)
+
+
+def _margins_intact(buf, fill):
+    head, tail = buf[:GUARD].float(), buf[-GUARD:].float()
+    return bool((head == fill).all()) and bool((tail == fill).all())
+
+
+@pytest.mark.parametrize("NB,H,Cin,Cout,k,stride", [(3, 8, 16, 16, 3, 1), (3, 16, 16, 32, 3, 2), (3, 16, 16, 32, 1, 2),
+                                                    (5, 8, 32, 64, 3, 2), (2, 14, 32, 64, 5, 1), (7, 8, 64, 64, 3, 1)])
+def test_conv_kernels_stay_inside_their_outputs(nat, NB, H, Cin, Cout, k, stride):
+    """Forward, input-gradient (halo, parity-class and generic paths) and weight-gradient kernels with odd batch
+    sizes / partial tiles: every output sits between sentinel margins that must survive the launch."""
+    Ho = H // stride
+    x = bf(rnd(NB, H, H, Cin, seed=1))
+    w = rnd(Cout, k, k, Cin, scale=1.0 / math.sqrt(k * k * Cin), seed=2)
+    gy = bf(rnd(NB, Ho, Ho, Cout, seed=3))
+    S = 7.0
+    # forward with statistics
+    obuf, out = _guarded((NB, Ho, Ho, Cout), torch.bfloat16, S)
+    sbuf, so = _guarded((2 * Cout,), torch.float32, S)
+    so.zero_()
+    nat.conv_gemm(nat.gather(x, H, H, Cin, KH=k, KW=k, stride=stride, pad=(k - 1) // 2), nat.pack_weight_host(w), out,
+                  NB=NB, Ho=Ho, Wo=Ho, N=Cout, epi_stats_out=so)
+    # input gradient (ReLU mask epilogue with statistics), then the accumulating variant
+    st_in = stats_of(x)
+    g_in, b_in = torch.ones(Cin, device="cuda"), torch.zeros(Cin, device="cuda")
+    epi_bn = nat.bn_ref(Cin, NB * H * H, stats=st_in, gamma=g_in, beta=b_in)
+    gbuf, gx = _guarded((NB, H, H, Cin), torch.bfloat16, S)
+    gx.zero_()
+    tbuf, ts = _guarded((2 * Cin,), torch.float32, S)
+    ts.zero_()
+    gg = nat.gather(gy, Ho, Ho, Cout, KH=k, KW=k, stride=stride, pad=(k - 1) // 2, transposed=True)
+    wd = nat.pack_weight_host(w, transpose_for_dgrad=True)
+    for acc in (False, True):
+        nat.conv_gemm(gg, wd, gx, NB=NB, Ho=H, Wo=H, N=Cin, epi_mode=nat.EPI_RELU_MASK, epi_x=x, epi_bn=epi_bn,
+                      epi_stats_out=ts, epi_accumulate=acc)
+    # weight gradient
+    wbuf, dw = _guarded((Cout, k, k, Cin), torch.float32, S)
+    dw.zero_()
+    nat.conv_wgrad(nat.gather(x, H, H, Cin, KH=k, KW=k, stride=stride, pad=(k - 1) // 2), nat.gather(gy, Ho, Ho, Cout), dw,
+                   NB=NB, Ho=Ho, Wo=Ho, Cout=Cout)
+    torch.cuda.synchronize()
+    for name, b in (("out", obuf), ("stats", sbuf), ("gx", gbuf), ("bwd stats", tbuf), ("dw", wbuf)):
+        assert _margins_intact(b, S), f"{name}: a kernel wrote outside its output"
+    assert torch.isfinite(out.float()).all() and torch.isfinite(gx.float()).all() and torch.isfinite(dw).all()
