@@ -96,7 +96,65 @@ def dgrad_case(H, Cin, Cout, k, stride, bn_pro):
                                  epi_bn=epi_bn, epi_stats_out=so, epi_accumulate=(k == 1)), keep
 
 
+def fwd_res_case(H, C):
+    """3x3 / stride-1 layer as it runs in a block: BN+ReLU prologue, residual epilogue, statistics."""
+    x, res = bf(NB, H, H, C), bf(NB, H, H, C)
+    w = torch.randn(C, 3, 3, C, device=dev) / math.sqrt(9 * C)
+    wpk = nat.pack_weight_host(w)
+    out = torch.empty(NB, H, H, C, device=dev, dtype=torch.bfloat16)
+    st = stats_of(x)
+    ones, zeros = torch.ones(C, device=dev), torch.zeros(C, device=dev)
+    bn = nat.bn_ref(C, NB * H * H, stats=st, gamma=ones, beta=zeros)
+    so = torch.zeros(2 * C, device=dev)
+    g = nat.gather(x, H, H, C, KH=3, KW=3, stride=1, pad=1, mode=nat.PRO_BN_RELU, bn=bn)
+    return lambda: nat.conv_gemm(g, wpk, out, NB=NB, Ho=H, Wo=H, N=C, epi_mode=nat.EPI_RESIDUAL, epi_res=res,
+                                 epi_stats_out=so), [x, res, st, ones, zeros]
+
+
+def bwd_fused_case(H, C):
+    """dgrad + wgrad of a 3x3 / stride-1 layer in one launch (BN-backward prologue on gy, ReLU-mask epilogue)."""
+    x_in, c_out, gy = bf(NB, H, H, C), bf(NB, H, H, C), bf(NB, H, H, C)
+    w = torch.randn(C, 3, 3, C, device=dev) / math.sqrt(9 * C)
+    wd = nat.pack_weight_host(w, transpose_for_dgrad=True)
+    st_i, st_o = stats_of(x_in), stats_of(c_out)
+    ones, zeros = torch.ones(C, device=dev), torch.zeros(C, device=dev)
+    bwd = torch.zeros(2 * C, device=dev)
+    bn_i = nat.bn_ref(C, NB * H * H, stats=st_i, gamma=ones, beta=zeros)
+    bn_o = nat.bn_ref(C, NB * H * H, stats=st_o, gamma=ones, beta=zeros)
+    out = torch.empty(NB, H, H, C, device=dev, dtype=torch.bfloat16)
+    so = torch.zeros(2 * C, device=dev)
+    dw = torch.zeros(C, 3, 3, C, device=dev)
+    gd = nat.gather(gy, H, H, C, KH=3, KW=3, stride=1, pad=1, transposed=True, mode=nat.PRO_BN_BWD, bn=bn_o,
+                    src2=c_out, bwd_stats=bwd)
+    dgrad = nat.conv_gemm_params(gd, wd, out, NB=NB, Ho=H, Wo=H, N=C, epi_mode=nat.EPI_RELU_MASK, epi_x=x_in,
+                                 epi_bn=bn_i, epi_stats_out=so)
+    gx = nat.gather(x_in, H, H, C, KH=3, KW=3, stride=1, pad=1, mode=nat.PRO_BN_RELU, bn=bn_i)
+    gg = nat.gather(gy, H, H, C, mode=nat.PRO_BN_BWD, bn=bn_o, src2=c_out, bwd_stats=bwd)
+    # the structs hold raw pointers: everything they point at must outlive the launches
+    return lambda: nat.conv_bwd(dgrad, gx, gg, dw, NB=NB, Ho=H, Wo=H, Cout=C), \
+        [x_in, c_out, gy, st_i, st_o, ones, zeros, bwd, wd, out, so, dw]
+
+
+def bn_bwd_case(H, C):
+    t, x, res = bf(NB, H, H, C), bf(NB, H, H, C), bf(NB, H, H, C)
+    st = stats_of(x)
+    ones, zeros = torch.ones(C, device=dev), torch.zeros(C, device=dev)
+    bwd = torch.zeros(2 * C, device=dev)
+    bn = nat.bn_ref(C, NB * H * H, stats=st, gamma=ones, beta=zeros)
+    out = torch.empty(NB, H, H, C, device=dev, dtype=torch.bfloat16)
+    return lambda: nat.bn_bwd_apply(t, x, res, out, bn, bwd, NB * H * H, C), [t, x, res, st, ones, zeros, bwd, out]
+
+
 CASES = [
+    ("fwd 3x3 16ch 32x32 (x10)", fwd_res_case, (32, 16)),
+    ("fwd 3x3 32ch 16x16 (x9)", fwd_res_case, (16, 32)),
+    ("fwd 3x3 64ch 8x8 (x9)", fwd_res_case, (8, 64)),
+    ("bwd fused 16ch 32x32 (x9)", bwd_fused_case, (32, 16)),
+    ("bwd fused 32ch 16x16 (x9)", bwd_fused_case, (16, 32)),
+    ("bwd fused 64ch 8x8 (x9)", bwd_fused_case, (8, 64)),
+    ("bn_bwd_apply 16ch 32x32 (x5)", bn_bwd_case, (32, 16)),
+    ("bn_bwd_apply 32ch 16x16 (x5)", bn_bwd_case, (16, 32)),
+    ("bn_bwd_apply 64ch 8x8 (x5)", bn_bwd_case, (8, 64)),
     ("fwd conv0 3x3 8->16", fwd_case, (32, 8, 16, 3, 1, False)),
     ("fwd proj 1x1 16->16", fwd_case, (32, 16, 16, 1, 1, True)),
     ("fwd proj 1x1 s2 16->32", fwd_case, (32, 16, 32, 1, 2, True)),

@@ -391,10 +391,12 @@ DTF_DEVINL void conv3x3_wgrad_body(const DtfConvWgrad& P, const HaloGeom& G, con
     griddep_wait();
     fill_prologue(P.x, cst->p0, cst->p1, cst->p2, tid, kHThreads);
     fill_prologue(P.gy, cst->q0, cst->q1, cst->q2, tid, kHThreads);
+    if (tid == 0) DTF_MARK(0);
     tc_fence_before_sync();
     __syncthreads();
     tc_fence_after_sync();
     const uint32_t tmem_base = hdr->tmem_base;
+    if (tid == 0) DTF_MARK(1);
 
     if (warp == kMmaWarp) {
         if (my_tiles > 0) {          // warp-uniform loop, one elected lane issues
@@ -406,6 +408,7 @@ DTF_DEVINL void conv3x3_wgrad_body(const DtfConvWgrad& P, const HaloGeom& G, con
                 mbar_wait(smem_u32(&hdr->full[st]), (it / nstages) & 1, 0x41);
                 tc_fence_after_sync();
                 if (elect_one()) {
+                    if (it < 4) DTF_MARK(8 + it);
                     for (int grp = 0; grp < ngroups; ++grp) {
                         const int c0 = grp * gchunks;
                         const int nc = min(gchunks, nchunks - c0);
@@ -416,6 +419,7 @@ DTF_DEVINL void conv3x3_wgrad_body(const DtfConvWgrad& P, const HaloGeom& G, con
                                       idesc0 + st * stage_units + c0 * (kChunkBytes >> 4) + ks * 16, idesc, (it | ks) != 0);
                     }
                     umma_commit(smem_u32(&hdr->empty[st]));
+                    if (it < 4) DTF_MARK(12 + it);
                 }
                 __syncwarp();
             }
@@ -443,6 +447,7 @@ DTF_DEVINL void conv3x3_wgrad_body(const DtfConvWgrad& P, const HaloGeom& G, con
             jg.src2 = P.gy.src2 ? P.gy.src2 + static_cast<size_t>(pix2) * P.Cout : nullptr;
             jg.dst = gy_base + g * 16;
             mbar_wait(smem_u32(&hdr->empty[st]), ((it / nstages) & 1) ^ 1, 0x42);
+            if (g == 0 && it < 4) DTF_MARK(16 + 4 * it);
             if (has_row) { RowJob j1[1] = {jx}; gather_rows<C8, 1>(j1, 1, G.cs, P.x.mode, cst->p0, cst->p1, cst->p2); }
             if (g < kTileM) {
                 RowJob j1[1] = {jg};
@@ -450,7 +455,9 @@ DTF_DEVINL void conv3x3_wgrad_body(const DtfConvWgrad& P, const HaloGeom& G, con
                 else if (G.gy_c8 == 4) gather_rows<4, 1>(j1, 1, kChunkBytes, P.gy.mode, cst->q0, cst->q1, cst->q2);
                 else gather_rows<8, 1>(j1, 1, kChunkBytes, P.gy.mode, cst->q0, cst->q1, cst->q2);
             }
+            if (g == 0 && it < 4) DTF_MARK(17 + 4 * it);
             named_bar_sync(2, kHGatherThreads);          // the halo tile is complete (gather warps only)
+            if (g == 0 && it < 4) DTF_MARK(18 + 4 * it);
             // im2col expansion: chunk (tap, c8), row r  <-  halo chunk c8, row r + shift(tap)
             const int items = nchunks * kTileM;
             for (int i = g; i < items; i += kHGatherThreads) {
@@ -463,10 +470,12 @@ DTF_DEVINL void conv3x3_wgrad_body(const DtfConvWgrad& P, const HaloGeom& G, con
             }
             fence_proxy_async_smem();
             mbar_arrive(smem_u32(&hdr->full[st]));
+            if (g == 0 && it < 4) DTF_MARK(19 + 4 * it);
         }
     } else if (my_tiles > 0) {
         mbar_wait(smem_u32(&hdr->acc_full[0]), 0, 0x43);
         tc_fence_after_sync();
+        if (tid == 0) DTF_MARK(32);
         const int co = warp * 32 + lane;
         const int ktot = 9 * Cin;
         const int kbase = tap_begin * Cin;
@@ -479,9 +488,11 @@ DTF_DEVINL void conv3x3_wgrad_body(const DtfConvWgrad& P, const HaloGeom& G, con
                 for (int i = 0; i < 16; i += 4) red_add_v4(dst + i, v[i], v[i + 1], v[i + 2], v[i + 3]);
             }
         }
+        if (tid == 0) DTF_MARK(33);
     }
     tc_fence_before_sync();
     __syncthreads();
+    if (tid == 0) DTF_MARK(4);
     if (warp == kMmaWarp) {
         tc_fence_after_sync();
         tmem_dealloc(tmem_base, acc_cols);
@@ -701,3 +712,10 @@ extern "C" int dtf_conv3x3_bwd_fused_try(const DtfConvGemm* pd, const DtfConvWgr
     else dtf_launch(conv3x3_bwd_fused_kernel<8>, dim3(grid), dim3(kHThreads), smem_bytes, stream, *pd, Gd, *pw, Gw, n_d, gx);
     return cudaGetLastError() == cudaSuccess ? 1 : DTF_ERR_CUDA;
 }
+
+#ifdef DTF_TIMING
+// Copies the 64 timeline slots (globaltimer ns, written by CTA 0) to the host.
+extern "C" int dtf_debug_timeline(unsigned long long* out) {
+    return cudaMemcpyFromSymbol(out, dtf::g_timeline, sizeof(unsigned long long) * 64) == cudaSuccess ? 0 : -1;
+}
+#endif
