@@ -391,6 +391,14 @@ DTF_DEVINL void conv3x3_wgrad_body(const DtfConvWgrad& P, const HaloGeom& G, con
     griddep_wait();
     fill_prologue(P.x, cst->p0, cst->p1, cst->p2, tid, kHThreads);
     fill_prologue(P.gy, cst->q0, cst->q1, cst->q2, tid, kHThreads);
+    // im2col expansion table: chunk j = (tap t, channel chunk c8) reads halo chunk c8 shifted by the tap
+    uint32_t* ex_tab = reinterpret_cast<uint32_t*>(&cst->bins[0][0]);     // the statistics bins are unused here
+    for (int j = tid; j < nchunks; j += kHThreads) {
+        const int t = j / C8, c8 = j - t * C8;
+        const int tap = tap_begin + t;
+        const int shift = (tap / 3) * G.Wp + (tap % 3);                   // (1+dy)*Wp + (1+dx)
+        ex_tab[j] = static_cast<uint32_t>(c8 * G.cs + shift * 16);
+    }
     if (tid == 0) DTF_MARK(0);
     tc_fence_before_sync();
     __syncthreads();
@@ -459,14 +467,22 @@ DTF_DEVINL void conv3x3_wgrad_body(const DtfConvWgrad& P, const HaloGeom& G, con
             named_bar_sync(2, kHGatherThreads);          // the halo tile is complete (gather warps only)
             if (g == 0 && it < 4) DTF_MARK(18 + 4 * it);
             // im2col expansion: chunk (tap, c8), row r  <-  halo chunk c8, row r + shift(tap)
+            // source offsets per im2col chunk come from a table built once per CTA (ex_tab); two copies in flight
             const int items = nchunks * kTileM;
-            for (int i = g; i < items; i += kHGatherThreads) {
-                const int r = i & (kTileM - 1);
-                const int j = i >> 7;
-                const int t = j / C8, c8 = j - t * C8;
-                const int tap = tap_begin + t;
-                const int shift = (tap / 3) * G.Wp + (tap % 3);          // (1+dy)*Wp + (1+dx)
-                sts16(im_base + j * kChunkBytes + r * 16, lds16(halo_base + c8 * G.cs + (r + shift) * 16));
+            int i = g;
+            for (; i + kHGatherThreads < items; i += 2 * kHGatherThreads) {
+                const int i2 = i + kHGatherThreads;
+                const uint32_t r0 = (i & (kTileM - 1)) * 16, r1 = (i2 & (kTileM - 1)) * 16;
+                const int j0 = i >> 7, j1 = i2 >> 7;
+                const uint4 v0 = lds16(halo_base + ex_tab[j0] + r0);
+                const uint4 v1 = lds16(halo_base + ex_tab[j1] + r1);
+                sts16(im_base + j0 * kChunkBytes + r0, v0);
+                sts16(im_base + j1 * kChunkBytes + r1, v1);
+            }
+            if (i < items) {
+                const uint32_t r0 = (i & (kTileM - 1)) * 16;
+                const int j0 = i >> 7;
+                sts16(im_base + j0 * kChunkBytes + r0, lds16(halo_base + ex_tab[j0] + r0));
             }
             fence_proxy_async_smem();
             mbar_arrive(smem_u32(&hdr->full[st]));
@@ -697,9 +713,27 @@ extern "C" int dtf_conv3x3_bwd_fused_try(const DtfConvGemm* pd, const DtfConvWgr
         attr_set = 1;
     }
     const int sms = halo_sms();
-    // split the SMs between the two halves in proportion to their MMA work (dgrad: 9*C8/2 small MMAs per
-    // tile, wgrad: 8 wide MMAs per tile per column group), never more CTAs than tiles
+    // Split the SMs between the two halves so that the slower half finishes as early as possible.  Both halves
+    // walk whole tiles, so the cost of a split is max(ceil(T / n_d) * t_d, ceil(T / gx) * t_w); the per-tile
+    // weights were fitted to a sweep of the split on B200 (bench/conv_micro.py with DTF_BWD_SPLIT=percent):
+    // 16 ch: 1.0 / 1.15, 32 ch: 2.5 / 2.0, 64 ch (two tap groups): 2.5 / 3.0.  A fixed 45 % cost 15 % on the
+    // 32-channel layers (5 dgrad tiles per CTA instead of 4).
+    static int pct = -1;
+    if (pct < 0) { const char* e = getenv("DTF_BWD_SPLIT"); pct = e ? atoi(e) : 0; if (pct < 5 || pct > 95) pct = 0; }
+    const double t_d = Gd.c8 == 2 ? 1.0 : 2.5, t_w = Gd.c8 == 2 ? 1.15 : (Gd.c8 == 4 ? 2.0 : 3.0);
     int n_d = (sms * 45) / 100;
+    if (pct > 0) {
+        n_d = (sms * pct) / 100;
+    } else {
+        double best = 1e30, best2 = 1e30;
+        for (int cand = 8; cand <= sms - 8 * ny; ++cand) {
+            const int g = (sms - cand) / ny;
+            const double cd = static_cast<double>((Gd.num_tiles + cand - 1) / cand) * t_d;
+            const double cw = static_cast<double>((Gw.num_tiles + g - 1) / g) * t_w;
+            const double c1 = cd > cw ? cd : cw, c2 = cd + cw;
+            if (c1 < best - 1e-9 || (c1 < best + 1e-9 && c2 < best2 - 1e-9)) { best = c1; best2 = c2; n_d = cand; }
+        }
+    }
     if (n_d > Gd.num_tiles) n_d = Gd.num_tiles;
     if (n_d < 1) n_d = 1;
     int gx = (sms - n_d) / ny;
