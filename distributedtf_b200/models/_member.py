@@ -158,19 +158,33 @@ class GpuMember(ModelBase):
         return steps
 
     def evaluate(self) -> float:
+        """Accuracy over the eval set.  A data-parallel member shards the eval batches over its replicas
+        (batch b goes to replica b % dp_size) and sums (correct, seen, non-finite-loss flag) over the group, so
+        every replica ends with the same score and the same drop decision."""
         bs = int(self.hparams["batch_size"])
         it = BatchIterator(len(self.eval_set), bs, False, device=self.device)
         correct = torch.zeros((), dtype=torch.int64, device=self.device)
         seen = 0
+        group = getattr(self.dp_group, "group", None) if self.dp_size > 1 else None
+        shard = group is not None
         with self._timed("eval"):
             for b, idx in enumerate(it.epoch_batches()):
                 if self.eval_batches is not None and b >= self.eval_batches:
                     break
+                if shard and b % self.dp_size != self.dp_rank:
+                    continue
                 x = self.preprocess(self.eval_set.images[idx], False)
                 correct += self.engine.eval_batch(x, self.eval_set.labels[idx]).to(torch.int64)
                 seen += int(idx.numel())
         loss = self.engine.last_loss
-        if loss is not None and not bool(torch.isfinite(loss)):
+        bad = loss is not None and not bool(torch.isfinite(loss))
+        if shard:
+            import torch.distributed as dist
+            packed = torch.stack([correct, torch.tensor(seen, device=self.device),
+                                  torch.tensor(int(bad), device=self.device)]).to(torch.int64)
+            dist.all_reduce(packed, group=group)
+            correct, seen, bad = packed[0], int(packed[1].item()), bool(packed[2].item() > 0)
+        if bad:
             return float("nan")
         self._publish_score(correct, seen)
         return float(correct.item()) / max(seen, 1)
