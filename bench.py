@@ -221,8 +221,8 @@ def main():
 
     def step_resident(i):
         idx = idx_dev[i % nbatches]
-        if args.impl == "native":
-            return eng.train_step_u8(dev_images[idx], dev_labels[idx], augment=True)
+        if args.impl == "native":       # the step's first kernel gathers the batch from the resident dataset
+            return eng.train_step_indexed(dev_images, dev_labels, idx, augment=True)
         x = cifar_preprocess_torch(dev_images[idx], True)
         return eng.train_step(x, dev_labels[idx])
 

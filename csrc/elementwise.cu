@@ -333,19 +333,25 @@ DTF_DEVINL uint64_t splitmix64(uint64_t x) {
 __global__ void __launch_bounds__(256)
 preprocess_kernel(const uint8_t* __restrict__ images, const int* __restrict__ indices,
                   dtf_bf16* __restrict__ out, const int* __restrict__ crop_flip,
-                  int H, int W, int C, int mode, unsigned long long seed, unsigned long long counter) {
+                  int H, int W, int C, int mode, unsigned long long seed, unsigned long long counter,
+                  const int* __restrict__ labels_all, int* __restrict__ labels_out,
+                  const long long* __restrict__ step) {
     griddep_launch_dependents();
     griddep_wait();
     __shared__ float red[2][8];
     __shared__ float s_mean, s_inv;
     const int n = blockIdx.x;
     const int src_idx = indices ? indices[n] : n;
+    if (labels_out != nullptr && threadIdx.x == 0) labels_out[n] = labels_all[src_idx];   // batch gather of the labels
     const uint8_t* img = images + static_cast<size_t>(src_idx) * H * W * C;
     int oy = 4, ox = 4, flip = 0;
     if (mode == 2) {
         if (crop_flip) { oy = crop_flip[3 * n]; ox = crop_flip[3 * n + 1]; flip = crop_flip[3 * n + 2]; }
         else {
-            const uint64_t r = splitmix64(seed ^ splitmix64(counter + n));
+            // `step` (device step counter, optional) keeps the draw fresh when the launch is replayed from a CUDA
+            // graph, where `counter` is frozen at capture time
+            const uint64_t ctr = counter + (step ? static_cast<uint64_t>(*step) * gridDim.x : 0ull);
+            const uint64_t r = splitmix64(seed ^ splitmix64(ctr + n));
             oy = static_cast<int>(r % 9); ox = static_cast<int>((r >> 16) % 9); flip = static_cast<int>((r >> 32) & 1);
         }
     }
@@ -451,8 +457,21 @@ extern "C" int dtf_fill(float* p, long long n, float v, cudaStream_t stream) {
 
 extern "C" int dtf_preprocess(const uint8_t* images, const int* indices, dtf_bf16* out, const int* crop_flip,
                               int n, int H, int W, int C, int mode, unsigned long long seed,
-                              unsigned long long counter, cudaStream_t stream) {
+                              unsigned long long counter, const long long* step, cudaStream_t stream) {
     if (C > 8 || n < 1) return DTF_ERR_SHAPE;
-    dtf_launch(dtf::preprocess_kernel, dim3(n), dim3(256), 0, stream, images, indices, out, crop_flip, H, W, C, mode, seed, counter);
+    dtf_launch(dtf::preprocess_kernel, dim3(n), dim3(256), 0, stream, images, indices, out, crop_flip, H, W, C, mode, seed, counter,
+               static_cast<const int*>(nullptr), static_cast<int*>(nullptr), step);
+    return DTF_CHECK_LAUNCH();
+}
+
+// Same, reading the batch straight out of a resident dataset: image n comes from images[indices[n]] and its
+// label from labels_all[indices[n]] (written to labels_out[n]) -- no separate gather / copy kernels per step.
+extern "C" int dtf_preprocess_indexed(const uint8_t* images, const int* indices, const int* labels_all, int* labels_out,
+                                      dtf_bf16* out, const int* crop_flip, int n, int H, int W, int C, int mode,
+                                      unsigned long long seed, unsigned long long counter, const long long* step,
+                                      cudaStream_t stream) {
+    if (C > 8 || n < 1 || indices == nullptr || labels_all == nullptr || labels_out == nullptr) return DTF_ERR_ARG;
+    dtf_launch(dtf::preprocess_kernel, dim3(n), dim3(256), 0, stream, images, indices, out, crop_flip, H, W, C, mode, seed, counter,
+               labels_all, labels_out, step);
     return DTF_CHECK_LAUNCH();
 }

@@ -144,8 +144,11 @@ class GpuMember(ModelBase):
                 if self.dp_size > 1:          # same permutation on every replica; each takes its slice
                     per = bs // self.dp_size
                     idx = idx[self.dp_rank * per: (self.dp_rank + 1) * per]
-                x = self.preprocess(self.train_set.images[idx], True)
-                loss = self.engine.train_step(x, self.train_set.labels[idx])
+                if self._indexed_steps():           # batch gathered inside the first kernel of the step
+                    loss = self.engine.train_step_indexed(self.train_set.images, self.train_set.labels, idx)
+                else:
+                    x = self.preprocess(self.train_set.images[idx], True)
+                    loss = self.engine.train_step(x, self.train_set.labels[idx])
                 if self.hooks:                    # values stay on the device unless a hook logs them
                     self._global_step = getattr(self, "_global_step", 0) + 1
                     vals = {"cross_entropy": loss, "learning_rate": self.hparams["opt_case"]["lr"]}
@@ -156,6 +159,11 @@ class GpuMember(ModelBase):
         if self.dp_size > 1 and bs % self.dp_size:
             raise ValueError(f"batch_size {bs} is not a multiple of dp_size {self.dp_size}")
         return steps
+
+    def _indexed_steps(self) -> bool:
+        """Native engines read the batch out of the resident dataset by index (no gather / copy kernels)."""
+        return (hasattr(self.engine, "train_step_indexed") and self.train_set.images.is_cuda
+                and self.train_set.images.dtype == torch.uint8 and self.train_set.labels.dtype == torch.int32)
 
     def evaluate(self) -> float:
         """Accuracy over the eval set.  A data-parallel member shards the eval batches over its replicas
@@ -173,8 +181,11 @@ class GpuMember(ModelBase):
                     break
                 if shard and b % self.dp_size != self.dp_rank:
                     continue
-                x = self.preprocess(self.eval_set.images[idx], False)
-                correct += self.engine.eval_batch(x, self.eval_set.labels[idx]).to(torch.int64)
+                if self._indexed_steps():
+                    correct += self.engine.eval_batch_indexed(self.eval_set.images, self.eval_set.labels, idx).to(torch.int64)
+                else:
+                    x = self.preprocess(self.eval_set.images[idx], False)
+                    correct += self.engine.eval_batch(x, self.eval_set.labels[idx]).to(torch.int64)
                 seen += int(idx.numel())
         loss = self.engine.last_loss
         bad = loss is not None and not bool(torch.isfinite(loss))

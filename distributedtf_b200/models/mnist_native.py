@@ -178,7 +178,7 @@ class NativeMnistEngine(NativeEngineBase):
     def _train_kernels(self, nb: int, pp_mode: int) -> None:
         self._count = 0
         self._begin_step()
-        native.preprocess(self.in_u8, None, self.image, mode=0, n=nb)
+        self.preprocess_batch(nb, 0)
         self._count += 1
         self._forward(nb, True)
         self._head(nb, True)
@@ -187,6 +187,6 @@ class NativeMnistEngine(NativeEngineBase):
 
     def _eval_kernels(self, nb: int) -> None:
         self._count = 0
-        native.preprocess(self.in_u8, None, self.image, mode=0, n=nb)
+        self.preprocess_batch(nb, 0)
         self._forward(nb, False)
         self._head(nb, False, loss=self.eval_cells[0:1], correct=self.eval_cells[1:2].view(torch.int32))

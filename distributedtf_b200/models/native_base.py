@@ -83,6 +83,8 @@ class NativeEngineBase:
         self._seed = seed
         self._count = 0
         self._side = None                       # side stream for independent kernels (engine-specific use)
+        self._src = None                        # (images_all, labels_all) while an indexed step is being issued
+        self._idx_buf = None
 
     # ------------------------------------------------------------------ memory
     def _finish_segments(self) -> None:
@@ -257,6 +259,52 @@ class NativeEngineBase:
         self.in_u8[:nb].copy_(images_u8, non_blocking=True)
         self.labels[:nb].copy_(labels.to(torch.int32), non_blocking=True)
         return nb
+
+    # -- steps that read their batch straight out of a resident dataset: the preprocessing kernel gathers images
+    #    and labels by index, so a step launches no torch gather / copy kernels at all
+    def _load_indices(self, images_all: torch.Tensor, labels_all: torch.Tensor, idx: torch.Tensor) -> int:
+        nb = int(idx.numel())
+        if nb > self.max_batch:
+            raise ValueError(f"batch {nb} exceeds the engine's max_batch {self.max_batch}")
+        if labels_all.dtype != torch.int32 or images_all.dtype != torch.uint8:
+            raise TypeError("indexed steps need a uint8 image tensor and int32 labels")
+        if self._idx_buf is None:
+            self._idx_buf = torch.zeros(self.max_batch, dtype=torch.int32, device=self.device)
+        self._idx_buf[:nb].copy_(idx, non_blocking=True)
+        self._src = (images_all, labels_all)
+        return nb
+
+    def preprocess_batch(self, nb: int, mode: int, counter: int = 0) -> None:
+        """First kernel of every step: uint8 batch (copied in, or gathered by index) -> standardised bf16 image."""
+        if self._src is not None:
+            images_all, labels_all = self._src
+            native.preprocess(images_all, self._idx_buf, self.image, mode=mode, seed=self._seed, counter=counter, n=nb,
+                              labels_all=labels_all, labels_out=self.labels, step=self.step_dev)
+        else:
+            native.preprocess(self.in_u8, None, self.image, mode=mode, seed=self._seed, counter=counter, n=nb,
+                              step=self.step_dev)
+
+    def train_step_indexed(self, images_all: torch.Tensor, labels_all: torch.Tensor, idx: torch.Tensor,
+                           augment: bool = True) -> torch.Tensor:
+        nb = self._load_indices(images_all, labels_all, idx)
+        mode = self.train_pp_mode if augment else self.eval_pp_mode
+        self._pp_counter += nb
+        try:
+            self._run(("train_idx" if augment else "train_idx_noaug", images_all.data_ptr(), labels_all.data_ptr()), nb,
+                      lambda: self._train_kernels(nb, mode))
+        finally:
+            self._src = None
+        self.last_loss = self.loss_cell
+        return self.loss_cell
+
+    def eval_batch_indexed(self, images_all: torch.Tensor, labels_all: torch.Tensor, idx: torch.Tensor) -> torch.Tensor:
+        nb = self._load_indices(images_all, labels_all, idx)
+        before = self.eval_cells[1:2].view(torch.int32).clone()
+        try:
+            self._run(("eval_idx", images_all.data_ptr(), labels_all.data_ptr()), nb, lambda: self._eval_kernels(nb))
+        finally:
+            self._src = None
+        return (self.eval_cells[1:2].view(torch.int32) - before).sum()
 
     def train_step_u8(self, images_u8: torch.Tensor, labels: torch.Tensor, augment: bool = True) -> torch.Tensor:
         """uint8 NHWC images (device or pinned host) -> one optimizer step; returns the loss cell."""

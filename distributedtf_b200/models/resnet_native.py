@@ -405,7 +405,7 @@ class NativeResNetEngine(NativeEngineBase):
     def _train_kernels(self, nb: int, pp_mode: int) -> None:
         self._count = 0
         self._begin_step()
-        native.preprocess(self.in_u8, None, self.image, mode=pp_mode, seed=self._seed, counter=self._pp_counter, n=nb)
+        self.preprocess_batch(nb, pp_mode)
         self._count += 1
         x_last = self._forward(nb, True)
         self._backward(x_last, nb)
@@ -413,7 +413,7 @@ class NativeResNetEngine(NativeEngineBase):
 
     def _eval_kernels(self, nb: int) -> None:
         self._count = 0
-        native.preprocess(self.in_u8, None, self.image, mode=1, n=nb)
+        self.preprocess_batch(nb, 1)
         x_last = self._forward(nb, False)
         self._head(x_last, nb, False, loss=self.eval_cells[0:1], correct=self.eval_cells[1:2].view(torch.int32))
 

@@ -139,7 +139,8 @@ def _declare(l: C.CDLL) -> None:
     l.dtf_optimizer_step.argtypes = [vp, vp, vp, vp, vp, vp, vp, i, vp, vp, f, vp]
     l.dtf_step_begin.argtypes = [vp, ll, vp, i, vp]
     l.dtf_fill.argtypes = [vp, ll, f, vp]
-    l.dtf_preprocess.argtypes = [vp, vp, vp, vp, i, i, i, i, i, C.c_ulonglong, C.c_ulonglong, vp]
+    l.dtf_preprocess.argtypes = [vp, vp, vp, vp, i, i, i, i, i, C.c_ulonglong, C.c_ulonglong, vp, vp]
+    l.dtf_preprocess_indexed.argtypes = [vp, vp, vp, vp, vp, vp, i, i, i, i, i, C.c_ulonglong, C.c_ulonglong, vp, vp]
     l.dtf_gemm.argtypes = [C.POINTER(Gemm), vp]
     l.dtf_maxpool_fwd.argtypes = [vp, vp, i, i, i, i, vp]
     l.dtf_maxpool_bwd.argtypes = [vp, vp, vp, vp, vp, i, i, i, i, vp]
@@ -280,11 +281,17 @@ def fill(t: torch.Tensor, value: float) -> None:
 
 def preprocess(images_u8: torch.Tensor, indices: Optional[torch.Tensor], out: torch.Tensor, *, mode: int,
                crop_flip: Optional[torch.Tensor] = None, seed: int = 0, counter: int = 0,
-               n: Optional[int] = None) -> None:
+               n: Optional[int] = None, labels_all: Optional[torch.Tensor] = None,
+               labels_out: Optional[torch.Tensor] = None, step: Optional[torch.Tensor] = None) -> None:
     _, H, W, Cc = images_u8.shape
     count = int(n if n is not None else (indices.numel() if indices is not None else images_u8.shape[0]))
+    if labels_all is not None:          # batch gathered inside the kernel (images and labels)
+        check(lib().dtf_preprocess_indexed(ptr(images_u8), ptr(indices), ptr(labels_all), ptr(labels_out), ptr(out),
+                                           ptr(crop_flip), count, H, W, Cc, mode, seed & (2 ** 64 - 1),
+                                           counter & (2 ** 64 - 1), ptr(step), stream_ptr()), "dtf_preprocess_indexed")
+        return
     check(lib().dtf_preprocess(ptr(images_u8), ptr(indices), ptr(out), ptr(crop_flip), count, H, W, Cc, mode,
-                               seed & (2 ** 64 - 1), counter & (2 ** 64 - 1), stream_ptr()), "dtf_preprocess")
+                               seed & (2 ** 64 - 1), counter & (2 ** 64 - 1), ptr(step), stream_ptr()), "dtf_preprocess")
 
 
 def struct_to_tensor(s: C.Structure, device) -> torch.Tensor:

@@ -164,7 +164,15 @@ int dtf_fill(float* p, long long n, float v, cudaStream_t stream);
  * (cifar10_main.py:96-109).  crop_flip: optional [n][3] = (oy, ox, flip) overriding the RNG. */
 int dtf_preprocess(const uint8_t* images, const int* indices, dtf_bf16* out, const int* crop_flip, int n,
                    int H, int W, int C, int mode, unsigned long long seed, unsigned long long counter,
-                   cudaStream_t stream);
+                   const long long* step, cudaStream_t stream);
+/* `step` (optional device step counter) is added to `counter` x batch so that the random crop / flip draw stays
+ * fresh when the launch is replayed from a CUDA graph.
+ * Same, with the batch gathered from a resident dataset inside the kernel: image n = images[indices[n]],
+ * labels_out[n] = labels_all[indices[n]]. */
+int dtf_preprocess_indexed(const uint8_t* images, const int* indices, const int* labels_all, int* labels_out,
+                           dtf_bf16* out, const int* crop_flip, int n, int H, int W, int C, int mode,
+                           unsigned long long seed, unsigned long long counter, const long long* step,
+                           cudaStream_t stream);
 
 /* ---- communication-bound hot paths over NVLink peer memory (csrc/comm_kernels.cu) ------------- */
 #define DTF_MAX_DP 8

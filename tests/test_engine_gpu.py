@@ -333,3 +333,43 @@ def test_native_vs_eager_training_parity(nat):
     mid_n, mid_r = sum(ln[36:44]) / 8, sum(lr_[36:44]) / 8
     assert abs(mid_n - mid_r) < 0.2 * mid_r + 0.05, (mid_n, mid_r)
     print("loss native/eager:", [round(x, 3) for x in ln[::10]], [round(x, 3) for x in lr_[::10]])
+
+
+def test_indexed_step_equals_copied_batch():
+    """train_step_indexed / eval_batch_indexed (batch gathered by the preprocessing kernel) == gathering the batch
+    with torch and copying it in; with augmentation off both are deterministic up to atomics order."""
+    from distributedtf_b200.hpspace import default_cifar_hparam
+    from distributedtf_b200.models import resnet
+    from distributedtf_b200.models.resnet_native import NativeResNetEngine
+    hp = default_cifar_hparam()
+    g = torch.Generator().manual_seed(5)
+    images = torch.randint(0, 256, (512, 32, 32, 3), dtype=torch.uint8, generator=g).cuda()
+    labels = torch.randint(0, 10, (512,), dtype=torch.int32, generator=g).cuda()
+    a = NativeResNetEngine(resnet.cifar10_config(8), hp, "cuda:0", seed=3)
+    b = NativeResNetEngine(resnet.cifar10_config(8), hp, "cuda:0", seed=3)
+    for step in range(4):                                   # step 0 = plain run + capture, then graph replays
+        idx = torch.randperm(512, generator=g)[:64].cuda()
+        la = a.train_step_indexed(images, labels, idx, augment=False).item()
+        lb = b.train_step_u8(images[idx], labels[idx], augment=False).item()
+        assert abs(la - lb) < 2e-3 * max(1.0, abs(lb)), (step, la, lb)
+    idx = torch.arange(100, 164).cuda()
+    assert int(a.eval_batch_indexed(images, labels, idx)) == int(b.eval_batch_u8(images[idx], labels[idx]).sum())
+    assert torch.equal(a.labels[:64], labels[idx])
+    assert torch.allclose(a.params, b.params, rtol=2e-2, atol=2e-3)
+
+
+def test_augmentation_draw_changes_between_graph_replays():
+    """The crop / flip draw depends on the device step counter, so replaying the captured step does not replay
+    the augmentation."""
+    from distributedtf_b200.hpspace import default_cifar_hparam
+    from distributedtf_b200.models import resnet
+    from distributedtf_b200.models.resnet_native import NativeResNetEngine
+    g = torch.Generator().manual_seed(6)
+    images = torch.randint(0, 256, (64, 32, 32, 3), dtype=torch.uint8, generator=g).cuda()
+    labels = torch.randint(0, 10, (64,), dtype=torch.int32, generator=g).cuda()
+    e = NativeResNetEngine(resnet.cifar10_config(8), default_cifar_hparam(), "cuda:0", seed=1)
+    seen = []
+    for _ in range(4):
+        e.train_step_u8(images, labels, augment=True)
+        seen.append(e.image[:64].float().clone())
+    assert not torch.equal(seen[1], seen[2]) and not torch.equal(seen[2], seen[3])      # replays 2 and 3
