@@ -11,6 +11,7 @@
 // coalesced global->shared gather (consecutive threads = consecutive chunks of one row) is free of bank
 // conflicts.  Tile 128 x 128 x 64, three operand stages, two TMEM accumulators are not needed (one tile
 // per CTA): 4 epilogue warps + 1 MMA warp + 8 gather warps.
+#include <cstdlib>
 #include "common.cuh"
 #include "dtf_b200.h"
 
@@ -67,7 +68,12 @@ gemm_kernel(const __grid_constant__ DtfGemm P) {
     uint8_t* stages = smem + 1024;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int m0 = blockIdx.x * kBM, n0 = blockIdx.y * kBN;
-    const int num_kb = (P.K + kBK - 1) / kBK;
+    // split-K: blockIdx.z owns the K blocks [kb_begin, kb_end); a dense layer with a small batch has very few
+    // output tiles (M = batch = 128 -> 8 tiles for the 3136 -> 1024 layer) but a long K loop
+    const int total_kb = (P.K + kBK - 1) / kBK;
+    const int kb_per = (total_kb + P.k_split - 1) / P.k_split;
+    const int kb_begin = blockIdx.z * kb_per;
+    const int num_kb = max(0, min(total_kb, kb_begin + kb_per) - kb_begin);
     if (tid == 0) {
         for (int i = 0; i < kGStages; ++i) { mbar_init(smem_u32(&hdr->full[i]), kGGather); mbar_init(smem_u32(&hdr->empty[i]), 1); }
         mbar_init(smem_u32(&hdr->acc_full), 1);
@@ -107,22 +113,78 @@ gemm_kernel(const __grid_constant__ DtfGemm P) {
             const uint32_t st = kb % kGStages;
             mbar_wait(smem_u32(&hdr->empty[st]), ((kb / kGStages) & 1) ^ 1, 0x52);
             const uint32_t a_dst = smem_u32(stages) + st * 2 * kPanelBytes, b_dst = a_dst + kPanelBytes;
-            load_panel(P.a, P.lda, P.a_mn_major, m0, P.M, kb * kBK, P.K, a_dst, g);
-            load_panel(P.b, P.ldb, P.b_mn_major, n0, P.N, kb * kBK, P.K, b_dst, g);
+            load_panel(P.a, P.lda, P.a_mn_major, m0, P.M, (kb_begin + kb) * kBK, P.K, a_dst, g);
+            load_panel(P.b, P.ldb, P.b_mn_major, n0, P.N, (kb_begin + kb) * kBK, P.K, b_dst, g);
             fence_proxy_async_smem();
             mbar_arrive(smem_u32(&hdr->full[st]));
         }
     } else {
-        mbar_wait(smem_u32(&hdr->acc_full), 0, 0x53);
-        tc_fence_after_sync();
         const int m = m0 + warp * 32 + lane;
         const bool mvalid = m < P.M;
         const long long step = P.step ? *P.step : 0;
-        for (int cg = 0; cg < kBN; cg += 16) {
+        bool finish = true;              // this CTA applies the epilogue (always, without split-K)
+        if (P.k_split > 1) {
+            // 1. add this CTA's partial tile into the fp32 workspace; 2. take a ticket; 3. the last CTA of the
+            // tile reads the sum back, leaves zeros behind (the workspace and the counters clean themselves) and
+            // runs the normal epilogue.
+            if (num_kb > 0) {
+                mbar_wait(smem_u32(&hdr->acc_full), 0, 0x53);
+                tc_fence_after_sync();
+                for (int cg = 0; cg < kBN; cg += 16) {
+                    float v[16];
+                    tmem_ld16(tmem_base + ((warp * 32u) << 16) + cg, v);
+                    const int n = n0 + cg;
+                    if (!mvalid || n >= P.N) continue;
+                    float* w = P.ws + static_cast<long long>(m) * P.N + n;
+                    if (n + 16 <= P.N && (P.N & 3) == 0) {        // 16-byte vector reductions
+#pragma unroll
+                        for (int i = 0; i < 16; i += 4)
+                            asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(w + i), "f"(v[i]), "f"(v[i + 1]),
+                                         "f"(v[i + 2]), "f"(v[i + 3]) : "memory");
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) if (n + i < P.N) atomicAdd(w + i, v[i]);
+                    }
+                }
+            }
+            __threadfence();
+            named_bar_sync(1, 128);
+            unsigned int* ctr = P.tile_counters + blockIdx.y * gridDim.x + blockIdx.x;
+            if (tid == 0) hdr->pad = atomicAdd(ctr, 1u);
+            named_bar_sync(1, 128);
+            finish = hdr->pad == static_cast<uint32_t>(P.k_split - 1);
+            if (finish) {
+                __threadfence();
+                if (tid == 0) *ctr = 0u;
+            }
+        } else {
+            mbar_wait(smem_u32(&hdr->acc_full), 0, 0x53);
+            tc_fence_after_sync();
+        }
+        for (int cg = 0; finish && cg < kBN; cg += 16) {
             float v[16];
-            tmem_ld16(tmem_base + ((warp * 32u) << 16) + cg, v);
             const int n = n0 + cg;
-            if (!mvalid || n >= P.N) continue;
+            if (P.k_split > 1) {
+                if (!mvalid || n >= P.N) continue;
+                float* w = P.ws + static_cast<long long>(m) * P.N + n;
+                if (n + 16 <= P.N && (P.N & 3) == 0) {
+#pragma unroll
+                    for (int i = 0; i < 16; i += 4) {
+                        const float4 t = __ldcg(reinterpret_cast<const float4*>(w + i));
+                        __stcg(reinterpret_cast<float4*>(w + i), make_float4(0.f, 0.f, 0.f, 0.f));
+                        v[i] = t.x; v[i + 1] = t.y; v[i + 2] = t.z; v[i + 3] = t.w;
+                    }
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) {
+                        v[i] = 0.f;
+                        if (n + i < P.N) { v[i] = __ldcg(w + i); __stcg(w + i, 0.f); }
+                    }
+                }
+            } else {
+                tmem_ld16(tmem_base + ((warp * 32u) << 16) + cg, v);
+                if (!mvalid || n >= P.N) continue;
+            }
             const long long o = static_cast<long long>(m) * P.ldo + n;
 #pragma unroll
             for (int i = 0; i < 16; ++i) {
@@ -268,8 +330,10 @@ act_mask_kernel(const dtf_bf16* __restrict__ g_in, const dtf_bf16* __restrict__ 
 
 #define DTF_CHECK_LAUNCH() (cudaGetLastError() == cudaSuccess ? DTF_OK : DTF_ERR_CUDA)
 
-extern "C" int dtf_gemm(const DtfGemm* p, cudaStream_t stream) {
+extern "C" int dtf_gemm(const DtfGemm* pin, cudaStream_t stream) {
     using namespace dtf;
+    DtfGemm q = *pin;
+    DtfGemm* p = &q;
     if (p->M < 1 || p->N < 1 || p->K < 1) return DTF_ERR_SHAPE;
     if ((p->lda & 7) || (p->ldb & 7) || ((uintptr_t)p->a & 15) || ((uintptr_t)p->b & 15)) return DTF_ERR_ARG;
     if (!p->a_mn_major && (p->K & 7)) return DTF_ERR_SHAPE;          // 16-byte chunks along K
@@ -282,7 +346,24 @@ extern "C" int dtf_gemm(const DtfGemm* p, cudaStream_t stream) {
         if (cudaFuncSetAttribute(gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes) != cudaSuccess) return DTF_ERR_CUDA;
         set = 1;
     }
-    dim3 grid((p->M + kBM - 1) / kBM, (p->N + kBN - 1) / kBN);
+    // split-K when the caller provided a (zeroed, self-cleaning) workspace and the output tiles alone cannot
+    // fill the GPU: aim for ~32 CTAs (measured optimum of 1 / 32 / 64 / 120 for the MNIST dense layer; more splits
+    // pay more in reductions than they save), at least two K blocks per CTA
+    const int gx = (p->M + kBM - 1) / kBM, gy = (p->N + kBN - 1) / kBN;
+    const int total_kb = (p->K + kBK - 1) / kBK;
+    int ks = 1;
+    if (p->ws != nullptr && p->tile_counters != nullptr && gx * gy < 64 && gx * gy <= p->max_tiles) {
+        static int target = 0;
+        if (target == 0) { const char* e = getenv("DTF_GEMM_SPLIT_TARGET"); target = e ? atoi(e) : 32; if (target < 1) target = 1; }
+        ks = target / (gx * gy);
+        if (ks > total_kb / 2) ks = total_kb / 2;
+        if (ks > 32) ks = 32;
+        if (ks < 1) ks = 1;
+        const int per = (total_kb + ks - 1) / ks;
+        ks = (total_kb + per - 1) / per;              // no empty splits
+    }
+    p->k_split = ks;
+    dim3 grid(gx, gy, ks);
     dtf_launch(gemm_kernel, grid, dim3(kGThreads), smem_bytes, stream, *p);
     return DTF_CHECK_LAUNCH();
 }

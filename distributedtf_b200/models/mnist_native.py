@@ -89,6 +89,9 @@ class NativeMnistEngine(NativeEngineBase):
         self.g_p1, self.g_c1 = bf(mb, 7, 7, 64), bf(mb, 14, 14, 64)
         self.g_p0, self.g_c0 = bf(mb, 14, 14, 32), bf(mb, 28, 28, 32)
         self.logits = torch.zeros(mb, 10, dtype=torch.float32, device=dev)
+        # split-K workspace of the dense-layer GEMMs (self-cleaning: zero between launches)
+        self.gemm_ws = torch.zeros(mb * 3136, dtype=torch.float32, device=dev)
+        self.gemm_ctr = torch.zeros(64, dtype=torch.int32, device=dev)
 
     # ------------------------------------------------------------------ params
     def _view(self, base, off, *shape):
@@ -136,7 +139,7 @@ class NativeMnistEngine(NativeEngineBase):
         n.maxpool_fwd(self.c1, self.p1, nb, 14, 14, 64)
         n.gemm(self.p1, self.pack[self.d0_pack:], self.h, M=nb, N=1024, K=3136, lda=3136, ldb=3136, ldo=1024,
                bias=self.params[self.d0_b:], relu=True, dropout_keep=self.dropout_keep if training else 1.0,
-               seed=self._seed, step=self.step_dev)
+               seed=self._seed, step=self.step_dev, ws=self.gemm_ws, tile_counters=self.gemm_ctr)
         self._count += 5
 
     def _head(self, nb: int, training: bool, loss=None, correct=None) -> None:
@@ -162,7 +165,7 @@ class NativeMnistEngine(NativeEngineBase):
         n.gemm(self.g_z, self.p1, self._view(self.grads, self.d0_w, 1024, 3136), M=1024, N=3136, K=nb, lda=1024,
                ldb=3136, ldo=3136, a_mn_major=True, b_mn_major=True)
         n.gemm(self.g_z, self.pack[self.d0_pack:], self.g_p1, M=nb, N=3136, K=1024, lda=1024, ldb=3136, ldo=3136,
-               b_mn_major=True)
+               b_mn_major=True, ws=self.gemm_ws, tile_counters=self.gemm_ctr)
         # conv 2
         n.maxpool_bwd(self.c1, self.p1, self.g_p1, self.g_c1, self.grads[self.c1_b:], nb, 14, 14, 64)
         n.conv_wgrad(n.gather(self.p0, 14, 14, 32, KH=5, KW=5, stride=1, pad=2), n.gather(self.g_c1, 14, 14, 64),

@@ -171,14 +171,19 @@ class Gemm(C.Structure):
                 ("lda", C.c_longlong), ("ldb", C.c_longlong), ("ldo", C.c_longlong),
                 ("M", C.c_int), ("N", C.c_int), ("K", C.c_int),
                 ("a_mn_major", C.c_int), ("b_mn_major", C.c_int), ("out_fp32", C.c_int), ("relu", C.c_int),
-                ("dropout_keep", C.c_float), ("seed", C.c_uint)]
+                ("dropout_keep", C.c_float), ("seed", C.c_uint),
+                ("ws", C.c_void_p), ("tile_counters", C.c_void_p), ("max_tiles", C.c_int), ("k_split", C.c_int)]
 
 
 def gemm(a, b, out, *, M: int, N: int, K: int, lda: int, ldb: int, ldo: int, a_mn_major=False, b_mn_major=False,
-         bias=None, relu=False, dropout_keep: float = 1.0, seed: int = 0, step=None) -> None:
-    """out[M][N] = A x B^T (see include/dtf_b200.h: DtfGemm); ``out`` fp32 or bf16."""
+         bias=None, relu=False, dropout_keep: float = 1.0, seed: int = 0, step=None, ws=None, tile_counters=None) -> None:
+    """out[M][N] = A x B^T (see include/dtf_b200.h: DtfGemm); ``out`` fp32 or bf16.  ``ws`` (fp32, >= M*N, zero)
+    and ``tile_counters`` (int32, zero) enable split-K for shapes with few output tiles."""
+    use_ws = ws is not None and tile_counters is not None and ws.numel() >= M * N
     p = Gemm(ptr(a), ptr(b), ptr(out), ptr(bias), ptr(step), lda, ldb, ldo, M, N, K, int(a_mn_major),
-             int(b_mn_major), int(out.dtype == torch.float32), int(relu), dropout_keep, seed & 0xFFFFFFFF)
+             int(b_mn_major), int(out.dtype == torch.float32), int(relu), dropout_keep, seed & 0xFFFFFFFF,
+             ptr(ws) if use_ws else None, ptr(tile_counters) if use_ws else None,
+             int(tile_counters.numel()) if use_ws else 0, 1)
     check(lib().dtf_gemm(C.byref(p), stream_ptr()), "dtf_gemm")
 
 

@@ -254,6 +254,12 @@ typedef struct {
     int a_mn_major, b_mn_major, out_fp32, relu;
     float dropout_keep;      /* 1.0 = no dropout */
     unsigned int seed;
+    /* optional split-K: `ws` = fp32 [M][N] workspace and `tile_counters` = one uint per 128x128 output tile
+     * (max_tiles of them), both zero before the first call; the kernel leaves them zero again. */
+    float* ws;
+    unsigned int* tile_counters;
+    int max_tiles;
+    int k_split;             /* filled by the launcher */
 } DtfGemm;
 int dtf_gemm(const DtfGemm* p, cudaStream_t stream);
 int dtf_maxpool_fwd(const dtf_bf16* x, dtf_bf16* y, int NB, int H, int W, int C, cudaStream_t stream);

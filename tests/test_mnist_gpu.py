@@ -58,6 +58,32 @@ def test_gemm_dense_backward_shapes(nat, batch):
     close(gflat, gz.float() @ w.float(), 1e-2, 1e-3, "dense dgrad")
 
 
+@pytest.mark.parametrize("batch", [65, 128, 256])
+def test_gemm_split_k_matches_and_cleans_up(nat, batch):
+    """Dense-layer shapes with few output tiles run split-K (partial tiles summed in an fp32 workspace, the last
+    CTA of a tile applies the epilogue): same results as the single-pass kernel, twice in a row, and the
+    workspace / counters are zero again afterwards."""
+    x = rnd(batch, 3136, seed=1).bfloat16()
+    w = rnd(1024, 3136, scale=0.02, seed=2).bfloat16()
+    bias = rnd(1024, scale=0.1, seed=3)
+    gz = rnd(batch, 1024, scale=0.05, seed=4).bfloat16()
+    ws = torch.zeros(batch * 3136, device="cuda")
+    ctr = torch.zeros(64, dtype=torch.int32, device="cuda")
+    want_f = torch.relu(x.float() @ w.float().t() + bias)
+    want_d = gz.float() @ w.float()
+    for rep in range(2):
+        h = torch.full((batch, 1024), float("nan"), device="cuda", dtype=torch.bfloat16)
+        nat.gemm(x, w, h, M=batch, N=1024, K=3136, lda=3136, ldb=3136, ldo=1024, bias=bias, relu=True,
+                 ws=ws, tile_counters=ctr)
+        close(h, want_f, 1e-2, 2e-2, f"split-K forward rep {rep}")
+        g = torch.full((batch, 3136), float("nan"), device="cuda", dtype=torch.bfloat16)
+        nat.gemm(gz, w, g, M=batch, N=3136, K=1024, lda=1024, ldb=3136, ldo=3136, b_mn_major=True,
+                 ws=ws, tile_counters=ctr)
+        close(g, want_d, 1e-2, 2e-3, f"split-K dgrad rep {rep}")
+        torch.cuda.synchronize()
+        assert float(ws.abs().max()) == 0.0 and int(ctr.abs().max()) == 0
+
+
 def test_gemm_dropout_statistics(nat):
     M, N, K = 256, 1024, 64
     a, b = torch.ones(M, K, device="cuda").bfloat16(), torch.ones(N, K, device="cuda").bfloat16() / K
