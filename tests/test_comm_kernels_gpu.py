@@ -128,12 +128,12 @@ def _two_rank(rank, world, port, fn_name, q):
         dist.destroy_process_group()
 
 
-def _run2(fn_name):
+def _run2(fn_name, world=2):
     import torch.multiprocessing as mp
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_two_rank, args=(r, 2, port, fn_name, q)) for r in range(2)]
+    procs = [ctx.Process(target=_two_rank, args=(r, world, port, fn_name, q)) for r in range(world)]
     for p in procs:
         p.start()
     res = [q.get(timeout=240) for _ in procs]
@@ -217,14 +217,15 @@ def _dp_step(rank, world):
     g = torch.Generator().manual_seed(1)
     imgs = torch.randint(0, 256, (64, 32, 32, 3), dtype=torch.uint8, generator=g)
     labels = torch.randint(0, 10, (64,), generator=g)
-    lo, hi = rank * 32, rank * 32 + 32
+    per = 64 // world
+    lo, hi = rank * per, rank * per + per
     losses = [eng.train_step_u8(imgs[lo:hi].to(dev), labels[lo:hi].to(dev), augment=False).clone()]
     torch.cuda.synchronize()
     dist.barrier()
     mine = eng.grads[: eng.n_params].clone()
     both = [torch.zeros_like(mine) for _ in range(world)]
     dist.all_gather(both, mine)
-    gmean = (both[0] + both[1]) / 2
+    gmean = sum(both) / world
     reg = torch.zeros_like(start)
     reg[: eng.n_conv_params] = 2e-4 * start[: eng.n_conv_params]
     want = start - 0.1 * 64 / 128 * (gmean + reg)          # first Momentum step: accumulator = gradient
@@ -246,3 +247,15 @@ def test_dp2_allreduce_update_two_gpus(nat):
     assert all(l == l for l in res[0]["loss"])
     assert res[0]["grads_differ"]                      # the replicas really saw different shards
     assert res[0]["err"] < 1e-6 and res[1]["err"] < 1e-6, (res[0]["err"], res[1]["err"])
+
+
+@pytest.mark.multigpu
+def test_dp4_allreduce_update_four_gpus(nat):
+    """Same check with the member sharded over four GPUs (one-shot all-reduce over three peers)."""
+    if torch.cuda.device_count() < 4:
+        pytest.skip("needs 4 GPUs")
+    res = _run2("_dp_step", world=4)
+    for r in range(1, 4):
+        assert torch.equal(res[0]["params"], res[r]["params"])
+    assert all(res[r]["step"] == 4 and res[r]["err"] < 1e-6 for r in range(4)), [res[r]["err"] for r in range(4)]
+    assert res[0]["grads_differ"]
