@@ -380,7 +380,7 @@ DTF_DEVINL void conv3x3_wgrad_body(const DtfConvWgrad& P, const HaloGeom& G, con
 
     if (tid == 0) {
         for (int i = 0; i < kHStages; ++i) {
-            mbar_init(smem_u32(&hdr->full[i]), kHGatherThreads);
+            mbar_init(smem_u32(&hdr->full[i]), kHGatherThreads + kTileM);   // x gather warps + gy' rows (epilogue warps)
             mbar_init(smem_u32(&hdr->empty[i]), 1);
         }
         mbar_init(smem_u32(&hdr->acc_full[0]), 1);
@@ -443,26 +443,15 @@ DTF_DEVINL void conv3x3_wgrad_body(const DtfConvWgrad& P, const HaloGeom& G, con
             const uint32_t gy_base = smem_u32(smem_a) + st * G.stage_bytes;
             const uint32_t im_base = gy_base + gy_bytes;
             const uint32_t halo_base = im_base + im_bytes;
-            RowJob jx, jg;
+            RowJob jx;
             uint32_t pix = 0;
             jx.valid = has_row && decode_virtual(tile * kTileM - G.Wp - 1 + g, G, pix);
             jx.src = P.x.src + static_cast<size_t>(pix) * Cin;
             jx.src2 = nullptr;
             jx.dst = halo_base + g * 16;
-            uint32_t pix2 = 0;
-            jg.valid = g < kTileM && decode_virtual(tile * kTileM + g, G, pix2);
-            jg.src = P.gy.src + static_cast<size_t>(pix2) * P.Cout;
-            jg.src2 = P.gy.src2 ? P.gy.src2 + static_cast<size_t>(pix2) * P.Cout : nullptr;
-            jg.dst = gy_base + g * 16;
             mbar_wait(smem_u32(&hdr->empty[st]), ((it / nstages) & 1) ^ 1, 0x42);
             if (g == 0 && it < 4) DTF_MARK(16 + 4 * it);
             if (has_row) { RowJob j1[1] = {jx}; gather_rows<C8, 1>(j1, 1, G.cs, P.x.mode, cst->p0, cst->p1, cst->p2); }
-            if (g < kTileM) {
-                RowJob j1[1] = {jg};
-                if (G.gy_c8 == 2) gather_rows<2, 1>(j1, 1, kChunkBytes, P.gy.mode, cst->q0, cst->q1, cst->q2);
-                else if (G.gy_c8 == 4) gather_rows<4, 1>(j1, 1, kChunkBytes, P.gy.mode, cst->q0, cst->q1, cst->q2);
-                else gather_rows<8, 1>(j1, 1, kChunkBytes, P.gy.mode, cst->q0, cst->q1, cst->q2);
-            }
             if (g == 0 && it < 4) DTF_MARK(17 + 4 * it);
             named_bar_sync(2, kHGatherThreads);          // the halo tile is complete (gather warps only)
             if (g == 0 && it < 4) DTF_MARK(18 + 4 * it);
@@ -489,6 +478,26 @@ DTF_DEVINL void conv3x3_wgrad_body(const DtfConvWgrad& P, const HaloGeom& G, con
             if (g == 0 && it < 4) DTF_MARK(19 + 4 * it);
         }
     } else if (my_tiles > 0) {
+        // The four epilogue warps have nothing to flush until the last tile: they load the gy' tile (128 rows = one
+        // row per thread, BN-backward prologue with its two sources) while the gather warps load and expand the
+        // x halo, so the two halves of a tile's operand traffic run side by side instead of back to back.
+        for (int it = 0; it < my_tiles; ++it) {
+            const int tile = cta + it * ncta;
+            const uint32_t st = it % nstages;
+            RowJob jg;
+            uint32_t pix2 = 0;
+            jg.valid = decode_virtual(tile * kTileM + tid, G, pix2);
+            jg.src = P.gy.src + static_cast<size_t>(pix2) * P.Cout;
+            jg.src2 = P.gy.src2 ? P.gy.src2 + static_cast<size_t>(pix2) * P.Cout : nullptr;
+            jg.dst = smem_u32(smem_a) + st * G.stage_bytes + tid * 16;
+            mbar_wait(smem_u32(&hdr->empty[st]), ((it / nstages) & 1) ^ 1, 0x44);
+            RowJob j1[1] = {jg};
+            if (G.gy_c8 == 2) gather_rows<2, 1>(j1, 1, kChunkBytes, P.gy.mode, cst->q0, cst->q1, cst->q2);
+            else if (G.gy_c8 == 4) gather_rows<4, 1>(j1, 1, kChunkBytes, P.gy.mode, cst->q0, cst->q1, cst->q2);
+            else gather_rows<8, 1>(j1, 1, kChunkBytes, P.gy.mode, cst->q0, cst->q1, cst->q2);
+            fence_proxy_async_smem();
+            mbar_arrive(smem_u32(&hdr->full[st]));
+        }
         mbar_wait(smem_u32(&hdr->acc_full[0]), 0, 0x43);
         tc_fence_after_sync();
         if (tid == 0) DTF_MARK(32);
@@ -716,11 +725,11 @@ extern "C" int dtf_conv3x3_bwd_fused_try(const DtfConvGemm* pd, const DtfConvWgr
     // Split the SMs between the two halves so that the slower half finishes as early as possible.  Both halves
     // walk whole tiles, so the cost of a split is max(ceil(T / n_d) * t_d, ceil(T / gx) * t_w); the per-tile
     // weights were fitted to a sweep of the split on B200 (bench/conv_micro.py with DTF_BWD_SPLIT=percent):
-    // 16 ch: 1.0 / 1.15, 32 ch: 2.5 / 2.0, 64 ch (two tap groups): 2.5 / 3.0.  A fixed 45 % cost 15 % on the
-    // 32-channel layers (5 dgrad tiles per CTA instead of 4).
+    // 16 ch: 1.0 / 0.88, 32 ch: 2.5 / 1.2, 64 ch (two tap groups): 2.5 / 1.5 (re-fitted after the gy' gather moved
+    // to the epilogue warps, which made the wgrad tiles cheaper).  A fixed 45 % costs 10-15 % on every stage.
     static int pct = -1;
     if (pct < 0) { const char* e = getenv("DTF_BWD_SPLIT"); pct = e ? atoi(e) : 0; if (pct < 5 || pct > 95) pct = 0; }
-    const double t_d = Gd.c8 == 2 ? 1.0 : 2.5, t_w = Gd.c8 == 2 ? 1.15 : (Gd.c8 == 4 ? 2.0 : 3.0);
+    const double t_d = Gd.c8 == 2 ? 1.0 : 2.5, t_w = Gd.c8 == 2 ? 0.88 : (Gd.c8 == 4 ? 1.2 : 1.5);
     int n_d = (sms * 45) / 100;
     if (pct > 0) {
         n_d = (sms * pct) / 100;
