@@ -203,7 +203,7 @@ conv_wgrad_kernel(const __grid_constant__ DtfConvWgrad P) {
 
     if (tid == 0) {
         for (int i = 0; i < 2; ++i) {
-            mbar_init(smem_u32(&hdr->full[i]), kGatherGroup);
+            mbar_init(smem_u32(&hdr->full[i]), kGatherGroup + kTileM);   // x rows (one gather group) + gy' rows (epilogue warps)
             mbar_init(smem_u32(&hdr->empty[i]), 1);
         }
         mbar_init(smem_u32(&hdr->acc_full[0]), 1);
@@ -255,13 +255,26 @@ conv_wgrad_kernel(const __grid_constant__ DtfConvWgrad P) {
             mbar_wait(smem_u32(&hdr->empty[group]), ((it >> 1) & 1) ^ 1, 7);
             const uint32_t a_dst = smem_u32(smem_ab) + group * buf_bytes + row * 16;
             const uint32_t b_dst = a_dst + gy_chunks * kChunkBytes;
-            // gy' chunks: a 1x1 "gather" at the output pixel itself
-            gather_row(P.gy, hdr->tap_dy + 31, hdr->tap_dx + 31, cst->q0, cst->q1, cst->q2, rc, 0, gy_chunks, a_dst);
             gather_row(P.x, hdr->tap_dy, hdr->tap_dx, cst->p0, cst->p1, cst->p2, rc, j0, j0 + nj, b_dst);
             fence_proxy_async_smem();
             mbar_arrive(smem_u32(&hdr->full[group]));
         }
     } else if (has_work) {
+        // The epilogue warps only flush at the very end: meanwhile they load the gy' rows of every tile (one row
+        // per thread), in parallel with the gather groups that build the im2col operand.
+        {
+            const int row = tid;                               // 4 warps = 128 rows
+            uint32_t it = 0;
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+                const uint32_t buf = it & 1;
+                const RowCoord rc = row_coord(tile * kTileM + row, M, P.Ho, P.Wo);
+                mbar_wait(smem_u32(&hdr->empty[buf]), ((it >> 1) & 1) ^ 1, 9);
+                const uint32_t a_dst = smem_u32(smem_ab) + buf * buf_bytes + row * 16;
+                gather_row(P.gy, hdr->tap_dy + 31, hdr->tap_dx + 31, cst->q0, cst->q1, cst->q2, rc, 0, gy_chunks, a_dst);
+                fence_proxy_async_smem();
+                mbar_arrive(smem_u32(&hdr->full[buf]));
+            }
+        }
         mbar_wait(smem_u32(&hdr->acc_full[0]), 0, 8);
         tc_fence_after_sync();
         const int co = warp * 32 + lane;                   // TMEM lane = output channel
