@@ -252,7 +252,9 @@ def test_native_step_matches_oracle(nat, size, nb):
         assert e < 0.02, f"{k}: {e}"
     if size == 8:
         assert worst < 0.15, "gradient errors: " + " ".join(report)
-    assert min(cosines) > 0.75 and sum(cosines) / len(cosines) > 0.85, " ".join(report)
+    # (the minimum is always a 16-element BN vector near the input; over repeated runs it moves between 0.78 and 0.87
+    # with the order of the fp32 atomics, the mean stays at 0.937 +- 0.002)
+    assert min(cosines) > 0.6 and sum(cosines) / len(cosines) > 0.9, " ".join(report)
     # running statistics moved like the oracle's (momentum 0.003)
     after = eng.export_named()
     for k in named:
