@@ -146,6 +146,10 @@ def _declare(l: C.CDLL) -> None:
     l.dtf_maxpool_bwd.argtypes = [vp, vp, vp, vp, vp, i, i, i, i, vp]
     l.dtf_act_mask.argtypes = [vp, vp, vp, vp, f, ll, i, vp]
     l.dtf_set_sm_limit.argtypes = [i]
+    l.dtf_cifar_decode.argtypes = [vp, ll, vp, vp, i]
+    l.dtf_read_file.argtypes = [C.c_char_p, ll, vp, ll]
+    l.dtf_read_file.restype = ll
+    l.dtf_idx_header.argtypes = [vp, ll, vp, vp, i]
     l.dtf_io_create.argtypes = [i]
     l.dtf_io_create.restype = vp
     l.dtf_io_submit.argtypes = [vp, C.c_char_p, vp, C.c_ulonglong, vp, i, C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p]

@@ -60,11 +60,40 @@ def load_cifar10(data_dir: str, train: bool, device="cpu") -> Dataset:
     if not os.path.isdir(root):
         raise FileNotFoundError(f"{root} not found (expected the CIFAR-10 binary version)")
     names = [f"data_batch_{i}.bin" for i in range(1, 6)] if train else ["test_batch.bin"]
-    raw = np.concatenate([np.fromfile(os.path.join(root, n), dtype=np.uint8) for n in names])
+    paths = [os.path.join(root, n) for n in names]
+    native = _native_lib()
+    if native is not None:                    # csrc/host_data.cpp: threaded record decode straight into the tensors
+        sizes = [os.path.getsize(p) for p in paths]
+        if any(sz % _CIFAR_RECORD for sz in sizes):
+            raise ValueError("CIFAR-10 binary file size is not a multiple of the 3073-byte record")
+        n = sum(sizes) // _CIFAR_RECORD
+        raw = torch.empty(sum(sizes), dtype=torch.uint8)
+        off = 0
+        for p, sz in zip(paths, sizes):
+            got = native.dtf_read_file(p.encode(), 0, raw.data_ptr() + off, sz)
+            if got != sz:
+                raise IOError(f"short read on {p}: {got} of {sz} bytes")
+            off += sz
+        images = torch.empty(n, 32, 32, 3, dtype=torch.uint8)
+        labels = torch.empty(n, dtype=torch.int32)
+        rc = native.dtf_cifar_decode(raw.data_ptr(), n, images.data_ptr(), labels.data_ptr(), min(8, os.cpu_count() or 1))
+        if rc != 0:
+            raise RuntimeError(f"dtf_cifar_decode failed: {rc}")
+        return Dataset(images.to(device), labels.to(device), "CIFAR-10")
+    raw = np.concatenate([np.fromfile(p, dtype=np.uint8) for p in paths])
     rec = raw.reshape(-1, _CIFAR_RECORD)
     labels = torch.from_numpy(rec[:, 0].astype(np.int32))
     images = torch.from_numpy(rec[:, 1:].reshape(-1, 3, 32, 32).transpose(0, 2, 3, 1).copy())
     return Dataset(images.to(device), labels.to(device), "CIFAR-10")
+
+
+def _native_lib():
+    """The native host runtime when the library is built (readers fall back to numpy otherwise)."""
+    try:
+        from ...ops import native
+        return native.lib() if native.available() else None
+    except Exception:
+        return None
 
 
 def load_mnist(data_dir: str, train: bool, device="cpu") -> Dataset:

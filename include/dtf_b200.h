@@ -293,6 +293,12 @@ int dtf_io_wait_all(void* writer);
 int dtf_io_pending(void* writer);
 long long dtf_io_bytes_written(void* writer);
 void dtf_io_destroy(void* writer);
+/* ---- host runtime: dataset readers (csrc/host_data.cpp) -----------------------------------------------------
+ * CIFAR-10 binary records (label + CHW planes; cifar10_main.py:54-109) -> HWC uint8 images + int32 labels with a
+ * few threads; raw file read; idx (MNIST, mnist_model.py:128-150) header parse.  Host memory only. */
+int dtf_cifar_decode(const uint8_t* records, long long n, uint8_t* images, int* labels, int threads);
+long long dtf_read_file(const char* path, long long offset, void* dst, long long nbytes);
+int dtf_idx_header(const uint8_t* buf, long long nbytes, int* ndim, int* dims, int max_dims);
 /* debugging aid: native backtrace of the faulting thread on SIGSEGV, then the previous handler */
 void dtf_install_crash_handler(void);
 

@@ -137,3 +137,35 @@ def test_static_loss_scale_leaves_the_update_unchanged():
     assert torch.allclose(flats[0], flats[1], rtol=1e-4, atol=1e-6)
     assert EagerEngine(resnet.param_specs(cfg), None, resnet.init_params(cfg, "None", 0), hp, "cpu",
                        compute_dtype=torch.float16).loss_scale == 128.0
+
+
+def test_native_cifar_decode_equals_numpy(tmp_path):
+    """csrc/host_data.cpp: threaded CHW-record -> HWC decode and the idx header parser against numpy."""
+    import ctypes as C
+    from distributedtf_b200.ops import native
+    if not native.available():
+        pytest.skip("native library not built")
+    lib = native.lib()
+    rng = np.random.default_rng(3)
+    n = 2500                                              # > 1024: exercises the threaded path
+    rec = rng.integers(0, 256, (n, 3073), dtype=np.uint8)
+    rec[:, 0] %= 10
+    raw = torch.from_numpy(rec.reshape(-1).copy())
+    images = torch.empty(n, 32, 32, 3, dtype=torch.uint8)
+    labels = torch.empty(n, dtype=torch.int32)
+    assert lib.dtf_cifar_decode(raw.data_ptr(), n, images.data_ptr(), labels.data_ptr(), 4) == 0
+    assert np.array_equal(labels.numpy(), rec[:, 0].astype(np.int32))
+    assert np.array_equal(images.numpy(), rec[:, 1:].reshape(n, 3, 32, 32).transpose(0, 2, 3, 1))
+    # file read with offset
+    path = tmp_path / "blob.bin"
+    path.write_bytes(bytes(range(256)) * 4)
+    buf = torch.zeros(100, dtype=torch.uint8)
+    assert lib.dtf_read_file(str(path).encode(), 250, buf.data_ptr(), 100) == 100
+    assert buf[:6].tolist() == [250, 251, 252, 253, 254, 255] and buf[6] == 0
+    # idx header
+    hdr = struct.pack(">IIII", 2051, 7, 28, 28) + bytes(7 * 28 * 28)
+    arr = torch.frombuffer(bytearray(hdr), dtype=torch.uint8)
+    nd, dims = C.c_int(), (C.c_int * 4)()
+    off = lib.dtf_idx_header(arr.data_ptr(), arr.numel(), C.byref(nd), dims, 4)
+    assert off == 16 and nd.value == 3 and list(dims)[:3] == [7, 28, 28]
+    assert lib.dtf_idx_header(arr.data_ptr(), 10, C.byref(nd), dims, 4) < 0
