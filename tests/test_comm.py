@@ -134,3 +134,22 @@ def test_local_fabric_abort_unblocks_recv():
     fabric.abort(ValueError("worker died"))
     t.join(5)
     assert not t.is_alive() and got and "worker died" in str(got[0])
+
+
+def test_tcp_master_notices_a_dead_worker():
+    """a worker process that dies must surface at the master as an error, not as a hang."""
+    import socket
+    import threading
+    from distributedtf_b200.parallel.tcp import TcpMasterComm, TcpWorkerComm
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    master = TcpMasterComm("127.0.0.1", port, 2)
+    worker = TcpWorkerComm("127.0.0.1", port, 1, 2)
+    master.wait_for_workers()
+    master.isend(("ping",), dest=1)
+    assert worker.recv(source=0, timeout=10) == ("ping",)
+    worker.close()                                   # the worker goes away without answering
+    with pytest.raises(ConnectionError):
+        master.recv(source=1, timeout=10)
+    master.close()
