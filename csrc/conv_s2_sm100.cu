@@ -44,8 +44,8 @@ DTF_DEVINL S2Row s2_row(int m, int Mc, int Hh, int Wh) {
     return r;
 }
 
-// One row of the operand tile: for every tap of the parity class, all chunks of the row.
-// All loads of up to `BUDGET` chunks are issued before the first is consumed.
+// TPB taps of one row starting at tap t0: every chunk of every tap is loaded (both sources when TWO) before the
+// first one goes through the prologue and into shared memory.
 template <int L, bool TWO, int TPB>
 DTF_DEVINL void s2_batch_t(const DtfGather& G, const S2Header* hdr, const SmemConsts* cst, int cls, const S2Row& rc,
                            int rowbase, uint32_t dst, int t0) {
@@ -87,9 +87,8 @@ DTF_DEVINL void s2_batch_t(const DtfGather& G, const S2Header* hdr, const SmemCo
     }
 }
 
-// One row of the operand tile: for every tap of the parity class (1, 2 or 4), this thread's chunks
-// The loads of a batch are issued before the first is consumed; batches are
-// sized to the class so that no dead tap costs instructions.
+// One row of the operand tile, all taps of its parity class (1, 2 or 4).  The loads of a batch are issued before
+// the first is consumed; batches are sized to the class so that no dead tap costs instructions.
 template <int L, bool TWO>
 DTF_DEVINL void s2_gather_t(const DtfGather& G, const S2Header* hdr, const SmemConsts* cst, int cls, const S2Row& rc,
                             int rowbase, uint32_t dst) {
