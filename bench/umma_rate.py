@@ -2,7 +2,8 @@ import ctypes, sys, os
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from distributedtf_b200.ops import native as nat
-lib = nat.lib()
+import build_native
+lib = ctypes.CDLL(build_native.build_bench())     # micro-benchmark kernels live in their own library (bench/csrc)
 lib.dtf_bench_umma.argtypes = [ctypes.c_int] * 5 + [ctypes.c_void_p, ctypes.c_void_p]
 out = torch.zeros(2, dtype=torch.int64, device="cuda")
 names = {0: "none", 6: "sw32", 4: "sw64", 2: "sw128"}

@@ -76,6 +76,26 @@ def build(force: bool = False, verbose: bool = False) -> str:
     return LIB
 
 
+BENCH_SRC = os.path.join(ROOT, "bench", "csrc")
+BENCH_LIB = os.path.join(OUT_DIR, "libdtf_bench.so")
+
+
+def build_bench() -> str:
+    """Micro-benchmark kernels (bench/csrc): their own library, never linked into libdtf_b200.so."""
+    os.makedirs(OUT_DIR, exist_ok=True)
+    srcs = sorted(os.path.join(BENCH_SRC, f) for f in os.listdir(BENCH_SRC) if f.endswith(".cu"))
+    if _newer(BENCH_LIB, srcs):
+        return BENCH_LIB
+    cmd = [nvcc()] + NVCC_FLAGS + ["-shared", "-o", BENCH_LIB] + srcs + ["-lcudart"]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        print(r.stdout + r.stderr)
+        raise RuntimeError("bench library build failed")
+    return BENCH_LIB
+
+
 if __name__ == "__main__":
     path = build(force="--force" in sys.argv, verbose="--verbose" in sys.argv)
     print(path)
+    if "--bench" in sys.argv:
+        print(build_bench())

@@ -19,6 +19,8 @@
 #include "common.cuh"
 #include "dtf_b200.h"
 
+#include <mutex>
+
 namespace dtf {
 
 DTF_DEVINL void st_release_sys(unsigned long long* p, unsigned long long v) {
@@ -137,10 +139,11 @@ __global__ void __launch_bounds__(256)
 allreduce_update_kernel(const __grid_constant__ DtfAllreduceUpdate P) {
     __shared__ DtfHparams hp;
     const int W = P.world;
-    // The epoch of this exchange is the device-resident step counter (bumped by dtf_dp_step_begin), so a
-    // captured CUDA graph of the step replays with the right epoch; P.epoch is only an offset.
+    // The epoch of this exchange is a device-resident counter (bumped by dtf_dp_step_begin), so a captured
+    // CUDA graph of the step replays with the right epoch; P.epoch is only an offset.  It is NOT the step
+    // counter: that one is part of the member state and jumps when the member adopts a winner or restores.
     const long long step = *P.step;
-    const unsigned long long epoch = static_cast<unsigned long long>(step) + P.epoch;
+    const unsigned long long epoch = *P.epoch_ctr + P.epoch;
     // ---- entry barrier: tell every peer that my gradients for `epoch` are complete, then wait for theirs
     if (blockIdx.x == 0 && threadIdx.x < W) {
         __threadfence_system();
@@ -219,10 +222,11 @@ allreduce_update_kernel(const __grid_constant__ DtfAllreduceUpdate P) {
 // counter so that no CTA can observe the bumped value while computing its wait target)
 __global__ void __launch_bounds__(256)
 dp_step_begin_kernel(float4* __restrict__ zero, long long n_vec, long long* __restrict__ step_ptr,
+                     unsigned long long* __restrict__ epoch_ctr,
                      const unsigned long long* __restrict__ local_done, int world, unsigned long long epoch_offset,
                      unsigned int* __restrict__ arrive_counter) {
-    // peers must have consumed the gradients of the previous step (= current counter value)
-    const unsigned long long prev_epoch = static_cast<unsigned long long>(*step_ptr) + epoch_offset;
+    // peers must have consumed the gradients of the previous exchange (= current counter value)
+    const unsigned long long prev_epoch = *epoch_ctr + epoch_offset;
     if (threadIdx.x < world) wait_flag_ge(local_done + threadIdx.x, prev_epoch, 2);
     __syncthreads();
     const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -236,6 +240,7 @@ dp_step_begin_kernel(float4* __restrict__ zero, long long n_vec, long long* __re
         if (prev == gridDim.x - 1) {
             *arrive_counter = 0;
             *step_ptr += 1;
+            *epoch_ctr += 1;
         }
     }
 }
@@ -249,8 +254,12 @@ extern "C" int dtf_exploit_copy(void* dst, const void* src, long long bytes, lon
                                 unsigned long long* done_flag, unsigned long long epoch,
                                 unsigned int* arrive_counter, int max_ctas, cudaStream_t stream) {
     if ((bytes & 15) || (zero_bytes & 15) || (hp_offset & 15)) return DTF_ERR_ARG;
+    if (bytes < 0 || zero_bytes < 0) return DTF_ERR_ARG;
     if (((uintptr_t)dst & 15) || ((uintptr_t)src & 15)) return DTF_ERR_ARG;
     if (done_flag != nullptr && arrive_counter == nullptr) return DTF_ERR_ARG;
+    // the hyper-parameter block must lie inside the copied range, or the kernel would write past `dst`
+    if (new_hp != nullptr && (hp_offset < 0 || hp_offset + (long long)((sizeof(DtfHparams) + 15) / 16 * 16) > bytes))
+        return DTF_ERR_ARG;
     const long long n_vec = bytes / 16;
     const int hp_vecs = new_hp ? static_cast<int>((sizeof(DtfHparams) + 15) / 16) : 0;
     DtfHparams hp_val;
@@ -274,21 +283,22 @@ extern "C" int dtf_score_publish(DtfScoreSlot* board_slot, const int* correct, i
 }
 
 extern "C" int dtf_allreduce_update(const DtfAllreduceUpdate* p, cudaStream_t stream) {
-    if (p->world < 1 || p->world > DTF_MAX_DP) return DTF_ERR_ARG;
+    if (p->world < 1 || p->world > DTF_MAX_DP || p->epoch_ctr == nullptr) return DTF_ERR_ARG;
     dtf::allreduce_update_kernel<<<p->n_chunks, 256, 0, stream>>>(*p);
     return DTF_CHECK_LAUNCH();
 }
 
 extern "C" int dtf_dp_step_begin(float* zero_base, long long zero_floats, long long* step,
+                                 unsigned long long* epoch_ctr,
                                  const unsigned long long* local_done, int world, unsigned long long epoch_offset,
                                  unsigned int* arrive_counter, cudaStream_t stream) {
-    if (zero_floats % 4 != 0 || ((uintptr_t)zero_base & 15) != 0) return DTF_ERR_ARG;
+    if (zero_floats % 4 != 0 || ((uintptr_t)zero_base & 15) != 0 || epoch_ctr == nullptr) return DTF_ERR_ARG;
     const long long n_vec = zero_floats / 4;
     long long blocks = (n_vec + 255) / 256;
     if (blocks > 148 * 4) blocks = 148 * 4;
     if (blocks < 1) blocks = 1;
     dtf::dp_step_begin_kernel<<<static_cast<int>(blocks), 256, 0, stream>>>(
-        reinterpret_cast<float4*>(zero_base), n_vec, step, local_done, world, epoch_offset, arrive_counter);
+        reinterpret_cast<float4*>(zero_base), n_vec, step, epoch_ctr, local_done, world, epoch_offset, arrive_counter);
     return DTF_CHECK_LAUNCH();
 }
 
@@ -365,7 +375,10 @@ static __device__ __align__(256) unsigned char g_exploit_noalloc_scratch[kNoAllo
 
 static const int kNoAllocMaxDevices = 64;
 static void* g_noalloc_scratch_ptr[kNoAllocMaxDevices];      // device address of the array, per device
-static char g_noalloc_error[256] = "";
+// Several member threads of one worker may call in at once (worker.members_in_flight): the pointer cache is
+// guarded by a mutex and the error text is kept per calling thread, so neither can be torn.
+static std::mutex g_noalloc_mutex;
+static thread_local char g_noalloc_error[256] = "";
 
 extern "C" const char* dtf_noalloc_last_error(void) { return g_noalloc_error; }
 
@@ -377,6 +390,7 @@ static int noalloc_scratch_for_current_device(void** out) {
         snprintf(g_noalloc_error, sizeof(g_noalloc_error), "dtf_exploit_copy_noalloc: no usable current device (%d)", dev);
         return DTF_ERR_CUDA;
     }
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
     if (g_noalloc_scratch_ptr[dev] == nullptr) {
         void* p = nullptr;
         const cudaError_t e = cudaGetSymbolAddress(&p, dtf::g_exploit_noalloc_scratch);
@@ -404,6 +418,13 @@ extern "C" int dtf_exploit_copy_noalloc(void* dst, const void* src, long long by
     if ((bytes & 15) || (zero_bytes & 15) || (hp_offset & 15) || ((uintptr_t)dst & 15) || ((uintptr_t)src & 15)) {
         snprintf(g_noalloc_error, sizeof(g_noalloc_error),
                  "dtf_exploit_copy_noalloc: pointers, sizes and the hyper-parameter offset must be multiples of 16 bytes");
+        return DTF_ERR_ARG;
+    }
+    if (zero_bytes < 0 ||
+        (new_hp != nullptr && (hp_offset < 0 || hp_offset + (long long)((sizeof(DtfHparams) + 15) / 16 * 16) > bytes))) {
+        snprintf(g_noalloc_error, sizeof(g_noalloc_error),
+                 "dtf_exploit_copy_noalloc: the hyper-parameter block [%lld, +%zu) must lie inside the %lld copied bytes "
+                 "and zero_bytes must not be negative", hp_offset, sizeof(DtfHparams), bytes);
         return DTF_ERR_ARG;
     }
     void* scratch = nullptr;

@@ -79,6 +79,7 @@ class GpuMember(ModelBase):
             self._bench_logger.log_run_info(type(self).__name__, "synthetic" if synthetic else "real",
                                             {"batch_size": int(hparams["batch_size"]), "dtype": dtype,
                                              "engine": engine, "synthetic_data": bool(synthetic)})
+        self._round_batch_to_dp()
         self._board = scoreboard                # {"ptr": local pointer} or {"handle": CUDA IPC handle of the board}
         self._board_ptr: Optional[int] = None
         self.train_set, self.eval_set = self.build_datasets()
@@ -131,8 +132,25 @@ class GpuMember(ModelBase):
                     member.device_times[key] += time.time() - s.t0
         return _T()
 
+    def _round_batch_to_dp(self) -> None:
+        """A data-parallel member keeps its global batch a multiple of its replica count.  Sampled and explored
+        batch sizes are odd about half the time; the reference's ``per_device_batch_size`` would reject those
+        (``distribution_utils.py:58-78``) and the worker would then drop the member, so the value is rounded to the
+        nearest lower multiple (upper at the bottom of the range) instead.  Every replica applies the same rule to
+        the same hyper-parameters, so the group stays consistent."""
+        if self.dp_size <= 1 or "batch_size" not in self.hparams:
+            return
+        bs = int(self.hparams["batch_size"])
+        rounded = bs - bs % self.dp_size
+        if rounded < 65:
+            rounded += self.dp_size
+        self.hparams["batch_size"] = rounded
+
     def train_one_epoch(self) -> int:
         bs = int(self.hparams["batch_size"])
+        if self.dp_size > 1:          # reject before any step runs (reference distribution_utils.py:58-78)
+            from ..parallel.dp import per_device_batch_size
+            per_device_batch_size(bs, self.dp_size)
         self._train_iter.set_batch_size(bs)
         steps = self.steps_per_epoch()
         if self.max_train_steps is not None:
@@ -156,8 +174,6 @@ class GpuMember(ModelBase):
                         h.after_step(self._global_step, vals)
         dt = max(self.device_times["train"], 1e-9)
         self.last_images_per_sec = steps * bs / max(time.time() - t0, 1e-9)
-        if self.dp_size > 1 and bs % self.dp_size:
-            raise ValueError(f"batch_size {bs} is not a multiple of dp_size {self.dp_size}")
         return steps
 
     def _indexed_steps(self) -> bool:
@@ -265,6 +281,7 @@ class GpuMember(ModelBase):
 
     # ------------------------------------------------------------------ state
     def on_hparams_changed(self) -> None:
+        self._round_batch_to_dp()
         if self._pending_exploit is not None and not self._pending_exploit.get("explore_follows", False):
             self.flush_exploit()
         elif self._pending_exploit is None:
@@ -274,6 +291,7 @@ class GpuMember(ModelBase):
     def perturb_hparams(self) -> None:
         from .. import explore as _explore
         _explore.perturb_hparams(self.hparams, self._rng, tuple(self._perturb_factors))
+        self._round_batch_to_dp()
         if self._pending_exploit is not None:
             self.flush_exploit()
         else:

@@ -24,7 +24,7 @@ ERRORS = {-1: "DTF_ERR_SHAPE", -2: "DTF_ERR_SMEM", -3: "DTF_ERR_CUDA", -4: "DTF_
 PRO_NONE, PRO_BN_RELU, PRO_BN_BWD = 0, 1, 3
 EPI_STORE, EPI_RESIDUAL, EPI_BIAS_RELU, EPI_RELU_MASK, EPI_BIAS = 0, 1, 2, 3, 4
 OPT_CHUNK = 1024
-MAX_LR_BOUNDARIES = 12
+MAX_LR_BOUNDARIES = 100
 BN_EPS, BN_DECAY = 1e-5, 0.997
 
 

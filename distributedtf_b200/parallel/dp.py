@@ -28,19 +28,19 @@ from . import symm
 
 vp, ll, ull, i32, f32 = C.c_void_p, C.c_longlong, C.c_ulonglong, C.c_int, C.c_float
 MAX_DP = 8
-FLAG_BYTES = 1024          # ready[8] u64 | done[8] u64 | arrive counters | pad
+FLAG_BYTES = 1024          # ready[8] u64 | done[8] u64 | arrive counters | exchange counter | pad
 
 
 class AllreduceUpdate(C.Structure):
     _fields_ = [("params", vp), ("slot0", vp), ("slot1", vp), ("pack", vp),
                 ("peer_grads", vp * MAX_DP), ("peer_ready", vp * MAX_DP), ("peer_done", vp * MAX_DP),
                 ("local_ready", vp), ("segs", vp), ("chunks", vp), ("hp", vp), ("step", vp),
-                ("arrive_counter", vp), ("epoch", ull), ("grad_scale", f32),
+                ("arrive_counter", vp), ("epoch_ctr", vp), ("epoch", ull), ("grad_scale", f32),
                 ("world", i32), ("rank", i32), ("n_chunks", i32)]
 
 
 native_ext.register("dtf_allreduce_update", [C.POINTER(AllreduceUpdate), vp])
-native_ext.register("dtf_dp_step_begin", [vp, ll, vp, vp, i32, ull, vp, vp])
+native_ext.register("dtf_dp_step_begin", [vp, ll, vp, vp, vp, i32, ull, vp, vp])
 
 
 def per_device_batch_size(batch_size: int, num_gpus: int) -> int:
@@ -100,10 +100,18 @@ class DataParallelGroup:
     def arrive_begin_ptr(self) -> int:
         return self.flag_buf.ptr + 16 * MAX_DP + 64
 
+    @property
+    def epoch_ctr_ptr(self) -> int:
+        """Exchange counter of this replica: counts ``step_begin`` launches since the group was built.  It is
+        deliberately not the member's step counter, which exploit and restore overwrite (members run different
+        batch sizes, so their step counts differ) while ready[] / done[] keep the old epochs."""
+        return self.flag_buf.ptr + 16 * MAX_DP + 128
+
     def step_begin(self, zero_region: torch.Tensor, step_dev: torch.Tensor) -> None:
         n = zero_region.numel() * zero_region.element_size() // 4
         native.check(native.lib().dtf_dp_step_begin(vp(zero_region.data_ptr()), n, vp(step_dev.data_ptr()),
-                                                    vp(self.done_ptr(self.rank)), self.world, 0,
+                                                    vp(self.epoch_ctr_ptr), vp(self.done_ptr(self.rank)),
+                                                    self.world, 0,
                                                     vp(self.arrive_begin_ptr), native.stream_ptr()),
                      "dtf_dp_step_begin")
 
@@ -117,6 +125,7 @@ class DataParallelGroup:
         p.local_ready = self.ready_ptr(self.rank)
         p.segs, p.chunks, p.hp, p.step = segs_dev.data_ptr(), chunks_dev.data_ptr(), hp_dev.data_ptr(), step_dev.data_ptr()
         p.arrive_counter = self.arrive_update_ptr
+        p.epoch_ctr = self.epoch_ctr_ptr
         p.epoch = 0
         p.grad_scale = 1.0 / self.world
         p.world, p.rank, p.n_chunks = self.world, self.rank, n_chunks

@@ -7,12 +7,13 @@ tensors travel here — the tensor path never uses this transport.
 """
 from __future__ import annotations
 
+import time
 from typing import Any, Optional
 
 import torch
 import torch.distributed as dist
 
-from .comm_base import Comm, Request, dumps, loads
+from .comm_base import Comm, CommTimeout, Request, dumps, loads
 
 
 class GlooComm(Comm):
@@ -42,9 +43,22 @@ class GlooComm(Comm):
 
         return Request(waiter)
 
+    def _recv_tensor(self, t: torch.Tensor, source: int, deadline: Optional[float]) -> None:
+        if deadline is None:
+            dist.recv(t, source, group=self._group)
+            return
+        # a dead worker must not hang the master: poll the non-blocking receive
+        work = dist.irecv(t, source, group=self._group)
+        while not work.is_completed():
+            if time.monotonic() > deadline:
+                raise CommTimeout(f"gloo control plane: no message from endpoint {source} within the timeout")
+            time.sleep(0.002)
+        work.wait()
+
     def recv(self, source: int, timeout: Optional[float] = None) -> Any:
+        deadline = None if timeout is None else time.monotonic() + float(timeout)
         header = torch.zeros(1, dtype=torch.int64)
-        dist.recv(header, source, group=self._group)
+        self._recv_tensor(header, source, deadline)
         payload = torch.empty(int(header.item()), dtype=torch.uint8)
-        dist.recv(payload, source, group=self._group)
+        self._recv_tensor(payload, source, deadline)
         return loads(payload.numpy().tobytes())

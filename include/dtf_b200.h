@@ -118,7 +118,8 @@ enum { DTF_OPT_GD = 0, DTF_OPT_MOMENTUM = 1, DTF_OPT_ADAGRAD = 2, DTF_OPT_ADADEL
        DTF_OPT_RMSPROP = 5 };
 enum { DTF_REG_NONE = 0, DTF_REG_L1 = 1, DTF_REG_L2 = 2, DTF_REG_L1_L2 = 3 };
 #define DTF_OPT_CHUNK 1024
-#define DTF_MAX_LR_BOUNDARIES 12
+/* worst case of the CIFAR schedule: decay_steps = 1 gives ceil(100/1) - 1 = 99 boundaries (cifar10_main.py:192-208) */
+#define DTF_MAX_LR_BOUNDARIES 100
 
 /* Device-resident hyper-parameter block of one member: explore rewrites it in place, so a
  * captured CUDA graph of the step never needs re-capture (constants.py:14-43 ranges). */
@@ -207,14 +208,18 @@ typedef struct {
     const DtfOptSegment* segs; const int* chunks;
     const DtfHparams* hp; const long long* step;
     unsigned int* arrive_counter;
-    unsigned long long epoch;                        /* offset added to *step to form the exchange epoch */
+    const unsigned long long* epoch_ctr;             /* exchange counter of the group (bumped by dtf_dp_step_begin);
+                                                        lives OUTSIDE the member state, so exploit / restore never touch it */
+    unsigned long long epoch;                        /* offset added to *epoch_ctr to form the exchange epoch */
     float grad_scale;
     int world, rank, n_chunks;
 } DtfAllreduceUpdate;
 int dtf_allreduce_update(const DtfAllreduceUpdate* p, cudaStream_t stream);
 /* Step begin of a data-parallel member: waits until every peer has consumed this replica's gradients
- * of the previous step (done[w] >= *step + epoch_offset), zeroes the accumulators, bumps *step. */
-int dtf_dp_step_begin(float* zero_base, long long zero_floats, long long* step,
+ * of the previous exchange (done[w] >= *epoch_ctr + epoch_offset), zeroes the accumulators, bumps *step and
+ * *epoch_ctr.  The exchange counter is separate from the step counter because exploit and restore overwrite
+ * the step (members run different batch sizes, hence different step counts) while the flags keep counting. */
+int dtf_dp_step_begin(float* zero_base, long long zero_floats, long long* step, unsigned long long* epoch_ctr,
                       const unsigned long long* local_done, int world, unsigned long long epoch_offset,
                       unsigned int* arrive_counter, cudaStream_t stream);
 

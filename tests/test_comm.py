@@ -153,3 +153,93 @@ def test_tcp_master_notices_a_dead_worker():
     with pytest.raises(ConnectionError):
         master.recv(source=1, timeout=10)
     master.close()
+
+
+def _gloo_silent_rank(rank, size, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(size))
+    import torch.distributed as dist
+    from distributedtf_b200.parallel.comm_base import CommTimeout
+    from distributedtf_b200.parallel.gloo import GlooComm
+    dist.init_process_group("gloo", rank=rank, world_size=size)
+    c = GlooComm()
+    if rank == 0:
+        try:
+            c.recv(source=1, timeout=1.0)        # the worker never answers
+            q.put("no timeout")
+        except CommTimeout as e:
+            q.put("timeout: " + str(e))
+        c.isend("done", dest=1).wait()
+    else:
+        assert c.recv(source=0, timeout=60) == "done"
+    dist.destroy_process_group()
+
+
+def test_gloo_recv_honours_timeout():
+    """A silent worker surfaces as CommTimeout on the gloo transport too (it used to block forever)."""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_gloo_silent_rank, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    out = q.get(timeout=120)
+    for p in procs:
+        p.join(60)
+    assert out.startswith("timeout:"), out
+
+
+def test_mpi_adapter_against_a_fake_mpi4py(monkeypatch):
+    """mpi4py is not on the image: drive MpiComm through a stand-in COMM_WORLD (queues between two threads)
+    so that its isend / recv / timeout code has run at least once."""
+    import queue
+    import sys
+    import threading
+    import types
+    from distributedtf_b200.parallel.comm_base import CommTimeout
+    boxes = {(s, d): queue.Queue() for s in range(2) for d in range(2)}
+    local = threading.local()
+
+    class _Req:
+        def wait(self):
+            return None
+
+    class _World:
+        def Get_rank(self):
+            return local.rank
+
+        def Get_size(self):
+            return 2
+
+        def isend(self, obj, dest):
+            boxes[(local.rank, dest)].put(obj)
+            return _Req()
+
+        def iprobe(self, source):
+            return not boxes[(source, local.rank)].empty()
+
+        def recv(self, source):
+            return boxes[(source, local.rank)].get()
+
+    fake = types.ModuleType("mpi4py")
+    fake.MPI = types.SimpleNamespace(COMM_WORLD=_World())
+    monkeypatch.setitem(sys.modules, "mpi4py", fake)
+    from distributedtf_b200.parallel import mpi
+    assert mpi.available()
+    out = {}
+
+    def worker():
+        local.rank = 1
+        c = mpi.MpiComm()
+        msg = c.recv(source=0, timeout=10)
+        c.send(("echo", msg, c.Get_rank(), c.Get_size()), dest=0)
+
+    t = threading.Thread(target=worker, daemon=True)
+    t.start()
+    local.rank = 0
+    c = mpi.MpiComm()
+    c.isend({"k": 1}, dest=1).wait()
+    out = c.recv(source=1, timeout=10)
+    t.join(5)
+    assert out == ("echo", {"k": 1}, 1, 2)
+    with pytest.raises(CommTimeout):
+        c.recv(source=1, timeout=0.05)

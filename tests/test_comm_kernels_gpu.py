@@ -259,3 +259,40 @@ def test_dp4_allreduce_update_four_gpus(nat):
         assert torch.equal(res[0]["params"], res[r]["params"])
     assert all(res[r]["step"] == 4 and res[r]["err"] < 1e-6 for r in range(4)), [res[r]["err"] for r in range(4)]
     assert res[0]["grads_differ"]
+
+
+def _dp_step_counter_jump(rank, world):
+    """The member's step counter is part of the exploited / restored state: it jumps when a data-parallel
+    member adopts a winner that ran a different batch size, or resumes from a checkpoint.  The flag handshake
+    counts exchanges with its own counter, so both directions (higher and lower step) keep working."""
+    import torch.distributed as dist
+    from distributedtf_b200.models import resnet
+    from distributedtf_b200.models.resnet_native import NativeResNetEngine
+    dev = torch.device("cuda", rank)
+    hp = {"opt_case": {"optimizer": "Momentum", "lr": 0.05, "momentum": 0.9}, "decay_steps": 20, "decay_rate": 0.1,
+          "weight_decay": 2e-4, "regularizer": "l2_regularizer", "initializer": "he_init", "batch_size": 32}
+    eng = NativeResNetEngine(resnet.cifar10_config(8), hp, dev, seed=5, use_graphs=True, dp_group=dist.group.WORLD)
+    g = torch.Generator().manual_seed(1)
+    imgs = torch.randint(0, 256, (32, 32, 32, 3), dtype=torch.uint8, generator=g)
+    labels = torch.randint(0, 10, (32,), generator=g)
+    per = 32 // world
+    x, y = imgs[rank * per:(rank + 1) * per].to(dev), labels[rank * per:(rank + 1) * per].to(dev)
+    steps = []
+    for jump in (None, 5000, 3):          # adopt a member that is far ahead, then one that is behind
+        if jump is not None:
+            torch.cuda.synchronize()
+            dist.barrier()
+            eng.step_dev.fill_(jump)
+        for _ in range(3):
+            eng.train_step_u8(x, y, augment=False)
+        torch.cuda.synchronize()
+        steps.append(eng.step)
+    return {"steps": steps, "params": eng.params[: eng.n_params].cpu()}
+
+
+@pytest.mark.multigpu
+def test_dp2_survives_step_counter_jumps(nat):
+    res = _run2("_dp_step_counter_jump")
+    assert res[0]["steps"] == [3, 5003, 6] and res[1]["steps"] == [3, 5003, 6]
+    assert torch.equal(res[0]["params"], res[1]["params"])
+    assert torch.isfinite(res[0]["params"]).all()
