@@ -38,9 +38,12 @@ class RunConfig:
     async_checkpoint: Optional[bool] = None   # None: on unless exploit_path == 'file' (native engines only)
     # --- data plane ---
     exploit_path: str = "file"            # file | p2p | nccl | host
-    scoreboard: bool = False              # eval scores reach the master through the device score board
+    scoreboard: Optional[bool] = None     # eval scores reach the master through the device score board
+                                          # (None: on for exploit_path == "p2p", off otherwise)
     engine: str = "auto"                  # native (sm_100a kernels) | eager (torch oracle) | auto
-    dtype: str = "bf16"                   # bf16 | fp32 | fp16 (compute dtype of the native engine)
+    dtype: str = "bf16"                   # bf16 | tf32 | fp32 | fp16 (compute dtype of the native engine; fp32 = tf32 MMA)
+    loss_scale: Optional[int] = None      # static loss scale; None = 128 for fp16, 1 otherwise (flags.get_loss_scale)
+    all_reduce_alg: Optional[str] = None  # data-parallel member: fused_p2p (default) | nccl (library baseline)
     # --- model / data ---
     resnet_size: int = 32
     resnet_version: int = 2
@@ -48,6 +51,10 @@ class RunConfig:
     data_dir: str = "./datasets"
     max_train_steps: Optional[int] = None  # cap steps per epoch (synthetic / smoke runs)
     eval_batches: Optional[int] = None
+    # --- run-loop controls of the model harness (resnet_run_loop.py:434-448,505-514) ---
+    epochs_between_evals: int = 1         # training epochs between two evaluations inside one train() call
+    stop_threshold: Optional[float] = None   # a member stops training early once its eval accuracy reaches this
+    export_dir: Optional[str] = None      # inference bundle of every member, written at the end of training
     # --- housekeeping ---
     save_root: str = "./savedata"
     results_file: str = "test_results.txt"
@@ -78,6 +85,17 @@ class RunConfig:
         if self.resnet_version == 1 and self.dtype == "fp16":
             # reference resnet_run_loop.py:542-549
             raise ValueError("ResNet v1 is not supported with fp16; use version 2")
+        if self.dtype not in ("bf16", "tf32", "fp32", "fp16"):
+            raise ValueError("dtype must be bf16 | tf32 | fp32 | fp16")
+        if self.loss_scale is not None and self.loss_scale <= 0:
+            raise ValueError("loss_scale should be a positive integer.")
+        if self.epochs_between_evals < 1:
+            raise ValueError("epochs_between_evals must be >= 1")
+        # strategy selection of the reference (distribution_utils.py:24-56): validates dp_size / all_reduce_alg
+        from .utils.misc.distribution_utils import get_distribution_strategy
+        get_distribution_strategy(self.dp_size, self.all_reduce_alg)
+        if self.scoreboard is None:
+            self.scoreboard = self.exploit_path == "p2p" and self.target_model != "toy"
         if self.resume:
             self.clean = False
         return self
@@ -86,10 +104,23 @@ class RunConfig:
         return dataclasses.replace(self, **kw)
 
 
+def harness_flags():
+    """The model-harness flag groups of the reference (``official/utils/flags``: base, performance, benchmark)
+    as one ``FlagSet``; the PBT-level arguments are added to the same parser by ``build_parser``.  Defaults
+    differ from the reference where the PBT runner differs: synthetic data and bf16 are on by default."""
+    from .utils.flags import core as flags_core
+    fs = flags_core.FlagSet("Population-based training on B200 (master/worker PBT).")
+    fs.parser.prog = "python -m distributedtf_b200"
+    flags_core.define_base(fs, model_dir=False, clean=False, train_epochs=False, batch_size=False, num_gpu=False)
+    flags_core.define_performance(fs, num_parallel_calls=False, inter_op=False, intra_op=False, synthetic_data=False)
+    flags_core.define_benchmark(fs, bigquery_uploader=False)
+    fs.set_defaults(data_dir="./datasets", dtype="bf16")
+    return fs
+
+
 def build_parser() -> argparse.ArgumentParser:
-    p = argparse.ArgumentParser(
-        prog="python -m distributedtf_b200",
-        description="Population-based training on B200 (master/worker PBT).")
+    fs = harness_flags()
+    p = fs.parser
     p.add_argument("population", nargs="?", type=int, default=None,
                    help="population size (positional, like the reference's sys.argv[1])")
     p.add_argument("--model", dest="target_model", choices=["toy", "mnist", "cifar10"], default="mnist")
@@ -102,7 +133,8 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--transport", choices=["local", "tcp", "torchrun", "gloo", "mpi"], default="local")
     p.add_argument("--master-addr", default="127.0.0.1")
     p.add_argument("--master-port", type=int, default=29611)
-    p.add_argument("--dp-size", type=int, choices=[1, 2, 4], default=1)
+    p.add_argument("--dp-size", "--num_gpus", "--num-gpus", dest="dp_size", type=int, choices=[1, 2, 4], default=1,
+                   help="GPUs per member (the reference's num_gpus, which it forces to 1)")
     p.add_argument("--members-in-flight", type=int, default=1,
                    help="members of one worker trained at once (own stream + host thread each)")
     p.add_argument("--checkpoint-every", type=int, default=1,
@@ -110,14 +142,13 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--async-checkpoint", action=argparse.BooleanOptionalAction, default=None)
     p.add_argument("--sm-limit", type=int, default=0, help="SMs a member's persistent kernels occupy (0 = all)")
     p.add_argument("--exploit-path", choices=["file", "p2p", "nccl", "host"], default="file")
-    p.add_argument("--scoreboard", action="store_true", help="rank by the device-side score board")
+    p.add_argument("--scoreboard", action=argparse.BooleanOptionalAction, default=None,
+                   help="rank by the device-side score board (default: on for the device exploit paths)")
     p.add_argument("--engine", choices=["auto", "native", "eager"], default="auto")
-    p.add_argument("--dtype", choices=["bf16", "fp32", "fp16"], default="bf16")
-    p.add_argument("--resnet-size", type=int, default=32)
-    p.add_argument("--resnet-version", type=int, choices=[1, 2], default=2)
-    p.add_argument("--synthetic", action=argparse.BooleanOptionalAction, default=True)
-    p.add_argument("--data-dir", default="./datasets")
-    p.add_argument("--max-train-steps", type=int, default=None)
+    p.add_argument("--resnet-size", "--resnet_size", dest="resnet_size", type=int, default=32)
+    p.add_argument("--resnet-version", "--resnet_version", dest="resnet_version", type=int, choices=[1, 2], default=2)
+    p.add_argument("--synthetic", "--use_synthetic_data", dest="synthetic", action=argparse.BooleanOptionalAction,
+                   default=True)
     p.add_argument("--eval-batches", type=int, default=None)
     p.add_argument("--save-root", default="./savedata")
     p.add_argument("--results-file", default="test_results.txt")
@@ -127,16 +158,16 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--initial-hp", default=None)
     p.add_argument("--inject-nan", action="append", default=[], metavar="ID@ROUND")
     p.add_argument("--quiet", dest="verbose", action="store_false")
-    p.add_argument("--hooks", nargs="*", default=["LoggingTensorHook"])
-    p.add_argument("--benchmark-logger-type", default="BaseBenchmarkLogger")
-    p.add_argument("--benchmark-log-dir", default=None)
+    p._dtf_flagset = fs
     return p
 
 
 def parse_args(argv=None) -> RunConfig:
-    ns = build_parser().parse_args(argv)
+    parser = build_parser()
+    ns = parser._dtf_flagset.validate(parser.parse_args(argv))    # group validators: loss_scale > 0, file logger dir
     kw = vars(ns)
     positional = kw.pop("population")
     if positional is not None:
         kw["population_size"] = positional
+    kw.pop("benchmark_test_id", None)
     return RunConfig(**kw).validate()

@@ -53,10 +53,16 @@ def model_kwargs(cfg: RunConfig, dp_group=None, dp_rank: int = 0) -> Dict[str, A
     kw = dict(engine=cfg.engine, dtype=cfg.dtype, synthetic=cfg.synthetic, data_dir=cfg.data_dir,
               max_train_steps=cfg.max_train_steps, eval_batches=cfg.eval_batches,
               resume=cfg.resume)
+    kw.update(epochs_between_evals=cfg.epochs_between_evals, stop_threshold=cfg.stop_threshold,
+              export_dir=cfg.export_dir)
     if cfg.target_model == "cifar10":
-        kw.update(resnet_size=cfg.resnet_size, resnet_version=cfg.resnet_version)
-    if cfg.dp_size > 1:
-        kw.update(dp_group=dp_group, dp_rank=dp_rank, dp_size=cfg.dp_size)
+        kw.update(resnet_size=cfg.resnet_size, resnet_version=cfg.resnet_version, loss_scale=cfg.loss_scale)
+    # reference distribution_utils.get_distribution_strategy: one device, or a mirrored (data-parallel) member
+    from .utils.misc.distribution_utils import get_distribution_strategy
+    strategy = get_distribution_strategy(cfg.dp_size if cfg.target_model != "toy" else 1, cfg.all_reduce_alg)
+    if strategy.kind == "data_parallel":
+        kw.update(dp_group=dp_group, dp_rank=dp_rank, dp_size=strategy.num_gpus,
+                  all_reduce_alg=strategy.all_reduce_alg)
     if getattr(cfg, "_board_info", None):
         kw["scoreboard"] = cfg._board_info
     if cfg.hooks and cfg.verbose:
@@ -82,8 +88,10 @@ def make_scoreboard(cfg: RunConfig, same_process: bool):
 
 
 def run_master(cfg: RunConfig, comm, board=None) -> Dict[str, Any]:
-    if cfg.clean:
-        shutil.rmtree(cfg.save_root, ignore_errors=True)
+    # main_manager.py:49-50 wipes savedata unconditionally; here `clean` can be switched off (resume)
+    from types import SimpleNamespace
+    from .utils.misc.model_helpers import apply_clean
+    apply_clean(SimpleNamespace(clean=cfg.clean, model_dir=cfg.save_root))
     os.makedirs(cfg.save_root, exist_ok=True)
     initial = None
     if cfg.initial_hp:

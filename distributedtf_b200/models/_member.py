@@ -40,6 +40,21 @@ def resolve_engine(engine: str, device: torch.device) -> str:
     return "eager"
 
 
+class _TrainAccuracy:
+    """Lazy ``train_accuracy`` of the last step: the head kernel counted the hits on the device
+    (``correct_cell``); nothing is read back unless a hook actually logs the value."""
+
+    def __init__(self, engine, batch: int):
+        self._engine, self._batch = engine, max(int(batch), 1)
+
+    def item(self) -> float:
+        cell = getattr(self._engine, "correct_cell", None)
+        if cell is None:
+            acc = getattr(self._engine, "last_train_accuracy", None)
+            return float(acc.item()) if acc is not None else float("nan")
+        return float(cell.item()) / self._batch
+
+
 class GpuMember(ModelBase):
     #: subclasses fill these in
     train_examples = 0
@@ -53,7 +68,8 @@ class GpuMember(ModelBase):
                  synthetic_mode: str = "random", device: Optional[torch.device] = None,
                  hooks: Optional[List[Any]] = None, dp_group=None, dp_rank: int = 0, dp_size: int = 1,
                  scoreboard: Optional[Dict[str, Any]] = None, benchmark=None, async_checkpoint: bool = False,
-                 checkpoint_every: int = 1, **_):
+                 checkpoint_every: int = 1, epochs_between_evals: int = 1, stop_threshold: Optional[float] = None,
+                 export_dir: Optional[str] = None, all_reduce_alg: Optional[str] = None, **_):
         super().__init__(cluster_id, hparams, save_base_dir)
         self.device = device or pick_device()
         self.dp_group, self.dp_rank, self.dp_size = dp_group, int(dp_rank), int(dp_size)
@@ -73,6 +89,12 @@ class GpuMember(ModelBase):
         # 1 = every round (the reference's behaviour); k > 1 = every k-th round and the last; 0 = the last only.
         # The state lives on the GPU between rounds, so with a device exploit path files are only for resume.
         self.checkpoint_every = int(checkpoint_every)
+        # run-loop controls of the reference harness (resnet_run_loop.py:434-448, 505-514)
+        self.epochs_between_evals = max(1, int(epochs_between_evals))
+        self.stop_threshold = stop_threshold
+        self.export_dir = export_dir
+        self.stopped_early = False
+        self.all_reduce_alg = all_reduce_alg    # data-parallel member: fused_p2p (default) | nccl (library baseline)
         if benchmark and benchmark[0] == "BenchmarkFileLogger" and benchmark[1]:
             from ..utils.logs import logger as _logger
             self._bench_logger = _logger.BenchmarkFileLogger(os.path.join(benchmark[1], f"model_{cluster_id}"))
@@ -169,7 +191,9 @@ class GpuMember(ModelBase):
                     loss = self.engine.train_step(x, self.train_set.labels[idx])
                 if self.hooks:                    # values stay on the device unless a hook logs them
                     self._global_step = getattr(self, "_global_step", 0) + 1
-                    vals = {"cross_entropy": loss, "learning_rate": self.hparams["opt_case"]["lr"]}
+                    # the reference's default logged tensors (hooks_helper.py:33-35)
+                    vals = {"cross_entropy": loss, "learning_rate": self.hparams["opt_case"]["lr"],
+                            "train_accuracy": _TrainAccuracy(self.engine, int(idx.numel()))}
                     for h in self.hooks:
                         h.after_step(self._global_step, vals)
         dt = max(self.device_times["train"], 1e-9)
@@ -249,14 +273,26 @@ class GpuMember(ModelBase):
         return int(cluster_id) * 8 + self.dp_rank
 
     def train(self, num_epoch: int, total_epochs: int) -> None:
+        """Train -> evaluate cycles of the reference's ``resnet_main`` (resnet_run_loop.py:446-507): every cycle
+        trains ``epochs_between_evals`` epochs, evaluates, appends a CSV row, and stops early once the accuracy
+        passes ``stop_threshold``.  Unlike the reference (``train_epochs // epochs_between_evals`` cycles, the
+        remainder silently untrained) the last cycle also trains the remainder."""
+        from ..utils.misc.model_helpers import past_stop_threshold
         self.flush_exploit()
         rows = []
-        for e in range(num_epoch):
-            self.train_one_epoch()
+        ebe = min(self.epochs_between_evals, max(num_epoch, 1))
+        done = 0
+        while done < num_epoch and not self.stopped_early:
+            n = ebe if num_epoch - done - ebe >= ebe else num_epoch - done
+            for _ in range(n):
+                self.train_one_epoch()
+            done += n
             self.accuracy = self.evaluate()
-            rows.append(self.csv_row(self.epoch_index_for_csv(e), self.accuracy))
+            rows.append(self.csv_row(self.epoch_index_for_csv(done - 1), self.accuracy))
             if self._bench_logger is not None:      # resnet_run_loop.py:466 log_evaluation_result
                 self._bench_logger.log_evaluation_result({"accuracy": self.accuracy, "global_step": self.engine.step})
+            if not math.isnan(self.accuracy) and past_stop_threshold(self.stop_threshold, float(self.accuracy)):
+                self.stopped_early = True           # resnet_run_loop.py:505-507; later train() calls are no-ops
         self.bump_epochs(num_epoch)
         if math.isnan(self.accuracy):
             return                      # the worker drops the member; nothing to persist
@@ -264,11 +300,29 @@ class GpuMember(ModelBase):
             from ..parallel import exploit
             exploit.publish(self, self.rounds_trained)
         self.rounds_trained += 1
-        last = self.epoches_trained >= total_epochs
+        last = self.epoches_trained >= total_epochs or self.stopped_early
         k = self.checkpoint_every
         if last or k == 1 or (k > 1 and self.rounds_trained % k == 0):
             self.save()
         report.append_csv(os.path.join(self.ensure_dir(), "learning_curve.csv"), self.csv_fields_now(), rows)
+        if last and self.export_dir and self.dp_rank == 0:      # resnet_run_loop.py:510-514
+            self.export(os.path.join(self.export_dir, "model_" + str(self.cluster_id)))
+
+    export_model_name = "model"
+    export_input_shape: List[int] = []
+
+    def export_config(self) -> Dict[str, Any]:
+        return {}
+
+    def export(self, export_dir: str) -> str:
+        """Inference bundle of this member (reference: ``classifier.export_savedmodel``,
+        resnet_run_loop.py:510-514): parameters in the oracle's naming + ``signature.json``."""
+        from ..utils.export import export as _export
+        self.flush_exploit()
+        eng = self.engine
+        named = eng.export_named() if hasattr(eng, "export_named") else {k: v.detach() for k, v in eng.params.items()}
+        return _export.export_inference_bundle(export_dir, named, self.export_model_name, self.export_config(),
+                                               list(self.export_input_shape))
 
     def epoch_index_for_csv(self, e: int) -> int:
         return self.epoches_trained + e

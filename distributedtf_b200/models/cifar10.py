@@ -49,7 +49,8 @@ class Cifar10Model(GpuMember):
             try:
                 return NativeResNetEngine(self.net_cfg, self.hparams, self.device, seed=seed, dtype=self.dtype,
                                           arena_alloc=self.make_symmetric_alloc,
-                                          dp_group=self.dp_group if self.dp_size > 1 else None)
+                                          dp_group=self.dp_group if self.dp_size > 1 else None,
+                                          all_reduce_alg=self.all_reduce_alg if self.dp_size > 1 else None)
             except NotImplementedError:
                 # ResNet v1 / bottleneck / fp16 are served by the eager engine; an explicit request for
                 # the native engine is an error, `auto` degrades.
@@ -64,13 +65,12 @@ class Cifar10Model(GpuMember):
                            if self.device.type == "cuda" else torch.float32, lr_schedule=True,
                            loss_scale=self.loss_scale)
 
-    def export(self, export_dir: str) -> str:
-        """Inference bundle (reference: ``classifier.export_savedmodel``, resnet_run_loop.py:510-514)."""
+    export_model_name = "resnet"
+    export_input_shape = [32, 32, 3]
+
+    def export_config(self) -> Dict[str, Any]:
         import dataclasses
-        from ..utils.export import export as _export
-        named = self.engine.export_named() if hasattr(self.engine, "export_named") else \
-            {k: v.detach() for k, v in self.engine.params.items()}
-        return _export.export_inference_bundle(export_dir, named, "resnet", dataclasses.asdict(self.net_cfg), [32, 32, 3])
+        return dataclasses.asdict(self.net_cfg)
 
     def preprocess(self, images_u8: torch.Tensor, training: bool) -> torch.Tensor:
         pre = getattr(self.engine, "preprocess", None)

@@ -104,6 +104,7 @@ class EagerEngine:
                                    step=self.step, momentum=float(oc.get("momentum", 0.0)),
                                    grad_decay=float(oc.get("grad_decay", 0.9)))
         self.last_loss = ce.detach()
+        self.last_train_accuracy = (logits.detach().argmax(dim=1) == labels.long()).float().mean()
         return self.last_loss
 
     @torch.no_grad()

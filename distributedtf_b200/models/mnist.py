@@ -25,6 +25,8 @@ class MNISTModel(GpuMember):
     train_examples = MNIST_TRAIN
     eval_examples = MNIST_EVAL
     csv_fields = ["global_step", "eval_accuracy", "optimizer", "lr"]
+    export_model_name = "mnist"
+    export_input_shape = [28, 28, 1]
 
     def build_datasets(self):
         if self.synthetic:
@@ -46,7 +48,8 @@ class MNISTModel(GpuMember):
             else:
                 return NativeMnistEngine(self.hparams, self.device, seed=seed, dtype=self.dtype,
                                          arena_alloc=self.make_symmetric_alloc,
-                                         dp_group=self.dp_group if self.dp_size > 1 else None)
+                                         dp_group=self.dp_group if self.dp_size > 1 else None,
+                                          all_reduce_alg=self.all_reduce_alg if self.dp_size > 1 else None)
         from .engine_eager import EagerEngine
         init = mnist_net.init_params(self.hparams.get("initializer", "None"), seed)
         return EagerEngine(mnist_net.param_specs(), mnist_net.forward, init, self.hparams, self.device,

@@ -30,11 +30,12 @@ class NativeMnistEngine(NativeEngineBase):
     train_pp_mode, eval_pp_mode = 0, 0        # pixels stay 0..255 floats, as in the reference
 
     def __init__(self, hparams: Dict[str, Any], device, *, seed: int = 0, dtype: str = "bf16",
-                 max_batch: int = 256, use_graphs: bool = True, arena_alloc=None, dp_group=None):
+                 max_batch: int = 256, use_graphs: bool = True, arena_alloc=None, dp_group=None,
+                 all_reduce_alg=None):
         if dtype != "bf16":
             raise NotImplementedError("native engine computes in bf16 with fp32 master weights / accumulation")
         super().__init__(device, max_batch=max_batch, use_graphs=use_graphs, arena_alloc=arena_alloc,
-                         dp_group=dp_group, seed=seed)
+                         dp_group=dp_group, seed=seed, all_reduce_alg=all_reduce_alg)
         self.image_size, self.image_channels = 28, 1
         self.dropout_keep = DROPOUT_KEEP
         self._build_plan()

@@ -67,7 +67,8 @@ class NativeEngineBase:
     image_channels = 3
     image_size = 32
 
-    def __init__(self, device, *, max_batch: int, use_graphs: bool, arena_alloc=None, dp_group=None, seed: int = 0):
+    def __init__(self, device, *, max_batch: int, use_graphs: bool, arena_alloc=None, dp_group=None, seed: int = 0,
+                 all_reduce_alg: Optional[str] = None):
         native.require()
         self.device = torch.device(device)
         self.max_batch = max_batch
@@ -76,6 +77,12 @@ class NativeEngineBase:
         self._graphs: Dict[Tuple[str, int], torch.cuda.CUDAGraph] = {}
         self.dp_group = dp_group          # torch.distributed group of this member's replicas (None = 1 GPU)
         self.dp = None
+        # gradient exchange of a data-parallel member: "fused_p2p" = the one-shot all-reduce + update kernel over
+        # peer memory (the product); "nccl" = library all-reduce followed by the plain optimizer kernel (the
+        # baseline the reference's dormant MirroredStrategy path amounts to, distribution_utils.py:41-47)
+        self.all_reduce_alg = (all_reduce_alg or "fused_p2p") if dp_group is not None else None
+        if self.all_reduce_alg not in (None, "fused_p2p", "nccl"):
+            raise ValueError("all_reduce_alg of the native engine must be fused_p2p or nccl")
         self._arena_alloc = arena_alloc
         self.last_loss: Optional[torch.Tensor] = None
         self.launches_per_step = 0
@@ -126,7 +133,7 @@ class NativeEngineBase:
         self.pack = torch.zeros(max(self.n_pack, 8), dtype=torch.bfloat16, device=dev)
         # per-step zeroed region: grads | batch statistics | loss, correct
         zfloats = P + _align(max(self.n_stats, 1) * 4) // 4 + 64
-        if self.dp_group is not None:
+        if self.dp_group is not None and self.all_reduce_alg == "fused_p2p":
             # data-parallel member: the gradient arena must be addressable by the peer replicas
             from ..parallel.dp import DataParallelGroup
             self.dp = DataParallelGroup(zfloats * 4, dev, group=self.dp_group)
@@ -208,7 +215,24 @@ class NativeEngineBase:
             native.step_begin(self.zero_region, self.step_dev, bump=True)
         self._count += 1
 
+    def _nccl_world(self) -> int:
+        import torch.distributed as dist
+        return dist.get_world_size(self.dp_group)
+
     def _apply_update(self) -> None:
+        if self.all_reduce_alg == "nccl":
+            # library baseline: NCCL all-reduce of the gradient arena, then the single-GPU optimizer kernel with
+            # a 1/W scale.  Issued outside the step's CUDA graph (see _run).
+            if torch.cuda.is_current_stream_capturing():
+                self.launches_per_step = self._count + 1
+                return
+            import torch.distributed as dist
+            dist.all_reduce(self.grads, group=self.dp_group)
+            native.optimizer_step(self.params, self.grads, self.slot0, self.slot1, self.pack, self.segs_dev,
+                                  self.chunks_dev, self.n_chunks, self.hp_dev, self.step_dev, 1.0 / self._nccl_world())
+            self._count += 1
+            self.launches_per_step = self._count
+            return
         if self.dp is not None:
             self.dp.allreduce_update(self.params, self.slot0, self.slot1, self.pack, self.segs_dev,
                                      self.chunks_dev, self.n_chunks, self.hp_dev, self.step_dev)
@@ -251,6 +275,9 @@ class NativeEngineBase:
             g.replay()
         finally:
             _GATE.exit_step()
+        name = kind[0] if isinstance(kind, tuple) else kind
+        if self.all_reduce_alg == "nccl" and str(name).startswith("train"):
+            self._apply_update()                   # the captured graph stops before the library all-reduce
 
     def load_batch(self, images_u8: torch.Tensor, labels: torch.Tensor) -> int:
         nb = int(images_u8.shape[0])

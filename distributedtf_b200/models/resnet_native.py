@@ -80,13 +80,13 @@ class NativeResNetEngine(NativeEngineBase):
 
     def __init__(self, cfg: resnet.ResNetConfig, hparams: Dict[str, Any], device, *, seed: int = 0,
                  dtype: str = "bf16", max_batch: int = MAX_BATCH, use_graphs: bool = True,
-                 arena_alloc=None, dp_group=None):
+                 arena_alloc=None, dp_group=None, all_reduce_alg=None):
         if cfg.resnet_version != 2 or cfg.bottleneck or cfg.first_pool_size:
             raise NotImplementedError("native engine covers the CIFAR configuration: ResNet v2, building blocks")
         if dtype != "bf16":
             raise NotImplementedError("native engine computes in bf16 with fp32 master weights / accumulation")
         super().__init__(device, max_batch=max_batch, use_graphs=use_graphs, arena_alloc=arena_alloc,
-                         dp_group=dp_group, seed=seed)
+                         dp_group=dp_group, seed=seed, all_reduce_alg=all_reduce_alg)
         self.cfg = cfg
         self.image_size, self.image_channels = cfg.image_size, cfg.in_channels
         self._build_plan()

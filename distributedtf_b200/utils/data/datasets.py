@@ -46,9 +46,11 @@ class Dataset:
 
 def synthetic_dataset(n: int, h: int, w: int, c: int, num_classes: int, mode: str = "random",
                       seed: int = 0, device="cpu") -> Dataset:
-    if mode == "zeros":   # reference generate_synthetic_data semantics
-        return Dataset(torch.zeros(n, h, w, c, dtype=torch.uint8, device=device),
-                       torch.zeros(n, dtype=torch.int32, device=device), "synthetic-zeros")
+    if mode == "zeros":   # the reference's synthetic data: one constant element repeated (model_helpers.py:59-86)
+        from ..misc.model_helpers import generate_synthetic_data
+        images, labels = next(generate_synthetic_data([h, w, c], 0, torch.uint8, [], 0, torch.int32,
+                                                      batch_size=n, device=device))
+        return Dataset(images, labels, "synthetic-zeros")
     g = torch.Generator().manual_seed(seed)
     images = torch.randint(0, 256, (n, h, w, c), dtype=torch.uint8, generator=g)
     labels = torch.randint(0, num_classes, (n,), dtype=torch.int32, generator=g)

@@ -21,7 +21,8 @@ import torch
 help_wrap = functools.partial(textwrap.fill, width=80)
 
 # dtype name -> (torch dtype, default loss scale)   (reference _performance.py:30-33)
-DTYPE_MAP = {"fp16": (torch.float16, 128), "bf16": (torch.bfloat16, 1), "fp32": (torch.float32, 1)}
+DTYPE_MAP = {"fp16": (torch.float16, 128), "bf16": (torch.bfloat16, 1), "fp32": (torch.float32, 1),
+             "tf32": (torch.float32, 1)}      # tf32: fp32 storage, tf32 tensor-core math (native engine)
 
 
 class FlagSet:
@@ -35,7 +36,8 @@ class FlagSet:
                type: Any = str, choices: Optional[Sequence[Any]] = None, nargs: Optional[str] = None) -> None:
         if name in self._defined:
             return
-        names = ["--" + name] + (["-" + short] if short else [])
+        # both spellings are accepted: --data_dir (the reference's absl names) and --data-dir (the PBT CLI)
+        names = ["--" + name] + (["--" + name.replace("_", "-")] if "_" in name else []) + (["-" + short] if short else [])
         kw: Dict[str, Any] = dict(default=default, help=help_wrap(help))
         if type is bool:
             kw["action"] = argparse.BooleanOptionalAction
@@ -59,13 +61,20 @@ class FlagSet:
         self._parser.set_defaults(**kw)
         self._defined.update(kw)
 
-    def parse(self, argv: Optional[Sequence[str]] = None) -> argparse.Namespace:
-        ns = self._parser.parse_args(list(argv) if argv is not None else [])
+    @property
+    def parser(self) -> argparse.ArgumentParser:
+        """The underlying parser, for callers that add their own (non-harness) arguments next to the groups."""
+        return self._parser
+
+    def validate(self, ns: argparse.Namespace) -> argparse.Namespace:
         for v in self._validators:
             msg = v(ns)
             if msg:
                 raise ValueError(msg)
         return ns
+
+    def parse(self, argv: Optional[Sequence[str]] = None) -> argparse.Namespace:
+        return self.validate(self._parser.parse_args(list(argv) if argv is not None else []))
 
 
 def define_base(fs: FlagSet, data_dir=True, model_dir=True, clean=True, train_epochs=True,
@@ -182,5 +191,5 @@ def define_resnet_flags(fs: Optional[FlagSet] = None, resnet_size_choices: Optio
     fs.define("resnet_size", "rs", "50", "The size of the ResNet model to use.",
               choices=list(resnet_size_choices) if resnet_size_choices else None)
     fs.validator(lambda ns: "ResNet version 1 is not currently supported with fp16. Please use version 2 instead."
-                 if ns.dtype == "fp16" and ns.resnet_version == "1" else None)
+                 if ns.dtype == "fp16" and str(ns.resnet_version) == "1" else None)
     return fs

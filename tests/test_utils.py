@@ -293,3 +293,80 @@ def test_bigquery_logger_uploads_from_threads(tmp_path):
     assert len({r["run_id"] for r in rows["ds.metric.jsonl"]}) == 1
     assert rows["ds.run.jsonl"][0]["model_name"] == "resnet" and rows["ds.run.jsonl"][0]["test_id"] == "t1"
     logger.config_benchmark_logger()                          # back to the default for later tests
+
+
+# --------------------------------------------------------------------------- harness wiring
+def test_cli_is_built_from_the_flag_groups():
+    """The PBT command line takes the harness flags of the reference's groups (either spelling) and runs their
+    validators; PBT-level arguments sit next to them."""
+    from distributedtf_b200.config import build_parser, parse_args
+    cfg = parse_args(["6", "--model", "cifar10", "--stop_threshold", "0.5", "--export-dir", "/tmp/e",
+                      "--epochs_between_evals", "2", "--dtype", "fp16", "--loss_scale", "64",
+                      "--benchmark_logger_type", "BenchmarkFileLogger", "--benchmark_log_dir", "/tmp/b"])
+    assert (cfg.population_size, cfg.stop_threshold, cfg.export_dir, cfg.epochs_between_evals) == (6, 0.5, "/tmp/e", 2)
+    assert cfg.dtype == "fp16" and cfg.loss_scale == 64 and cfg.benchmark_log_dir == "/tmp/b"
+    assert "stop_threshold" in build_parser()._dtf_flagset.key_flags
+    with pytest.raises(ValueError, match="loss_scale"):
+        parse_args(["--loss_scale", "-3"])
+    with pytest.raises(ValueError, match="benchmark_log_dir"):
+        parse_args(["--benchmark_logger_type", "BenchmarkFileLogger"])
+    assert parse_args(["--exploit-path", "p2p", "--model", "cifar10"]).scoreboard is True
+    assert parse_args(["--exploit-path", "p2p", "--model", "cifar10", "--no-scoreboard"]).scoreboard is False
+    assert parse_args([]).scoreboard is False
+
+
+def test_run_synthetic_drives_the_cifar_harness(tmp_path):
+    """integration.run_synthetic -> resnet_run.main(argv): one tiny member through the stand-alone run loop
+    (flag groups, apply_clean, strategy selection, train -> eval cycle, CSV row, export)."""
+    from distributedtf_b200.models import resnet_run
+    from distributedtf_b200.utils.testing import integration
+    export = tmp_path / "export"
+    seen = {}
+
+    def main(argv):
+        seen["argv"] = list(argv)
+        model_dir = argv[argv.index("--model_dir") + 1]
+        out = resnet_run.main(argv)
+        seen["csv"] = open(os.path.join(model_dir, "model_0", "learning_curve.csv")).read()
+        return out
+
+    acc, mid = integration.run_synthetic(main, tmp_root=str(tmp_path), max_train=2, extra_flags=[
+        "--resnet_size", "8", "--batch_size", "16", "--train_epochs", "2", "--epochs_between_evals", "1",
+        "--engine", "eager", "--dtype", "fp32", "--export_dir", str(export), "--stop_threshold", "0.0"])
+    assert mid == 0 and 0.0 <= acc <= 1.0
+    assert "--use_synthetic_data" in seen["argv"] and "--max_train_steps" in seen["argv"]
+    # stop_threshold 0.0 is passed by the first evaluation: one cycle, one CSV row (plus the header)
+    assert len(seen["csv"].strip().splitlines()) == 2
+    assert (export / "model_0" / "signature.json").exists()
+    assert not any(p.name.startswith("tmp") and p.is_dir() for p in tmp_path.iterdir() if p.name != "export")
+
+
+def test_member_train_cycles_follow_epochs_between_evals(tmp_path):
+    from distributedtf_b200.hpspace import default_cifar_hparam
+    from distributedtf_b200.models.cifar10 import Cifar10Model
+    hp = default_cifar_hparam()
+    hp["batch_size"] = 16
+    m = Cifar10Model(3, hp, str(tmp_path / "model_"), engine="eager", dtype="fp32", max_train_steps=1, eval_batches=1,
+                     resnet_size=8, epochs_between_evals=2, device=torch.device("cpu"))
+    evals = []
+    real = m.evaluate
+    m.evaluate = lambda: (evals.append(1), real())[1]
+    m.train(5, 5)
+    assert len(evals) == 2 and m.epoches_trained == 5          # cycles of 2 and 3 epochs
+    rows = open(tmp_path / "model_3" / "learning_curve.csv").read().strip().splitlines()
+    assert [r.split(",")[0] for r in rows[1:]] == ["1", "4"]
+
+
+def test_train_accuracy_reaches_the_logging_hook(tmp_path):
+    from distributedtf_b200.hpspace import default_cifar_hparam
+    from distributedtf_b200.models.cifar10 import Cifar10Model
+    from distributedtf_b200.utils.logs import hooks as hooks_lib
+    lines = []
+    hook = hooks_lib.LoggingTensorHook(["learning_rate", "cross_entropy", "train_accuracy"], every_n_iter=1,
+                                       sink=lines.append)
+    hp = default_cifar_hparam()
+    hp["batch_size"] = 16
+    m = Cifar10Model(0, hp, str(tmp_path / "model_"), engine="eager", dtype="fp32", max_train_steps=2, eval_batches=1,
+                     resnet_size=8, device=torch.device("cpu"), hooks=[hook])
+    m.train(1, 1)
+    assert len(lines) == 2 and all("train_accuracy = " in ln and "cross_entropy = " in ln for ln in lines)
