@@ -55,7 +55,14 @@ __global__ void __launch_bounds__(512)
 exploit_copy_kernel(uint4* __restrict__ dst, const uint4* __restrict__ src, long long n_vec,
                     long long hp_vec_off, int hp_vecs, const __grid_constant__ DtfHparams hp,
                     uint4* __restrict__ zero, long long zero_vecs,
-                    unsigned long long* done_flag, unsigned long long epoch, unsigned int* arrive_counter) {
+                    unsigned long long* done_flag, unsigned long long epoch, unsigned int* arrive_counter,
+                    const unsigned long long* wait_flag, unsigned long long wait_value) {
+    // device-side ordering against the producer of `src` (the winner's snapshot publish): acquire its epoch flag
+    // before the first load.  Every CTA waits for itself, so no CTA depends on another one being resident.
+    if (wait_flag != nullptr) {
+        if (threadIdx.x == 0) wait_flag_ge(wait_flag, wait_value, 3);
+        __syncthreads();
+    }
     const long long tid = blockIdx.x * (long long)blockDim.x + threadIdx.x;
     const long long nthreads = (long long)gridDim.x * blockDim.x;
     long long i = tid;
@@ -101,11 +108,36 @@ __global__ void score_publish_kernel(DtfScoreSlot* __restrict__ board_slot, cons
                                      int total, unsigned long long epoch, int reset_counter, int* correct_rw) {
     if (threadIdx.x == 0 && blockIdx.x == 0) {
         const int c = *correct;
-        board_slot->score = total > 0 ? static_cast<float>(c) / static_cast<float>(total) : 0.f;
-        board_slot->count = static_cast<unsigned int>(total);
+        board_slot->hits = static_cast<unsigned int>(c);
+        board_slot->seen = static_cast<unsigned int>(total);
         __threadfence_system();
         st_release_sys(&board_slot->epoch, epoch);
         if (reset_counter) *correct_rw = 0;
+    }
+}
+
+// start of a member's evaluation: the slot's counters restart at zero (the epoch keeps its last value)
+__global__ void score_reset_kernel(DtfScoreSlot* __restrict__ board_slot) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) {
+        board_slot->hits = 0u;
+        board_slot->seen = 0u;
+    }
+}
+
+// end of a member's evaluation: every evaluation kernel of the round has completed (stream order), their
+// system-scope reductions into the slot are performed; publish the epoch.  A non-finite loss turns the entry
+// into the "dropped" marker so that the master does not wait for a member its worker is about to remove.
+__global__ void score_release_kernel(DtfScoreSlot* __restrict__ board_slot, unsigned long long epoch,
+                                     const float* __restrict__ loss, int dropped) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) {
+        bool bad = dropped != 0;
+        if (loss != nullptr) {
+            const float l = *loss;
+            bad = bad || !(l == l) || fabsf(l) > 3.0e38f;
+        }
+        if (bad) board_slot->hits = DTF_SCORE_DROPPED;
+        __threadfence_system();
+        st_release_sys(&board_slot->epoch, epoch);
     }
 }
 
@@ -249,10 +281,11 @@ dp_step_begin_kernel(float4* __restrict__ zero, long long n_vec, long long* __re
 
 #define DTF_CHECK_LAUNCH() (cudaGetLastError() == cudaSuccess ? DTF_OK : DTF_ERR_CUDA)
 
-extern "C" int dtf_exploit_copy(void* dst, const void* src, long long bytes, long long hp_offset,
-                                const DtfHparams* new_hp, void* zero_region, long long zero_bytes,
-                                unsigned long long* done_flag, unsigned long long epoch,
-                                unsigned int* arrive_counter, int max_ctas, cudaStream_t stream) {
+extern "C" int dtf_exploit_copy_ordered(void* dst, const void* src, long long bytes, long long hp_offset,
+                                        const DtfHparams* new_hp, void* zero_region, long long zero_bytes,
+                                        unsigned long long* done_flag, unsigned long long epoch,
+                                        unsigned int* arrive_counter, const unsigned long long* wait_flag,
+                                        unsigned long long wait_value, int max_ctas, cudaStream_t stream) {
     if ((bytes & 15) || (zero_bytes & 15) || (hp_offset & 15)) return DTF_ERR_ARG;
     if (bytes < 0 || zero_bytes < 0) return DTF_ERR_ARG;
     if (((uintptr_t)dst & 15) || ((uintptr_t)src & 15)) return DTF_ERR_ARG;
@@ -271,7 +304,28 @@ extern "C" int dtf_exploit_copy(void* dst, const void* src, long long bytes, lon
     dtf::exploit_copy_kernel<<<grid, 512, 0, stream>>>(
         reinterpret_cast<uint4*>(dst), reinterpret_cast<const uint4*>(src), n_vec,
         new_hp ? hp_offset / 16 : -1, hp_vecs, hp_val, reinterpret_cast<uint4*>(zero_region), zero_bytes / 16,
-        done_flag, epoch, arrive_counter);
+        done_flag, epoch, arrive_counter, wait_flag, wait_value);
+    return DTF_CHECK_LAUNCH();
+}
+
+extern "C" int dtf_exploit_copy(void* dst, const void* src, long long bytes, long long hp_offset,
+                                const DtfHparams* new_hp, void* zero_region, long long zero_bytes,
+                                unsigned long long* done_flag, unsigned long long epoch,
+                                unsigned int* arrive_counter, int max_ctas, cudaStream_t stream) {
+    return dtf_exploit_copy_ordered(dst, src, bytes, hp_offset, new_hp, zero_region, zero_bytes, done_flag, epoch,
+                                    arrive_counter, nullptr, 0ull, max_ctas, stream);
+}
+
+extern "C" int dtf_score_reset(DtfScoreSlot* board_slot, cudaStream_t stream) {
+    if (board_slot == nullptr) return DTF_ERR_ARG;
+    dtf::score_reset_kernel<<<1, 32, 0, stream>>>(board_slot);
+    return DTF_CHECK_LAUNCH();
+}
+
+extern "C" int dtf_score_release(DtfScoreSlot* board_slot, unsigned long long epoch, const float* loss, int dropped,
+                                 cudaStream_t stream) {
+    if (board_slot == nullptr) return DTF_ERR_ARG;
+    dtf::score_release_kernel<<<1, 32, 0, stream>>>(board_slot, epoch, loss, dropped);
     return DTF_CHECK_LAUNCH();
 }
 
@@ -446,7 +500,7 @@ extern "C" int dtf_exploit_copy_noalloc(void* dst, const void* src, long long by
     dtf::exploit_copy_kernel<<<grid, 512, 0, stream>>>(
         reinterpret_cast<uint4*>(dst), reinterpret_cast<const uint4*>(src), n_vec,
         new_hp ? hp_offset / 16 : -1, hp_vecs, hp_val, reinterpret_cast<uint4*>(zero_region), zero_bytes / 16,
-        done_flag, epoch, static_cast<unsigned int*>(scratch));
+        done_flag, epoch, static_cast<unsigned int*>(scratch), nullptr, 0ull);
     if (cudaGetLastError() != cudaSuccess) {
         snprintf(g_noalloc_error, sizeof(g_noalloc_error), "dtf_exploit_copy_noalloc: kernel launch failed");
         return DTF_ERR_CUDA;

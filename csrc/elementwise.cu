@@ -142,6 +142,12 @@ head_kernel(const __grid_constant__ DtfHead P) {
             dlog[k] = (__expf(logits[k] - lse) - (k == label ? 1.f : 0.f)) * inv_n * P.loss_scale;
         atomicAdd(P.loss_out, (lse - logits[label]) * inv_n);
         if (arg == label) atomicAdd(P.correct_out, 1);
+        // eval-score reduction: the hit also goes straight into this member's slot of the master's score board
+        // (a peer pointer when the master's GPU is another one) -- fire-and-forget system-scope reductions
+        if (P.board_hits != nullptr) {
+            if (arg == label) asm volatile("red.relaxed.sys.global.add.u32 [%0], 1;" ::"l"(P.board_hits) : "memory");
+            if (n == 0) asm volatile("red.relaxed.sys.global.add.u32 [%0], %1;" ::"l"(P.board_hits + 1), "r"(P.batch) : "memory");
+        }
     }
     if (P.logits_out != nullptr && tid < K) P.logits_out[n * K + tid] = logits[tid];
     if (!P.training) return;

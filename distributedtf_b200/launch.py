@@ -83,8 +83,9 @@ def make_scoreboard(cfg: RunConfig, same_process: bool):
     if not torch.cuda.is_available():
         return None, None
     from .parallel.scoreboard import ScoreBoard
-    board = ScoreBoard(max(cfg.population_size, 1), torch.device("cuda", 0))
-    return board, ({"ptr": board.ptr} if same_process else {"handle": board.handle()})
+    board = ScoreBoard(max(cfg.population_size, 1), torch.device("cuda", torch.cuda.current_device()))
+    # members in the owner's process use the raw pointer, everyone else maps the CUDA IPC handle
+    return board, {"ptr": board.ptr, "owner_pid": os.getpid(), "handle": board.handle()}
 
 
 def run_master(cfg: RunConfig, comm, board=None) -> Dict[str, Any]:
@@ -292,10 +293,12 @@ def run_torchrun(cfg: RunConfig) -> Optional[Dict[str, Any]]:
     cfg = cfg.replace(workers=world, master_addr=addr, master_port=port)
     result: Dict[str, Any] = {}
     master_thread = None
+    board, info = (make_scoreboard(cfg, same_process=False) if rank == 0 else (None, None))
+    box = [info]
+    dist.broadcast_object_list(box, src=0)          # every rank's members need the board's handle
+    object.__setattr__(cfg, "_board_info", box[0])
     if rank == 0:
         master = TcpMasterComm(addr, port, world + 1)
-        board, info = make_scoreboard(cfg, same_process=False)
-        object.__setattr__(cfg, "_board_info", info)
 
         def _m():
             master.wait_for_workers()

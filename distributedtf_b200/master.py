@@ -20,8 +20,12 @@ What is different, on purpose:
   (``pbt_cluster.py:154-162``).
 * ``recv`` carries an optional timeout so a dead worker aborts the run instead of
   hanging it.
-* An optional device score board (``parallel/scoreboard.py``) supplies the eval
-  scores the ranking uses; the GET replies remain the source of hparams.
+* With a device score board (``parallel/scoreboard.py``) the board IS the round barrier and
+  the source of the scores: after TRAIN the master polls it until every live member's evaluation
+  kernels have released the round's epoch, ranks, and sends SET — without a GET round trip on
+  that path (the reference's GET is both gather and barrier, ``pbt_cluster.py:114-128,191-193``).
+  The hyper-parameter dicts still travel by GET, but off the critical path: EXPLORE, GET and the
+  next round's TRAIN are sent back to back, so a worker answers and starts training at once.
 """
 from __future__ import annotations
 
@@ -92,6 +96,9 @@ class PBTCluster:
         self.rounds_done = 0
         self.history: List[Dict[str, Any]] = []   # per-round pairs, for tests / reports
         self.cluster_id_to_worker_rank: Dict[int, int] = {}
+        self._known: Optional[Dict[int, List[Any]]] = None   # last GET view: id -> [id, acc, hparams]
+        self.board_timeout = 120.0
+        self.board_fallbacks = 0                  # rounds ranked from a GET gather because the board timed out
 
         self.dispatch_hparams_to_workers(initial_hparams)
 
@@ -140,16 +147,35 @@ class PBTCluster:
         self._broadcast(protocol.exit_())
 
     # ------------------------------------------------------------------ rounds
+    @property
+    def board_mode(self) -> bool:
+        # the file path needs the GET barrier: its checkpoints must be on disk before the master copies them
+        return self.scoreboard is not None and self.do_exploit and self.exploit_path != "file"
+
     def train(self, round_num: int) -> float:
         start = time.time()
+        train_sent_ahead = False
+        if self.board_mode and self._known is None:
+            self.get_all_values()
         for rnd in range(round_num):
             t0 = time.time()
             self._say("\nRound {}".format(rnd))
-            self._broadcast(protocol.train(self.epochs_per_round, self.epochs_per_round * round_num))
+            if not train_sent_ahead:
+                self._broadcast(protocol.train(self.epochs_per_round, self.epochs_per_round * round_num))
+            train_sent_ahead = False
             if self.do_exploit:
                 self.exploit()
             if self.do_explore:
                 self.explore()
+            if self.board_mode:
+                # Refresh the master's view of hyper-parameters and membership.  EXPLORE, GET and the next TRAIN
+                # go out back to back: the workers answer the GET right after exploring and start the next round
+                # without waiting for the master to have read the replies.
+                self._broadcast(protocol.get())
+                if rnd + 1 < round_num:
+                    self._broadcast(protocol.train(self.epochs_per_round, self.epochs_per_round * round_num))
+                    train_sent_ahead = True
+                self._remember(self._gather())
             self.rounds_done += 1
             self._say("Round elapsed time: {}\n".format(datetime.timedelta(seconds=time.time() - t0)))
         self.flush_all_instructions()
@@ -157,28 +183,54 @@ class PBTCluster:
         self._say("Total elapsed time: {}".format(datetime.timedelta(seconds=elapsed)))
         return elapsed
 
-    def exploit(self) -> None:
-        t_gather = time.time()
-        self._broadcast(protocol.get())
-        replies = self._gather()
-        all_values: List[List[Any]] = []
+    def _remember(self, replies: Dict[int, Any]) -> List[List[Any]]:
+        """Digest GET replies: who is alive, who owns whom, current hparams."""
+        out: List[List[Any]] = []
         owner: Dict[int, int] = {}
         for rank in self.worker_ranks:
             for rec in replies[rank]:
-                all_values.append(list(rec))
+                out.append(list(rec))
                 owner[rec[0]] = rank
         self.cluster_id_to_worker_rank = owner
+        self._known = {rec[0]: rec for rec in out}
+        return out
+
+    def _gather_values(self) -> List[List[Any]]:
+        """The reference's gather: GET to everyone, replies in rank order; doubles as the round barrier."""
+        self._broadcast(protocol.get())
+        return self._remember(self._gather())
+
+    def _values_from_board(self) -> Optional[List[List[Any]]]:
+        """Board path of the ranking input: wait on the device board (the round barrier), take scores from it
+        and hyper-parameters from the last GET view.  Returns None when the board timed out."""
+        ids = sorted(self._known)
+        try:
+            scores = self.scoreboard.read(self.rounds_done + 1, members=ids, timeout=self.board_timeout)
+        except TimeoutError as e:
+            self._say("score board timed out ({}); falling back to the GET gather".format(e))
+            self.board_fallbacks += 1
+            return None
+        self.board_scores = dict(scores)
+        out = []
+        for cid in ids:
+            sc = scores[cid]
+            if isinstance(sc, float) and math.isnan(sc):
+                continue                          # dropped marker: the worker removes this member
+            rec = self._known[cid]
+            out.append([cid, sc, copy.deepcopy(rec[2])])
+        return out
+
+    def exploit(self) -> None:
+        t_gather = time.time()
+        all_values: Optional[List[List[Any]]] = None
+        if self.board_mode and self._known is not None:
+            all_values = self._values_from_board()
+        if all_values is None:
+            all_values = self._gather_values()
+        owner = self.cluster_id_to_worker_rank
         self.gather_time += time.time() - t_gather
 
         t0 = time.time()
-        if self.scoreboard is not None:
-            # Device-side scores win over the host copies when the board is live.
-            # every live member published (hits / seen, epoch = rounds trained) from its eval kernel stream
-            scores = self.scoreboard.read(self.rounds_done + 1, members=[rec[0] for rec in all_values])
-            self.board_scores = dict(scores)
-            for rec in all_values:
-                if rec[0] in scores:
-                    rec[1] = scores[rec[0]]
         all_values.sort(key=lambda v: v[1])
         self.pop_size = len(all_values)       # dropped members shrink the population
         pairs = exploit_pairs(all_values)
@@ -226,12 +278,7 @@ class PBTCluster:
         self.get_all_values()
 
     def get_all_values(self) -> List[List[Any]]:
-        self._broadcast(protocol.get())
-        replies = self._gather()
-        out: List[List[Any]] = []
-        for rank in self.worker_ranks:
-            out += [list(r) for r in replies[rank]]
-        return out
+        return self._gather_values()
 
     # ------------------------------------------------------------------ reports
     def profiling_info(self) -> Dict[str, float]:

@@ -109,6 +109,7 @@ class GpuMember(ModelBase):
         self._pending_exploit: Optional[Dict[str, Any]] = None
         self.rounds_trained = 0
         self.engine = self.build_engine()
+        self._attach_board()
         self._train_iter = BatchIterator(len(self.train_set), int(self.hparams["batch_size"]), True,
                                          seed=1000 + cluster_id, device=self.device)
         self.last_images_per_sec = 0.0
@@ -205,17 +206,51 @@ class GpuMember(ModelBase):
         return (hasattr(self.engine, "train_step_indexed") and self.train_set.images.is_cuda
                 and self.train_set.images.dtype == torch.uint8 and self.train_set.labels.dtype == torch.int32)
 
-    def evaluate(self) -> float:
-        """Accuracy over the eval set.  A data-parallel member shards the eval batches over its replicas
+    def _board_pointer(self) -> Optional[int]:
+        """Device address of the master's score board in this process (None: no board / not a CUDA member)."""
+        if self._board is None or self.device.type != "cuda":
+            return None
+        if self._board_ptr is None:
+            if "ptr" in self._board and int(self._board.get("owner_pid", os.getpid())) == os.getpid():
+                self._board_ptr = int(self._board["ptr"])          # the board lives in this very process
+            else:
+                import ctypes as C
+                from ..ops import native
+                out = C.c_void_p()
+                native.check(native.lib().dtf_ipc_open_handle(self._board["handle"], C.byref(out)), "open score board")
+                self._board_ptr = int(out.value)
+        return self._board_ptr
+
+    def _attach_board(self) -> None:
+        """Native single-GPU members: the evaluation kernels add their hits straight into the board slot.  Done
+        once, before the first evaluation graph is captured (the pointer is baked into that graph)."""
+        board = self._board_pointer()
+        if board is not None and self.dp_size == 1 and hasattr(self.engine, "board_slot_ptr"):
+            from ..parallel import scoreboard as sb
+            self.engine.board_slot_ptr = sb.slot_ptr(board, self.cluster_id)
+
+    def evaluate(self, final: bool = True) -> float:
+        """Accuracy over the eval set (``final``: the last evaluation of this round -- only that one releases the
+        round's epoch on the score board).  A data-parallel member shards the eval batches over its replicas
         (batch b goes to replica b % dp_size) and sums (correct, seen, non-finite-loss flag) over the group, so
-        every replica ends with the same score and the same drop decision."""
+        every replica ends with the same score and the same drop decision.
+
+        With a score board the score is on the board (and the round's epoch released) by device-side work
+        alone, enqueued before this function first synchronises with the host: the master ranks from the board
+        while this member is still reading its own accuracy back (``pbt_cluster.py:114-128`` gathered it)."""
+        from ..parallel import scoreboard as sb
         bs = int(self.hparams["batch_size"])
         it = BatchIterator(len(self.eval_set), bs, False, device=self.device)
         correct = torch.zeros((), dtype=torch.int64, device=self.device)
         seen = 0
         group = getattr(self.dp_group, "group", None) if self.dp_size > 1 else None
         shard = group is not None
+        board = self._board_pointer() if self.dp_rank == 0 else None
+        direct = board is not None and getattr(self.engine, "board_slot_ptr", 0) != 0
+        epoch = self.rounds_trained + 1
         with self._timed("eval"):
+            if direct:
+                sb.reset(board, self.cluster_id)
             for b, idx in enumerate(it.epoch_batches()):
                 if self.eval_batches is not None and b >= self.eval_batches:
                     break
@@ -227,7 +262,10 @@ class GpuMember(ModelBase):
                     x = self.preprocess(self.eval_set.images[idx], False)
                     correct += self.engine.eval_batch(x, self.eval_set.labels[idx]).to(torch.int64)
                 seen += int(idx.numel())
-        loss = self.engine.last_loss
+            loss = self.engine.last_loss
+            if direct and final:   # hits and seen are already in the slot; the drop decision is taken on the device
+                sb.release(board, self.cluster_id, epoch, loss=loss.reshape(-1)[:1].float() if loss is not None
+                           and loss.dtype == torch.float32 else None)
         bad = loss is not None and not bool(torch.isfinite(loss))
         if shard:
             import torch.distributed as dist
@@ -235,28 +273,42 @@ class GpuMember(ModelBase):
                                   torch.tensor(int(bad), device=self.device)]).to(torch.int64)
             dist.all_reduce(packed, group=group)
             correct, seen, bad = packed[0], int(packed[1].item()), bool(packed[2].item() > 0)
+        if board is not None and bad and direct and not final:
+            sb.release(board, self.cluster_id, epoch, dropped=True)
+        if board is not None and not direct and (final or bad):
+            if bad:
+                sb.release(board, self.cluster_id, epoch, dropped=True)
+            else:
+                cell = correct.to(torch.int32).reshape(1).contiguous()
+                sb.publish(board, self.cluster_id, cell, seen, epoch=epoch, reset=False)
         if bad:
             return float("nan")
-        self._publish_score(correct, seen)
-        return float(correct.item()) / max(seen, 1)
+        hits = int(correct.item())
+        self._last_score = (hits, seen)
+        return float(hits) / max(seen, 1)
 
-    def _publish_score(self, correct: torch.Tensor, seen: int) -> None:
-        """Device path of the eval-score reduction: the hit counter goes to this member's slot of the
-        master-visible board (peer store + release of the round epoch), no host round trip involved."""
-        if self._board is None or self.device.type != "cuda" or self.dp_rank != 0:
+    def publish_dropped(self) -> None:
+        """The worker is about to drop this member (its training raised): leave the dropped marker on the
+        score board so that the master's ranking does not wait for it."""
+        if self.dp_rank != 0:
+            return
+        try:
+            board = self._board_pointer()
+            if board is not None:
+                from ..parallel import scoreboard as sb
+                sb.release(board, self.cluster_id, self.rounds_trained + 1, dropped=True)
+        except Exception:
+            pass        # a broken CUDA context cannot publish; the master falls back to the GET gather on timeout
+
+    def _republish_score(self) -> None:
+        """A member that stopped early (stop_threshold) keeps its score: show it for the new round as well."""
+        board = self._board_pointer() if self.dp_rank == 0 else None
+        if board is None:
             return
         from ..parallel import scoreboard as sb
-        if self._board_ptr is None:
-            if "ptr" in self._board:
-                self._board_ptr = int(self._board["ptr"])
-            else:
-                import ctypes as C
-                from ..ops import native
-                out = C.c_void_p()
-                native.check(native.lib().dtf_ipc_open_handle(self._board["handle"], C.byref(out)), "open score board")
-                self._board_ptr = int(out.value)
-        cell = correct.to(torch.int32).reshape(1).contiguous()
-        sb.publish(self._board_ptr, self.cluster_id, cell, seen, epoch=self.rounds_trained + 1, reset=False)
+        hits, seen = getattr(self, "_last_score", (0, 1))
+        cell = torch.tensor([hits], dtype=torch.int32, device=self.device)
+        sb.publish(board, self.cluster_id, cell, seen, epoch=self.rounds_trained + 1, reset=False)
 
     def make_symmetric_alloc(self, state_bytes: int) -> torch.Tensor:
         """``arena_alloc`` callback for native engines: puts the member state in exportable memory
@@ -282,22 +334,33 @@ class GpuMember(ModelBase):
         rows = []
         ebe = min(self.epochs_between_evals, max(num_epoch, 1))
         done = 0
+        if self.stopped_early:
+            self._republish_score()
         while done < num_epoch and not self.stopped_early:
             n = ebe if num_epoch - done - ebe >= ebe else num_epoch - done
             for _ in range(n):
                 self.train_one_epoch()
             done += n
-            self.accuracy = self.evaluate()
+            if done >= num_epoch and self.symm is not None:
+                # The round's weights are final: publish the snapshot BEFORE the evaluation, so that its epoch
+                # flag is released ahead of the score's on the same stream -- by the time the master can rank
+                # this member, a loser's pull of this snapshot never has to wait.
+                from ..parallel import exploit
+                exploit.publish(self, self.rounds_trained)
+                self._published_round = self.rounds_trained
+            self.accuracy = self.evaluate(final=done >= num_epoch)
             rows.append(self.csv_row(self.epoch_index_for_csv(done - 1), self.accuracy))
             if self._bench_logger is not None:      # resnet_run_loop.py:466 log_evaluation_result
                 self._bench_logger.log_evaluation_result({"accuracy": self.accuracy, "global_step": self.engine.step})
             if not math.isnan(self.accuracy) and past_stop_threshold(self.stop_threshold, float(self.accuracy)):
                 self.stopped_early = True           # resnet_run_loop.py:505-507; later train() calls are no-ops
+                if done < num_epoch:
+                    self._republish_score()         # the round ends here: release its epoch on the score board
         self.bump_epochs(num_epoch)
         if math.isnan(self.accuracy):
             return                      # the worker drops the member; nothing to persist
-        if self.symm is not None:       # publish the round's snapshot where peers can pull it
-            from ..parallel import exploit
+        if self.symm is not None and getattr(self, "_published_round", -1) != self.rounds_trained:
+            from ..parallel import exploit      # (stopped early: the state did not change, the snapshot moves on)
             exploit.publish(self, self.rounds_trained)
         self.rounds_trained += 1
         last = self.epoches_trained >= total_epochs or self.stopped_early

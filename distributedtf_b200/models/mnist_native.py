@@ -156,6 +156,7 @@ class NativeMnistEngine(NativeEngineBase):
         h.loss_scale = 1.0
         h.batch, h.HW, h.C, h.classes = nb, 1, 1024, 10
         h.has_bn, h.training, h.update_running = 0, int(training), 0
+        h.board_hits = 0 if training else self.board_slot_ptr     # evaluation hits go straight to the score board
         native.head(h)
         self._count += 1
 

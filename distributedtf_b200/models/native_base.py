@@ -90,6 +90,7 @@ class NativeEngineBase:
         self._seed = seed
         self._count = 0
         self._side = None                       # side stream for independent kernels (engine-specific use)
+        self.board_slot_ptr = 0                 # this member's score-board slot (device / peer pointer), 0 = none
         self._src = None                        # (images_all, labels_all) while an indexed step is being issued
         self._idx_buf = None
 

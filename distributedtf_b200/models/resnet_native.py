@@ -320,6 +320,7 @@ class NativeResNetEngine(NativeEngineBase):
         h.loss_scale = 1.0
         h.batch, h.HW, h.C, h.classes = nb, b.h * b.h, b.c, self.cfg.num_classes
         h.has_bn, h.training, h.update_running = 1, int(training), int(training)
+        h.board_hits = 0 if training else self.board_slot_ptr     # evaluation hits go straight to the score board
         native.head(h)
         self._count += 1
 

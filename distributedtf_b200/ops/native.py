@@ -110,7 +110,8 @@ class Head(C.Structure):
                 ("logits_out", C.c_void_p), ("dw", C.c_void_p), ("db", C.c_void_p), ("t_out", C.c_void_p),
                 ("bwd_stats_out", C.c_void_p), ("loss_scale", C.c_float),
                 ("batch", C.c_int), ("HW", C.c_int), ("C", C.c_int), ("classes", C.c_int),
-                ("has_bn", C.c_int), ("training", C.c_int), ("update_running", C.c_int)]
+                ("has_bn", C.c_int), ("training", C.c_int), ("update_running", C.c_int),
+                ("board_hits", C.c_void_p)]
 
 
 class Hparams(C.Structure):

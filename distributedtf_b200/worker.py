@@ -124,6 +124,9 @@ class TrainingWorker:
         except Exception:  # member-level failure: drop it, keep the worker alive
             if self.verbose:
                 traceback.print_exc()
+            marker = getattr(g, "publish_dropped", None)
+            if marker is not None:      # device score board: the master must not wait for this member
+                marker()
             return False
 
     def _train_member_on_stream(self, g, num_epoches: int, total_epochs: int) -> bool:

@@ -111,6 +111,10 @@ typedef struct {
     float loss_scale;
     int batch, HW, C, classes;
     int has_bn, training, update_running;
+    unsigned int* board_hits;  /* optional (evaluation): this member's DtfScoreSlot on the master-visible score board, a
+                                  peer pointer when the master sits on another GPU.  Every hit is added to slot->hits and
+                                  the batch size to slot->seen with system-scope reductions, so the eval score reaches the
+                                  master without a host round trip (pbt_cluster.py:114-128 gathered it over MPI). */
 } DtfHead;
 
 /* ---- optimizer ------------------------------------------------------------------------ */
@@ -178,11 +182,15 @@ int dtf_preprocess_indexed(const uint8_t* images, const int* indices, const int*
 /* ---- communication-bound hot paths over NVLink peer memory (csrc/comm_kernels.cu) ------------- */
 #define DTF_MAX_DP 8
 
+/* One member's cell of the score board.  hits / seen are accumulated by the evaluation kernels (dtf_head with
+ * board_hits set); `epoch` is release-stored once the member's evaluation of a round is complete.  hits ==
+ * DTF_SCORE_DROPPED marks a member whose loss went non-finite (the worker drops it, training_worker.py:63-80). */
 typedef struct {
-    float score;
-    unsigned int count;
+    unsigned int hits;
+    unsigned int seen;
     unsigned long long epoch;
 } DtfScoreSlot;
+#define DTF_SCORE_DROPPED 0xFFFFFFFFu
 
 /* Exploit transfer (pbt_cluster.py:145-147,168-181 did this with `cp`): copy `bytes` of member state
  * from `src` to `dst` — either may be a peer-mapped pointer — skip the hyper-parameter block at
@@ -191,11 +199,27 @@ typedef struct {
 int dtf_exploit_copy(void* dst, const void* src, long long bytes, long long hp_offset, const DtfHparams* new_hp,
                      void* zero_region, long long zero_bytes, unsigned long long* done_flag,
                      unsigned long long epoch, unsigned int* arrive_counter, int max_ctas, cudaStream_t stream);
+/* Same, device-ordered against the producer of `src`: every CTA first waits (ld.acquire.sys, watchdog-protected)
+ * until *wait_flag >= wait_value.  The winner publishes its round snapshot with dtf_exploit_copy(done_flag =
+ * &snapshot_epoch[parity], epoch = round + 1); the loser passes that flag's (peer) address here, so the pull may
+ * be launched before the winner's publish has finished and no host barrier sits between the two. */
+int dtf_exploit_copy_ordered(void* dst, const void* src, long long bytes, long long hp_offset,
+                             const DtfHparams* new_hp, void* zero_region, long long zero_bytes,
+                             unsigned long long* done_flag, unsigned long long epoch, unsigned int* arrive_counter,
+                             const unsigned long long* wait_flag, unsigned long long wait_value, int max_ctas,
+                             cudaStream_t stream);
 
-/* Eval-score reduction (pbt_cluster.py:114-128): accuracy = *correct / total is stored into the
- * master-visible board slot (peer pointer allowed) followed by a release-store of `epoch`. */
+/* Eval-score reduction (pbt_cluster.py:114-128).  dtf_score_publish stores (*correct, total) into the
+ * master-visible board slot (peer pointer allowed) followed by a release-store of `epoch` — the path of a
+ * data-parallel member, whose replicas first sum their counts.  A single-GPU member lets its evaluation
+ * kernels add straight into the slot (DtfHead.board_hits) and brackets them with dtf_score_reset (hits = seen
+ * = 0 at the start of the evaluation) and dtf_score_release (epoch release once the last batch is in; writes
+ * DTF_SCORE_DROPPED instead of the hits when *loss is not finite; loss may be NULL). */
 int dtf_score_publish(DtfScoreSlot* board_slot, const int* correct, int total, unsigned long long epoch,
                       int reset_counter, int* correct_rw, cudaStream_t stream);
+int dtf_score_reset(DtfScoreSlot* board_slot, cudaStream_t stream);
+int dtf_score_release(DtfScoreSlot* board_slot, unsigned long long epoch, const float* loss, int dropped,
+                      cudaStream_t stream);
 
 /* Fused one-shot gradient all-reduce + optimizer update for a data-parallel member
  * (distribution_utils.py:41-47 + resnet_run_loop.py:552-586). */

@@ -235,3 +235,112 @@ def test_members_in_flight_matches_sequential_on_toy(tmp_path):
         outs.append(run_local(cfg))
     assert outs[0]["best"] == outs[1]["best"]
     assert [h["pairs"] for h in outs[0]["history"]] == [h["pairs"] for h in outs[1]["history"]]
+
+
+# --------------------------------------------------------------------------- device score board as the barrier
+class FakeBoard:
+    """Stands in for parallel/scoreboard.ScoreBoard: members write (score, epoch) into a dict."""
+
+    def __init__(self):
+        self.slots = {}
+        self.lock = threading.Lock()
+        self.reads = []
+
+    def put(self, member, score, epoch):
+        with self.lock:
+            self.slots[member] = (score, epoch)
+
+    def read(self, epoch, members=None, timeout=60.0):
+        deadline = time.time() + timeout
+        ids = list(members)
+        while True:
+            with self.lock:
+                if all(self.slots.get(i, (0, 0))[1] >= epoch for i in ids):
+                    self.reads.append((epoch, tuple(ids)))
+                    return {i: self.slots[i][0] for i in ids}
+            if time.time() > deadline:
+                raise TimeoutError("members did not publish")
+            time.sleep(0.001)
+
+
+class BoardModel(ScoreModel):
+    """Publishes its score on the fake board at the end of train, like a GPU member's evaluation kernels."""
+    board = None
+    silent = set()          # members that never publish (board time-out path)
+    nan_at = {}             # member -> round at which its score turns NaN
+    seen = []               # instruction trace of the workers
+
+    def train(self, num_epoch, total_epochs):
+        super().train(num_epoch, total_epochs)
+        self.rounds = getattr(self, "rounds", 0) + 1
+        if BoardModel.nan_at.get(self.cluster_id) == self.rounds:
+            self.accuracy = float("nan")
+        if self.cluster_id not in BoardModel.silent:
+            BoardModel.board.put(self.cluster_id, self.accuracy, self.rounds)
+
+
+class TracingWorker(TrainingWorker):
+    def main_loop(self):
+        orig = self.comm.recv
+
+        def recv(source, **kw):
+            msg = orig(source=source, **kw)
+            BoardModel.seen.append((self.rank, WI(msg[0]).name))
+            return msg
+        self.comm.recv = recv
+        super().main_loop()
+
+
+def _board_cluster(pop, workers, tmp_path, **kw):
+    BoardModel.board, BoardModel.silent, BoardModel.nan_at, BoardModel.seen = FakeBoard(), set(), {}, []
+    fabric = LocalFabric(workers + 1)
+    ws = [TracingWorker(fabric.endpoint(r), 0, BoardModel, save_base_dir=str(tmp_path / "model_"), verbose=False)
+          for r in range(1, workers + 1)]
+    threads = [threading.Thread(target=w.main_loop, daemon=True) for w in ws]
+    for t in threads:
+        t.start()
+    cluster = PBTCluster(pop, fabric.endpoint(0), 0, 1, save_root=str(tmp_path), verbose=False, exploit_path="p2p",
+                         initial_hparams=[_hp(i) for i in range(pop)], scoreboard=BoardModel.board, **kw)
+    return cluster, ws, threads
+
+
+def test_board_is_the_round_barrier_and_get_leaves_the_critical_path(tmp_path):
+    """With a score board the master ranks without a GET between TRAIN and SET; the hyper-parameter refresh
+    (GET) and the next TRAIN follow EXPLORE back to back."""
+    pop = 8
+    cluster, ws, threads = _board_cluster(pop, 2, tmp_path)
+    cluster.train(3)
+    values = sorted(cluster.get_all_values())
+    cluster.kill_all_workers()
+    for t in threads:
+        t.join(5)
+    assert cluster.board_fallbacks == 0 and [e for e, _ in BoardModel.board.reads] == [1, 2, 3]
+    trace = [name for rank, name in BoardModel.seen if rank == 1]
+    # initial view, then per round TRAIN -> SET (rank 1 owns the losers) -> EXPLORE -> GET, flush GET, our GET, EXIT
+    assert trace == ["ADD_GRAPHS", "GET",
+                     "TRAIN", "SET", "EXPLORE", "GET",
+                     "TRAIN", "SET", "EXPLORE", "GET",
+                     "TRAIN", "SET", "EXPLORE", "GET", "GET", "GET", "EXIT"]
+    n = math.ceil(pop / 4)
+    for h in cluster.history:           # same pairing as the GET path (scores = id + eps)
+        assert h["pairs"] == [(pop - n + i, i) for i in range(n)]
+    members = {g.cluster_id: g for w in ws for g in w.worker_graphs}
+    assert [e["src_id"] for e in members[0].adopted] == [pop - n] * 3
+    # the master's view follows the explored hyper-parameters of the losers
+    assert {v[0]: v[2] for v in values} == {i: m.hparams for i, m in members.items()}
+
+
+def test_board_dropped_marker_and_timeout_fallback(tmp_path):
+    cluster, ws, threads = _board_cluster(6, 2, tmp_path)
+    BoardModel.nan_at = {5: 1}            # best member turns NaN in round 1: marker on the board, worker drops it
+    cluster.train(1)
+    assert cluster.pop_size == 5 and cluster.history[0]["pairs"] == [(3, 0), (4, 1)]
+    BoardModel.silent = {2}               # a member that never reaches the board: time out, rank from a GET gather
+    cluster.board_timeout = 0.3
+    cluster.train(1)
+    assert cluster.board_fallbacks == 1 and len(cluster.history) == 2
+    values = cluster.get_all_values()
+    cluster.kill_all_workers()
+    for t in threads:
+        t.join(5)
+    assert sorted(v[0] for v in values) == [0, 1, 2, 3, 4]

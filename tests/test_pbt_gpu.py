@@ -116,6 +116,10 @@ def test_scoreboard_feeds_the_ranking(tmp_path):
     scores = seen["board"].read(2, members=[0, 1, 2, 3], timeout=5)
     assert set(scores) == {0, 1, 2, 3} and all(0 <= v <= 1 for v in scores.values())
     assert out["pop_size"] == 4
+    # what the evaluation kernels added into the board equals what each member read back and logged
+    for i in range(4):
+        rows = open(tmp_path / "savedata" / f"model_{i}" / "learning_curve.csv").read().strip().splitlines()
+        assert float(rows[-1].split(",")[1]) == pytest.approx(scores[i], abs=1e-6)
 
 
 @pytest.mark.parametrize("model", ["cifar10", "mnist"])

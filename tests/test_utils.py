@@ -350,9 +350,9 @@ def test_member_train_cycles_follow_epochs_between_evals(tmp_path):
                      resnet_size=8, epochs_between_evals=2, device=torch.device("cpu"))
     evals = []
     real = m.evaluate
-    m.evaluate = lambda: (evals.append(1), real())[1]
+    m.evaluate = lambda **kw: (evals.append(kw.get('final')), real(**kw))[1]
     m.train(5, 5)
-    assert len(evals) == 2 and m.epoches_trained == 5          # cycles of 2 and 3 epochs
+    assert evals == [False, True] and m.epoches_trained == 5          # cycles of 2 and 3 epochs
     rows = open(tmp_path / "model_3" / "learning_curve.csv").read().strip().splitlines()
     assert [r.split(",")[0] for r in rows[1:]] == ["1", "4"]
 
