@@ -41,7 +41,10 @@ def parse():
     p.add_argument("--gpus", type=int, default=1)
     p.add_argument("--steps", type=int, default=200)
     p.add_argument("--warmup", type=int, default=20)
-    p.add_argument("--impl", choices=["native", "restated", "reference"], default="native")
+    p.add_argument("--impl", choices=["native", "restated", "restated-graph", "reference"], default="native",
+                   help="native = this framework; restated = the same model / update rules in torch eager on "
+                        "cuDNN/cuBLAS (launch-bound); restated-graph = that step captured in a CUDA graph (what a "
+                        "TF-1 graph executor amounts to; the strong library baseline); reference = unavailable here")
     p.add_argument("--batch", type=int, default=BATCH)
     p.add_argument("--resnet-size", type=int, default=32)
     p.add_argument("--dp-size", type=int, default=1, choices=[1, 2, 4],
@@ -203,11 +206,9 @@ def main():
     else:
         from distributedtf_b200.models.engine_eager import EagerEngine
         from distributedtf_b200.utils.data import cifar_preprocess_torch
-        if D > 1:
-            raise SystemExit("--dp-size > 1 is implemented for --impl native")
-        init = resnet.init_params(cfg, hp["initializer"], 1234 + rank)
+        init = resnet.init_params(cfg, hp["initializer"], 1234 + member_id)
         eng = EagerEngine(resnet.param_specs(cfg), lambda p, x, t: resnet.forward(cfg, p, x, t), init, hp, dev,
-                          compute_dtype=torch.bfloat16, lr_schedule=True)
+                          compute_dtype=torch.bfloat16, lr_schedule=True, dp_group=dp_group)   # NCCL all-reduce for D > 1
 
     # ---- synthetic CIFAR-shaped data: resident uint8 dataset larger than L2 + pinned host copy ----
     g = torch.Generator().manual_seed(99 + rank)
@@ -219,10 +220,66 @@ def main():
     idx_dev = perm[: nbatches * B].view(nbatches, B).to(dev)
     idx_host = perm[: nbatches * B].view(nbatches, B)
 
+    def preprocess_on_device(x_u8):
+        """cifar_preprocess_torch with the random draw on the device (no host round trip, graph-capturable)."""
+        x = x_u8.float()
+        n, h, w, c = x.shape
+        padded = torch.zeros(n, h + 8, w + 8, c, device=dev)
+        padded[:, 4:4 + h, 4:4 + w] = x
+        oy = torch.randint(0, 9, (n,), device=dev)
+        ox = torch.randint(0, 9, (n,), device=dev)
+        flip = torch.rand(n, device=dev) < 0.5
+        rows = oy[:, None] + torch.arange(h, device=dev)[None]
+        cols = ox[:, None] + torch.arange(w, device=dev)[None]
+        cols = torch.where(flip[:, None], cols.flip(1), cols)
+        x = padded[torch.arange(n, device=dev)[:, None, None], rows[:, :, None], cols[:, None, :]]
+        mean = x.mean(dim=(1, 2, 3), keepdim=True)
+        std = x.std(dim=(1, 2, 3), keepdim=True, unbiased=False)
+        return (x - mean) / torch.clamp(std, min=1.0 / float(h * w * c) ** 0.5)
+
+    graphed = None
+    if args.impl == "restated-graph":
+        if D > 1:
+            raise SystemExit("restated-graph covers one GPU per member; use --impl restated for the NCCL data-parallel arm")
+
+        class GraphedStep:
+            """Whole step (augmentation, forward, backward, update) of the torch model in ONE CUDA graph:
+            static input buffers, autograd captured, cuDNN / cuBLAS kernels underneath."""
+
+            def __init__(self):
+                self.x = torch.zeros(B, 32, 32, 3, dtype=torch.uint8, device=dev)
+                self.y = torch.zeros(B, dtype=torch.int64, device=dev)
+                side = torch.cuda.Stream()
+                side.wait_stream(torch.cuda.current_stream())
+                with torch.cuda.stream(side):
+                    for _ in range(3):
+                        eng.train_step(preprocess_on_device(self.x), self.y)
+                torch.cuda.current_stream().wait_stream(side)
+                torch.cuda.synchronize()
+                self.graph = torch.cuda.CUDAGraph()
+                eng.flat.grad = None
+                with torch.cuda.graph(self.graph):
+                    self.loss = eng.train_step(preprocess_on_device(self.x), self.y)
+
+            def __call__(self, idx):
+                torch.index_select(dev_images, 0, idx, out=self.x)
+                self.y.copy_(dev_labels[idx])
+                self.graph.replay()
+                return self.loss
+
+            def step_from(self, images_u8, labels):
+                self.x.copy_(images_u8, non_blocking=True)
+                self.y.copy_(labels, non_blocking=True)
+                self.graph.replay()
+                return self.loss
+        graphed = GraphedStep()
+
     def step_resident(i):
         idx = idx_dev[i % nbatches]
         if args.impl == "native":       # the step's first kernel gathers the batch from the resident dataset
             return eng.train_step_indexed(dev_images, dev_labels, idx, augment=True)
+        if graphed is not None:
+            return graphed(idx)
         x = cifar_preprocess_torch(dev_images[idx], True)
         return eng.train_step(x, dev_labels[idx])
 
@@ -243,6 +300,8 @@ def main():
         d_lab.copy_(stage_lab, non_blocking=True)
         if args.impl == "native":
             loss = eng.train_step_u8(d_img, d_lab, augment=True)
+        elif graphed is not None:
+            loss = graphed.step_from(d_img, d_lab)
         else:
             loss = eng.train_step(cifar_preprocess_torch(d_img, True), d_lab)
         loss_host.copy_(loss.reshape(1), non_blocking=True)
@@ -282,13 +341,20 @@ def main():
         if dp_rank == 0:
             eng.board_slot_ptr = sb.slot_ptr(board_ptr, member_id)
 
-    def pbt_event_native():
+    def pbt_begin_native():
+        """Device half of the event: nothing here waits for the host or for another rank."""
         rnd = pbt_round[0]
         exploit.publish_buffer(symm_buf, rnd)                           # snapshot + release of its epoch flag
         if dp_rank == 0:
             sb.reset(board_ptr, member_id)
             eng.eval_batch_indexed(dev_images, dev_labels, eval_idx)    # hits -> board slot (head kernel, peer red)
             sb.release(board_ptr, member_id, rnd + 1, loss=eng.loss_cell)
+
+    def pbt_finish_native():
+        """Controller half: the board is the barrier.  It runs PBT_LOOKAHEAD training steps after the device half,
+        so the GPU works on while this host thread waits for the slowest member's score (a loser's look-ahead
+        steps are overwritten by the winner's state, which is what exploit means anyway)."""
+        rnd = pbt_round[0]
         scores = board_view.read(rnd + 1, members=range(members), timeout=60.0, poll=0.0)
         order = sorted(range(members), key=lambda m: (scores[m], m))    # ascending, ties by id: same on every rank
         for top, bottom in exploit_pairs(order):
@@ -316,7 +382,7 @@ def main():
         loss = eng.last_loss.reshape(1).float().clone()
         allv = [torch.zeros_like(loss) for _ in range(world)]
         dist.all_gather(allv, loss)
-        scores = [-float(allv[m].item()) for m in range(members)]
+        scores = [-float(allv[m * D].item()) for m in range(members)]
         order = sorted(range(members), key=lambda m: scores[m])
         n = -(-members // 4)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -325,23 +391,28 @@ def main():
             if winner == loser:
                 continue
             flat = eng.flat.detach()
-            if rank == winner:
+            if member_id == winner:       # replica r of the winner feeds replica r of the loser
                 for t in (flat, eng.slot0, eng.slot1):
-                    dist.send(t, dst=loser)
-            elif rank == loser:
+                    dist.send(t, dst=loser * D + dp_rank)
+            elif member_id == loser:
                 for t in (flat, eng.slot0, eng.slot1):
-                    dist.recv(t, src=winner)
+                    dist.recv(t, src=winner * D + dp_rank)
         e1.record()
         exploit_events.append((e0, e1))
         pbt_round[0] += 1
 
-    pbt_event = pbt_event_native if args.impl == "native" else pbt_event_restated
+    if args.impl == "native":
+        pbt_begin, pbt_finish = pbt_begin_native, pbt_finish_native
+    else:
+        pbt_begin, pbt_finish = (lambda: None), pbt_event_restated
+    PBT_LOOKAHEAD = 2
 
     # ---- warm-up (includes one PBT event: eval graph capture, peer mappings and -- in the library arm -- NCCL's
     #      lazy point-to-point connection set-up all happen here, not in the timed region) ----
     for i in range(max(args.warmup, 3)):
         step_resident(i)
-    pbt_event()
+    pbt_begin()
+    pbt_finish()
     exploit_events.clear()
     barrier()
 
@@ -355,7 +426,9 @@ def main():
         for i in range(steps):
             fn(1000 + i)
             if with_pbt and i == steps // 2:
-                pbt_event()
+                pbt_begin()
+            if with_pbt and i == min(steps // 2 + PBT_LOOKAHEAD, steps - 1):
+                pbt_finish()
         e1.record()
         barrier()
         wall = time.time() - t0

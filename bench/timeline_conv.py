@@ -24,13 +24,15 @@ for rep in range(3):
     nat.conv_gemm(g, wpk, out, NB=NB, Ho=H, Wo=H, N=Cc, epi_mode=nat.EPI_RESIDUAL, epi_res=res, epi_stats_out=so)
     e1.record()
     torch.cuda.synchronize()
-    buf = (ctypes.c_ulonglong * 64)()
+    buf = (ctypes.c_ulonglong * 128)()
     rc = lib.dtf_debug_timeline(buf)
     t = list(buf)
     t0 = t[0]
     names = {0: "setup done (pre-sync)", 1: "after sync", 2: "weights landed", 3: "role done (tid0)", 4: "final sync"}
     for i in range(4): names[8 + i] = f"mma: full[{i}] ready"; names[12 + i] = f"mma: tile {i} issued"
     for i in range(8): names[16 + i] = f"gather: batch {i} start"; names[24 + i] = f"gather: batch {i} arrived"
+    for i in range(8): names[64 + i] = f"gather: batch {i} empty ok, loads next"; names[72 + i] = f"gather: batch {i} stored"; names[80 + i] = f"gather: batch {i} fenced"
+    for i in range(8): names[88 + i] = f"MMA {i}: acc free"; names[96 + i] = f"MMA {i}: operands ready"; names[104 + i] = f"MMA {i}: issued+committed"; names[112 + i] = f"epi {i}: waiting for acc"
     for i in range(8): names[32 + i] = f"epi: acc_full tile {i}"; names[40 + i] = f"epi: tile {i} done"
     print(f"--- rep {rep}: event time {e0.elapsed_time(e1)*1000:.1f} us, rc={rc}")
     for k, v in sorted(((k, v) for k, v in enumerate(t) if v and k in names), key=lambda kv: kv[1]):

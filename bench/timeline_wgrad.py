@@ -22,13 +22,15 @@ for i in range(4):
     names[8 + i] = f"mma: full[{i}] ready"; names[12 + i] = f"mma: tile {i} issued+committed"
     names[16 + 4 * i] = f"gather {i}: stage free, start loads"; names[17 + 4 * i] = f"gather {i}: rows stored"
     names[18 + 4 * i] = f"gather {i}: barrier passed"; names[19 + 4 * i] = f"gather {i}: expanded + arrived"
+for i in range(4):
+    names[64 + i] = f"expander {i}: halo ready"; names[72 + i] = f"expander {i}: copies issued"
 for rep in range(3):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     nat.conv_wgrad(gx, gg, dw, NB=NB, Ho=H, Wo=H, Cout=Cc)
     e1.record()
     torch.cuda.synchronize()
-    buf = (ctypes.c_ulonglong * 64)()
+    buf = (ctypes.c_ulonglong * 128)()
     lib.dtf_debug_timeline(buf)
     t = list(buf); t0 = t[0]
     print(f"--- rep {rep}: event time {e0.elapsed_time(e1)*1000:.1f} us")

@@ -17,11 +17,15 @@ import sys
 ROOT = os.path.dirname(os.path.abspath(__file__))
 SRC = os.path.join(ROOT, "csrc")
 OUT_DIR = os.path.join(ROOT, "distributedtf_b200", "lib")
-OBJ_DIR = os.path.join(ROOT, "build", "obj")
-LIB = os.path.join(OUT_DIR, "libdtf_b200.so")
+# DTF_BUILD_TAG=name builds a side-by-side variant (e.g. DTF_TIMING=1 DTF_BUILD_TAG=timing -> libdtf_b200_timing.so,
+# loaded with DTF_LIB=...); the production library has no tag
+_TAG = os.environ.get("DTF_BUILD_TAG", "")
+OBJ_DIR = os.path.join(ROOT, "build", "obj" + ("_" + _TAG if _TAG else ""))
+LIB = os.path.join(OUT_DIR, "libdtf_b200" + ("_" + _TAG if _TAG else "") + ".so")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 NVCC_FLAGS = ARCH + ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-I" + os.path.join(ROOT, "include"),
-                     "-I" + SRC, "--expt-relaxed-constexpr"] + (["-DDTF_TIMING"] if os.environ.get("DTF_TIMING") else [])
+                     "-I" + SRC, "--expt-relaxed-constexpr"] + (["-DDTF_TIMING"] if os.environ.get("DTF_TIMING") else []) + \
+    os.environ.get("DTF_NVCC_EXTRA", "").split()
 
 
 def nvcc() -> str:

@@ -26,7 +26,7 @@ class EagerEngine:
     def __init__(self, specs: Sequence[ParamSpec], forward: Callable[..., torch.Tensor],
                  init: Dict[str, torch.Tensor], hparams: Dict[str, Any], device, *,
                  compute_dtype: torch.dtype = torch.float32, lr_schedule: bool = False,
-                 channels_last: bool = True, loss_scale: Optional[float] = None):
+                 channels_last: bool = True, loss_scale: Optional[float] = None, dp_group=None):
         self.specs = list(specs)
         self.device = torch.device(device)
         self.forward_fn = forward
@@ -35,6 +35,10 @@ class EagerEngine:
         # 1 otherwise (reference: _performance.py:30-33, resnet_run_loop.py:284-294)
         self.loss_scale = float(loss_scale) if loss_scale else (128.0 if compute_dtype == torch.float16 else 1.0)
         self.lr_schedule = lr_schedule
+        # data-parallel baseline (BASELINE.md "B-allreduce-nccl"): NCCL all-reduce of the flat gradient, then the
+        # separate optimizer step -- what the reference's dormant MirroredStrategy path amounts to
+        # (official/utils/misc/distribution_utils.py:41-47)
+        self.dp_group = dp_group
         self.channels_last = channels_last and self.device.type == "cuda"
         self.train_specs = [s for s in self.specs if s.trainable]
         self.state_specs = [s for s in self.specs if not s.trainable]
@@ -96,6 +100,11 @@ class EagerEngine:
         oc = self.hp["opt_case"]
         reg, wd = self.hp.get("regularizer", "None"), float(self.hp.get("weight_decay", 0.0))
         with torch.no_grad():
+            if self.dp_group is not None:
+                import torch.distributed as dist
+                g = g.contiguous()
+                dist.all_reduce(g, group=self.dp_group)
+                g = g / dist.get_world_size(self.dp_group)
             if reg != "None":
                 g = g + self.reg_mask * reference.regularizer_grad(self.flat, reg, wd)
             lr = self.current_lr()
