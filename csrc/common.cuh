@@ -23,7 +23,9 @@ namespace dtf {
 // ---------------------------------------------------------------------------------------
 // error reporting from device code: print the failing site and trap (never hang the GPU)
 // ---------------------------------------------------------------------------------------
-DTF_DEVINL void device_fail(unsigned int code) {
+// (never inlined: the printf set-up would otherwise be copied into every wait site -- tens of kilobytes of cold
+// code inside the kernels' loops, and instruction-cache misses are a first-order cost for 10 us kernels)
+static __device__ __noinline__ void device_fail(unsigned int code) {
     printf("[dtf_b200] device watchdog/assert: site 0x%x block (%d,%d) thread %d\n", code,
            (int)blockIdx.x, (int)blockIdx.y, (int)threadIdx.x);
     __trap();
@@ -70,12 +72,18 @@ DTF_DEVINL bool mbar_try_wait(uint32_t bar, uint32_t parity) {
 }
 // Wait for the phase with the given parity to complete.  Traps (instead of hanging the GPU)
 // if the barrier has not flipped within the watchdog window.
-DTF_DEVINL void mbar_wait(uint32_t bar, uint32_t parity, unsigned int site) {
-    if (mbar_try_wait(bar, parity)) return;
+static __device__ __noinline__ void mbar_wait_slow(uint32_t bar, uint32_t parity, unsigned int site) {
     const uint64_t t0 = globaltimer_ns();
     while (!mbar_try_wait(bar, parity)) {
         if (globaltimer_ns() - t0 > kWatchdogNs) device_fail(0x1000u | site);
     }
+}
+DTF_DEVINL void mbar_wait(uint32_t bar, uint32_t parity, unsigned int site) {
+    // a few polls inline (try_wait itself suspends the thread for a while), then the out-of-line watchdog loop
+#pragma unroll 1
+    for (int i = 0; i < 8; ++i)
+        if (mbar_try_wait(bar, parity)) return;
+    mbar_wait_slow(bar, parity, site);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -99,6 +107,14 @@ DTF_DEVINL void bulk_g2s(uint32_t dst_smem, const void* src, uint32_t bytes, uin
     asm volatile(
         "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
         ::"r"(dst_smem), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+
+// bulk copy shared -> shared inside the CTA (the async copy engine moves the bytes, no thread touches them);
+// completion is counted on an mbarrier like a global -> shared bulk copy.  16-byte aligned addresses and size.
+DTF_DEVINL void bulk_s2s(uint32_t dst_smem, uint32_t src_smem, uint32_t bytes, uint32_t bar) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+        ::"r"(dst_smem), "r"(src_smem), "r"(bytes), "r"(bar) : "memory");
 }
 
 // ---------------------------------------------------------------------------------------
@@ -240,17 +256,33 @@ inline bool dtf_pdl_enabled() {
     return on != 0;
 }
 template <typename... KArgs, typename... Args>
-inline cudaError_t dtf_launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
-                              Args&&... args) {
+inline cudaError_t dtf_launch_ex(bool cluster_of_one, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem,
+                                 cudaStream_t stream, Args&&... args) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = grid;
     cfg.blockDim = block;
     cfg.dynamicSmemBytes = smem;
     cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cudaLaunchAttribute attr[2];
+    int n = 0;
+    if (cluster_of_one) {      // explicit 1x1x1 cluster: makes the shared::cluster forms (shared -> shared bulk copy) legal
+        attr[n].id = cudaLaunchAttributeClusterDimension;
+        attr[n].val.clusterDim.x = 1;
+        attr[n].val.clusterDim.y = 1;
+        attr[n].val.clusterDim.z = 1;
+        ++n;
+    }
+    if (dtf_pdl_enabled()) {
+        attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[n].val.programmaticStreamSerializationAllowed = 1;
+        ++n;
+    }
     cfg.attrs = attr;
-    cfg.numAttrs = dtf_pdl_enabled() ? 1 : 0;
+    cfg.numAttrs = n;
     return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+template <typename... KArgs, typename... Args>
+inline cudaError_t dtf_launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                              Args&&... args) {
+    return dtf_launch_ex(false, kernel, grid, block, smem, stream, static_cast<Args&&>(args)...);
 }

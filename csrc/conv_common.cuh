@@ -34,6 +34,7 @@ struct SmemConsts {
     float q0[kMaxC], q1[kMaxC], q2[kMaxC];        // prologue second operand (wgrad gy side)
     float e_scale[kMaxC], e_shift[kMaxC], e_mean[kMaxC], e_invstd[kMaxC];   // epilogue
     float bins[2][kMaxC];
+    float wbins[8][2][64];     // halo kernels: private statistics bins of each epilogue warp (no atomics, N <= 64)
 };
 
 // ---- BN helper math -------------------------------------------------------------------
@@ -373,12 +374,21 @@ DTF_DEVINL int butterfly_channel(int lane) {
 //   valid  : this TMEM lane maps to a real output pixel
 // ---------------------------------------------------------------------------------------
 // warp butterfly of 16 per-lane partial sums per statistic -> shared bins (one add per channel per warp)
-DTF_DEVINL void flush_stats16(SmemConsts* cst, float* s1, float* s2, int cg, int lane) {
+// `wb` (optional): this warp's private bins [2][64] -- after the butterfly each even lane owns one channel, so a
+// plain read-modify-write replaces the shared-memory atomic (eight warps hitting the same 16 addresses every tile
+// made those atomics the most expensive part of the epilogue).
+DTF_DEVINL void flush_stats16(SmemConsts* cst, float* s1, float* s2, int cg, int lane, float* wb = nullptr) {
     const float a1 = butterfly16(s1, lane);
     const float a2 = butterfly16(s2, lane);
     if ((lane & 1) == 0) {
-        atomicAdd(&cst->bins[0][cg + butterfly_channel(lane)], a1);
-        atomicAdd(&cst->bins[1][cg + butterfly_channel(lane)], a2);
+        const int c = cg + butterfly_channel(lane);
+        if (wb != nullptr) {
+            wb[c] += a1;
+            wb[64 + c] += a2;
+        } else {
+            atomicAdd(&cst->bins[0][c], a1);
+            atomicAdd(&cst->bins[1][c], a2);
+        }
     }
 }
 
@@ -392,7 +402,7 @@ DTF_DEVINL const dtf_bf16* epilogue_aux_ptr(const DtfConvGemm& P) {
 // when given, the warp butterfly is skipped here and done once per CTA by the caller.
 DTF_DEVINL void epilogue_group(const DtfConvGemm& P, SmemConsts* cst, float* v, bool valid, size_t obase,
                                int cg, int lane, const uint4* aux = nullptr, float* acc1 = nullptr,
-                               float* acc2 = nullptr) {
+                               float* acc2 = nullptr, float* wb = nullptr) {
     float s2[16];
     if (P.epi_mode == DTF_EPI_RESIDUAL) {
         if (valid) {
@@ -436,7 +446,7 @@ DTF_DEVINL void epilogue_group(const DtfConvGemm& P, SmemConsts* cst, float* v, 
 #pragma unroll
                 for (int i = 0; i < 16; ++i) { acc1[i] += s1[i]; acc2[i] += s2[i]; }
             } else {
-                flush_stats16(cst, s1, s2, cg, lane);
+                flush_stats16(cst, s1, s2, cg, lane, wb);
             }
         }
     }
@@ -451,7 +461,7 @@ DTF_DEVINL void epilogue_group(const DtfConvGemm& P, SmemConsts* cst, float* v, 
 #pragma unroll
             for (int i = 0; i < 16; ++i) { acc1[i] += s1[i]; acc2[i] += s2[i]; }
         } else {
-            flush_stats16(cst, s1, s2, cg, lane);
+            flush_stats16(cst, s1, s2, cg, lane, wb);
         }
     }
     if (valid) {

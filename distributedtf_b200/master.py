@@ -193,6 +193,7 @@ class PBTCluster:
                 owner[rec[0]] = rank
         self.cluster_id_to_worker_rank = owner
         self._known = {rec[0]: rec for rec in out}
+        self.pop_size = len(out)              # the GET view is authoritative: dropped members shrink the population
         return out
 
     def _gather_values(self) -> List[List[Any]]:
