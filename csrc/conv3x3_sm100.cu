@@ -55,6 +55,8 @@ constexpr int kHThreads = (kHEpiWarps + 2 + kHGatherWarps) * 32;   // 768
 constexpr int kHGatherThreads = kHGatherWarps * 32;               // 448
 constexpr int kHMaxRows = 224;                                     // halo rows per tile the item maths assumes
 constexpr int kHStages = 4;
+constexpr int kHAcc = 4;     // TMEM accumulators of the forward / dgrad kernels: the MMA warp runs up to four tiles
+                             // ahead of the epilogue sets (with two, accumulator hand-over was the critical cycle)
 
 struct HaloGeom {
     FastDiv div_wp, div_hp;
@@ -76,8 +78,8 @@ struct __align__(16) HaloHeader {
     uint64_t full[kHStages];
     uint64_t empty[kHStages];
     uint64_t halo[kHStages];     // weight gradient: the x halo tile of a stage is in shared memory
-    uint64_t acc_full[2];
-    uint64_t acc_empty[2];
+    uint64_t acc_full[4];
+    uint64_t acc_empty[4];
     uint64_t bfull;
     uint32_t tmem_base;
     uint32_t pad;
@@ -190,7 +192,7 @@ DTF_DEVINL void conv3x3_body(const DtfConvGemm& P, const HaloGeom& G, const int 
             mbar_init(smem_u32(&hdr->full[i]), kHGatherThreads);
             mbar_init(smem_u32(&hdr->empty[i]), 1);
         }
-        for (int i = 0; i < 2; ++i) {
+        for (int i = 0; i < kHAcc; ++i) {
             mbar_init(smem_u32(&hdr->acc_full[i]), 1);
             mbar_init(smem_u32(&hdr->acc_empty[i]), kEpiPerAcc);
         }
@@ -239,24 +241,30 @@ DTF_DEVINL void conv3x3_body(const DtfConvGemm& P, const HaloGeom& G, const int 
         const uint32_t b_pair = static_cast<uint32_t>(2 * N), b_tap = static_cast<uint32_t>(C8 * N);
         const uint64_t adesc0 = umma_desc(smem_u32(smem_a), G.cs, 128);
         const uint64_t bdesc0 = umma_desc(smem_u32(smem_b), N * 16, 128);
+        // the start-address field (bits 0-13 of the low word, units of 16 bytes) never carries out of the field for
+        // addresses inside the 227 KB of shared memory, so the shifted views only touch the low words
+        const uint32_t a_lo0 = static_cast<uint32_t>(adesc0), a_hi = static_cast<uint32_t>(adesc0 >> 32);
+        const uint32_t b_lo0 = static_cast<uint32_t>(bdesc0), b_hi = static_cast<uint32_t>(bdesc0 >> 32);
         const uint32_t stage_units = static_cast<uint32_t>(G.stage_bytes >> 4);
         for (int it = 0; it < my_tiles; ++it) {
-            const uint32_t a = it & 1, st = it % kHStages;
-            mbar_wait(smem_u32(&hdr->acc_empty[a]), ((it >> 1) & 1) ^ 1, 0x32);
+            const uint32_t a = it % kHAcc, st = it % kHStages;
+            mbar_wait(smem_u32(&hdr->acc_empty[a]), ((it / kHAcc) & 1) ^ 1, 0x32);
             if (it < 8) DTF_MARK(88 + it);
             mbar_wait(smem_u32(&hdr->full[st]), (it / kHStages) & 1, 0x33);
             tc_fence_after_sync();
             if (it < 4) DTF_MARK(8 + it);
             if (it < 8) DTF_MARK(96 + it);
-            const uint64_t adesc_st = adesc0 + st * stage_units;
+            const uint32_t a_lo_st = a_lo0 + st * stage_units;
             const uint32_t d_tmem = tmem_base + a * N;
             if (elect_one()) {
+                umma_bf16_lohi<false>(d_tmem, a_lo_st + a_tap[0], a_hi, b_lo0, b_hi, idesc);
 #pragma unroll
                 for (int tap = 0; tap < 9; ++tap)
 #pragma unroll
                     for (int kp = 0; kp < kPairs; ++kp)
-                        umma_bf16(d_tmem, adesc_st + (a_tap[tap] + kp * a_pair), bdesc0 + (tap * b_tap + kp * b_pair), idesc,
-                                  (tap | kp) != 0);
+                        if ((tap | kp) != 0)
+                            umma_bf16_lohi<true>(d_tmem, a_lo_st + (a_tap[tap] + kp * a_pair), a_hi,
+                                                 b_lo0 + (tap * b_tap + kp * b_pair), b_hi, idesc);
                 umma_commit(smem_u32(&hdr->empty[st]));
                 umma_commit(smem_u32(&hdr->acc_full[a]));
             }
@@ -328,7 +336,7 @@ DTF_DEVINL void conv3x3_body(const DtfConvGemm& P, const HaloGeom& G, const int 
                              ? ldg16(aux_src + static_cast<size_t>(pix_nxt) * N + g0 * 16 + j * 8)
                              : make_uint4(0, 0, 0, 0);
         for (int it = t_first; it < my_tiles; it += t_step) {
-            const uint32_t a = it & 1;
+            const uint32_t a = it % kHAcc;
             const bool valid = valid_nxt;
             const size_t obase = static_cast<size_t>(pix_nxt) * N;
             uint4 aux[2 * kGPS];
@@ -344,7 +352,7 @@ DTF_DEVINL void conv3x3_body(const DtfConvGemm& P, const HaloGeom& G, const int 
                                      : make_uint4(0, 0, 0, 0);
             }
             if (tid == 0 && it < 8) DTF_MARK(112 + it);
-            mbar_wait(smem_u32(&hdr->acc_full[a]), (it >> 1) & 1, 0x35);
+            mbar_wait(smem_u32(&hdr->acc_full[a]), (it / kHAcc) & 1, 0x35);
             tc_fence_after_sync();
             if (tid == 0 && it < 8) DTF_MARK(32 + it);
 #pragma unroll
