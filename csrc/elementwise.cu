@@ -67,6 +67,125 @@ bn_bwd_apply_kernel(const dtf_bf16* __restrict__ t, const dtf_bf16* __restrict__
 }
 
 // ---------------------------------------------------------------------------------------
+// ResNet v1 (post-activation) block tail, forward:  y = relu( bn(x) + shortcut )
+//   shortcut = none | sc (identity, already activated) | bn_sc(sc) (projection: conv + BN, resnet_model.py:127-168)
+// CTA 0 also updates the moving averages of the BatchNorm layers it applies (training).
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+bn_act_apply_kernel(const dtf_bf16* __restrict__ x, DtfBnRef bn, const dtf_bf16* __restrict__ sc, DtfBnRef bn_sc,
+                    int sc_mode, dtf_bf16* __restrict__ out, long long total_vec, int C, int update_running) {
+    griddep_launch_dependents();
+    griddep_wait();
+    __shared__ float a0[256], a1[256], b0[256], b1[256];
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+        float mean, invstd;
+        bn_consts(bn, c, a0[c], a1[c], mean, invstd);
+        b0[c] = 1.f; b1[c] = 0.f;
+        if (sc_mode == 2) bn_consts(bn_sc, c, b0[c], b1[c], mean, invstd);
+    }
+    if (blockIdx.x == 0 && update_running) {
+        for (int which = 0; which < (sc_mode == 2 ? 2 : 1); ++which) {
+            const DtfBnRef& B = which == 0 ? bn : bn_sc;
+            if (B.use_running) continue;
+            const float m = 1.f / B.inv_count;
+            const float unbias = m > 1.f ? m / (m - 1.f) : 1.f;
+            for (int c = threadIdx.x; c < C; c += blockDim.x) {
+                const float mean = B.stats[c] * B.inv_count;
+                const float var = fmaxf(B.stats[C + c] * B.inv_count - mean * mean, 0.f);
+                B.run_mean[c] = B.decay * B.run_mean[c] + (1.f - B.decay) * mean;
+                B.run_var[c] = B.decay * B.run_var[c] + (1.f - B.decay) * var * unbias;
+            }
+        }
+    }
+    __syncthreads();
+    const int cvec = C / 8;
+    for (long long v = blockIdx.x * (long long)blockDim.x + threadIdx.x; v < total_vec;
+         v += (long long)gridDim.x * blockDim.x) {
+        const int cb = static_cast<int>(v % cvec) * 8;
+        float fx[8], fs[8];
+        unpack8(ldg16(x + v * 8), fx);
+        if (sc_mode != 0) unpack8(ldg16(sc + v * 8), fs);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            float y = fmaf(fx[i], a0[cb + i], a1[cb + i]);
+            if (sc_mode != 0) y += fmaf(fs[i], b0[cb + i], b1[cb + i]);
+            fx[i] = fmaxf(y, 0.f);
+        }
+        *reinterpret_cast<uint4*>(out + v * 8) = pack8(fx);
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// ResNet v1 block tail, backward:  t = dy * (y > 0), written out, plus the BatchNorm-backward sums of the
+// layer(s) that fed the tail:  stats[0..C) += sum t,  stats[C..2C) += sum t * xhat(x)  (= dbeta, dgamma), and the
+// same against the projection's BatchNorm input when there is one.  The convolutions upstream then apply the
+// BN-backward combination in their operand gather (DTF_PRO_BN_BWD), exactly as in the v2 blocks.
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+relu_bwd_stats_kernel(const dtf_bf16* __restrict__ dy, const dtf_bf16* __restrict__ y, dtf_bf16* __restrict__ t_out,
+                      const dtf_bf16* __restrict__ x, DtfBnRef bn, float* __restrict__ stats,
+                      const dtf_bf16* __restrict__ x2, DtfBnRef bn2, float* __restrict__ stats2,
+                      long long total_vec, int C) {
+    griddep_launch_dependents();
+    griddep_wait();
+    __shared__ float m1[256], i1[256], m2[256], i2[256];
+    __shared__ float acc[4][256];
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+        float sc_, sh_;
+        bn_consts(bn, c, sc_, sh_, m1[c], i1[c]);
+        if (x2 != nullptr) bn_consts(bn2, c, sc_, sh_, m2[c], i2[c]);
+        acc[0][c] = acc[1][c] = acc[2][c] = acc[3][c] = 0.f;
+    }
+    __syncthreads();
+    const int cvec = C / 8;
+    // a thread keeps the same 8 channels for all its vectors when the stride is a multiple of cvec
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    const bool fixed = (stride % cvec) == 0;
+    float s[4][8];
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+#pragma unroll
+        for (int i = 0; i < 8; ++i) s[k][i] = 0.f;
+    int cb_fixed = 0;
+    for (long long v = blockIdx.x * (long long)blockDim.x + threadIdx.x; v < total_vec; v += stride) {
+        const int cb = static_cast<int>(v % cvec) * 8;
+        cb_fixed = cb;
+        float g[8], fy[8], fx[8], fx2[8];
+        unpack8(ldg16(dy + v * 8), g);
+        unpack8(ldg16(y + v * 8), fy);
+        unpack8(ldg16(x + v * 8), fx);
+        if (x2 != nullptr) unpack8(ldg16(x2 + v * 8), fx2);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const float t = fy[i] > 0.f ? g[i] : 0.f;
+            g[i] = t;
+            const float h1 = t * (fx[i] - m1[cb + i]) * i1[cb + i];
+            const float h2 = x2 != nullptr ? t * (fx2[i] - m2[cb + i]) * i2[cb + i] : 0.f;
+            if (fixed) { s[0][i] += t; s[1][i] += h1; s[2][i] += h2; }
+            else {
+                atomicAdd(&acc[0][cb + i], t); atomicAdd(&acc[1][cb + i], h1);
+                if (x2 != nullptr) atomicAdd(&acc[2][cb + i], h2);
+            }
+        }
+        *reinterpret_cast<uint4*>(t_out + v * 8) = pack8(g);
+    }
+    if (fixed) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            atomicAdd(&acc[0][cb_fixed + i], s[0][i]);
+            atomicAdd(&acc[1][cb_fixed + i], s[1][i]);
+            if (x2 != nullptr) atomicAdd(&acc[2][cb_fixed + i], s[2][i]);
+        }
+    }
+    __syncthreads();
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+        atomicAdd(stats + c, acc[0][c]);
+        atomicAdd(stats + C + c, acc[1][c]);
+        if (x2 != nullptr) { atomicAdd(stats2 + c, acc[0][c]); atomicAdd(stats2 + C + c, acc[2][c]); }
+    }
+}
+
+// ---------------------------------------------------------------------------------------
 // classifier head: one CTA per image
 // ---------------------------------------------------------------------------------------
 constexpr int kHeadThreads = 256;
@@ -419,6 +538,36 @@ extern "C" int dtf_bn_bwd_apply(const dtf_bf16* t, const dtf_bf16* x, const dtf_
     long long blocks = (total_vec + 255) / 256;
     if (blocks > 148 * 8) blocks = 148 * 8;
     dtf_launch(dtf::bn_bwd_apply_kernel, dim3(static_cast<int>(blocks)), dim3(256), 0, stream, t, x, res, out, *bn, bwd_stats, total_vec, C);
+    return DTF_CHECK_LAUNCH();
+}
+
+extern "C" int dtf_bn_act_apply(const dtf_bf16* x, const DtfBnRef* bn, const dtf_bf16* sc, const DtfBnRef* bn_sc,
+                                dtf_bf16* out, long long pixels, int C, int update_running, cudaStream_t stream) {
+    if (C % 8 != 0 || C > 256 || bn == nullptr) return DTF_ERR_SHAPE;
+    const long long total_vec = pixels * (C / 8);
+    long long blocks = (total_vec + 255) / 256;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    const int sc_mode = sc == nullptr ? 0 : (bn_sc == nullptr ? 1 : 2);
+    DtfBnRef none = {};
+    dtf_launch(dtf::bn_act_apply_kernel, dim3(static_cast<int>(blocks)), dim3(256), 0, stream, x, *bn, sc,
+               bn_sc ? *bn_sc : none, sc_mode, out, total_vec, C, update_running);
+    return DTF_CHECK_LAUNCH();
+}
+
+extern "C" int dtf_relu_bwd_stats(const dtf_bf16* dy, const dtf_bf16* y, dtf_bf16* t_out, const dtf_bf16* x,
+                                  const DtfBnRef* bn, float* stats, const dtf_bf16* x2, const DtfBnRef* bn2,
+                                  float* stats2, long long pixels, int C, cudaStream_t stream) {
+    if (C % 8 != 0 || C > 256 || bn == nullptr || stats == nullptr) return DTF_ERR_SHAPE;
+    if (x2 != nullptr && (bn2 == nullptr || stats2 == nullptr)) return DTF_ERR_ARG;
+    const long long total_vec = pixels * (C / 8);
+    const int cvec = C / 8;
+    long long blocks = (total_vec + 255) / 256;
+    if (blocks > 148 * 4) blocks = 148 * 4;
+    // keep the grid stride a multiple of the channel-vector count: each thread then owns fixed channels
+    while (blocks > 1 && (blocks * 256) % cvec != 0) --blocks;
+    DtfBnRef none = {};
+    dtf_launch(dtf::relu_bwd_stats_kernel, dim3(static_cast<int>(blocks)), dim3(256), 0, stream, dy, y, t_out, x, *bn,
+               stats, x2, bn2 ? *bn2 : none, stats2, total_vec, C);
     return DTF_CHECK_LAUNCH();
 }
 

@@ -46,13 +46,16 @@ class Cifar10Model(GpuMember):
         seed = 7919 * (self.cluster_id + 1)
         if self.engine_kind == "native":
             from .resnet_native import NativeResNetEngine
+            from .resnet_native_v1 import NativeResNetV1Engine
+            cls = NativeResNetEngine if self.net_cfg.resnet_version == 2 else NativeResNetV1Engine
             try:
-                return NativeResNetEngine(self.net_cfg, self.hparams, self.device, seed=seed, dtype=self.dtype,
-                                          arena_alloc=self.make_symmetric_alloc,
-                                          dp_group=self.dp_group if self.dp_size > 1 else None,
-                                          all_reduce_alg=self.all_reduce_alg if self.dp_size > 1 else None)
+                return cls(self.net_cfg, self.hparams, self.device, seed=seed, dtype=self.dtype,
+                           loss_scale=self.loss_scale,
+                           arena_alloc=self.make_symmetric_alloc,
+                           dp_group=self.dp_group if self.dp_size > 1 else None,
+                           all_reduce_alg=self.all_reduce_alg if self.dp_size > 1 else None)
             except NotImplementedError:
-                # ResNet v1 / bottleneck / fp16 are served by the eager engine; an explicit request for
+                # bottleneck blocks and fp32 / tf32 are served by the eager engine; an explicit request for
                 # the native engine is an error, `auto` degrades.
                 if self._engine_requested == "native":
                     raise

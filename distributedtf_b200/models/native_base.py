@@ -91,6 +91,9 @@ class NativeEngineBase:
         self._count = 0
         self._side = None                       # side stream for independent kernels (engine-specific use)
         self.board_slot_ptr = 0                 # this member's score-board slot (device / peer pointer), 0 = none
+        # static loss scale (reference resnet_run_loop.py:284-294): the head kernel multiplies d(loss)/d(logits) by it,
+        # the optimizer / all-reduce kernel multiplies the gradients by 1 / scale (DtfHparams.inv_loss_scale)
+        self.loss_scale = 1.0
         self._src = None                        # (images_all, labels_all) while an indexed step is being issued
         self._idx_buf = None
 
@@ -173,7 +176,7 @@ class NativeEngineBase:
         h.momentum = float(oc.get("momentum", 0.0))
         h.grad_decay = float(oc.get("grad_decay", 0.9))
         h.weight_decay = float(hp.get("weight_decay", 0.0))
-        h.inv_loss_scale = 1.0
+        h.inv_loss_scale = 1.0 / float(getattr(self, "loss_scale", 1.0) or 1.0)
         bounds, values = self.lr_schedule(hp)
         if len(bounds) > native.MAX_LR_BOUNDARIES:
             raise ValueError("LR schedule has too many boundaries for the device block")

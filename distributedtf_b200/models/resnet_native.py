@@ -77,16 +77,23 @@ class Block:
 
 
 class NativeResNetEngine(NativeEngineBase):
+    version = 2
 
     def __init__(self, cfg: resnet.ResNetConfig, hparams: Dict[str, Any], device, *, seed: int = 0,
                  dtype: str = "bf16", max_batch: int = MAX_BATCH, use_graphs: bool = True,
-                 arena_alloc=None, dp_group=None, all_reduce_alg=None):
-        if cfg.resnet_version != 2 or cfg.bottleneck or cfg.first_pool_size:
-            raise NotImplementedError("native engine covers the CIFAR configuration: ResNet v2, building blocks")
-        if dtype != "bf16":
-            raise NotImplementedError("native engine computes in bf16 with fp32 master weights / accumulation")
+                 arena_alloc=None, dp_group=None, all_reduce_alg=None, loss_scale: Optional[float] = None):
+        if cfg.resnet_version != self.version or cfg.bottleneck or cfg.first_pool_size:
+            raise NotImplementedError("native engines cover the CIFAR configuration: building blocks, v1 or v2")
+        if dtype not in ("bf16", "fp16"):
+            raise NotImplementedError("native engine computes with 16-bit operands, fp32 accumulation and fp32 master "
+                                      "weights; fp32 / tf32 runs on the eager engine")
         super().__init__(device, max_batch=max_batch, use_graphs=use_graphs, arena_alloc=arena_alloc,
                          dp_group=dp_group, seed=seed, all_reduce_alg=all_reduce_alg)
+        # dtype "fp16" = the reference's mixed-precision mode (fp32 master weights, static loss scale 128,
+        # resnet_model.py:439-474): on B200 the 16-bit operand type is bf16 (same tensor-core rate, fp32's exponent
+        # range), the loss scaling is applied exactly as specified.
+        self.compute_dtype = "bf16"
+        self.loss_scale = float(loss_scale) if loss_scale else (128.0 if dtype == "fp16" else 1.0)
         self.cfg = cfg
         self.image_size, self.image_channels = cfg.image_size, cfg.in_channels
         self._build_plan()
@@ -317,7 +324,7 @@ class NativeResNetEngine(NativeEngineBase):
         h.db = self.grads[self.dense_b_off:].data_ptr()
         h.t_out = t_out.data_ptr() if t_out is not None else 0
         h.bwd_stats_out = self._bwd_stats(b).data_ptr()
-        h.loss_scale = 1.0
+        h.loss_scale = float(self.loss_scale)
         h.batch, h.HW, h.C, h.classes = nb, b.h * b.h, b.c, self.cfg.num_classes
         h.has_bn, h.training, h.update_running = 1, int(training), int(training)
         h.board_hits = 0 if training else self.board_slot_ptr     # evaluation hits go straight to the score board

@@ -136,6 +136,10 @@ def _declare(l: C.CDLL) -> None:
     l.dtf_conv_bwd.restype = i
     l.dtf_bn_bwd_apply.argtypes = [vp, vp, vp, vp, C.POINTER(BnRef), vp, ll, i, vp]
     l.dtf_head.argtypes = [C.POINTER(Head), vp]
+    l.dtf_bn_act_apply.argtypes = [vp, C.POINTER(BnRef), vp, C.POINTER(BnRef), vp, ll, i, i, vp]
+    l.dtf_bn_act_apply.restype = i
+    l.dtf_relu_bwd_stats.argtypes = [vp, vp, vp, vp, C.POINTER(BnRef), vp, vp, C.POINTER(BnRef), vp, ll, i, vp]
+    l.dtf_relu_bwd_stats.restype = i
     l.dtf_pack_weights.argtypes = [vp, vp, vp, vp, i, vp]
     l.dtf_optimizer_step.argtypes = [vp, vp, vp, vp, vp, vp, vp, i, vp, vp, f, vp]
     l.dtf_step_begin.argtypes = [vp, ll, vp, i, vp]
@@ -253,6 +257,21 @@ def conv_wgrad(x: Gather, gy: Gather, dw: torch.Tensor, *, NB: int, Ho: int, Wo:
 def bn_bwd_apply(t, x, res, out, bn: BnRef, bwd_stats, pixels: int, channels: int) -> None:
     check(lib().dtf_bn_bwd_apply(ptr(t), ptr(x), ptr(res), ptr(out), C.byref(bn), ptr(bwd_stats),
                                  pixels, channels, stream_ptr()), "dtf_bn_bwd_apply")
+
+
+def bn_act_apply(x, bn: BnRef, out, pixels: int, channels: int, *, sc=None, bn_sc: Optional[BnRef] = None,
+                 update_running: bool = False) -> None:
+    """ResNet v1 block tail: out = relu(bn(x) + shortcut); shortcut = none | sc | bn_sc(sc)."""
+    check(lib().dtf_bn_act_apply(ptr(x), C.byref(bn), ptr(sc), C.byref(bn_sc) if bn_sc is not None else None, ptr(out),
+                                 pixels, channels, int(update_running), stream_ptr()), "dtf_bn_act_apply")
+
+
+def relu_bwd_stats(dy, y, t_out, x, bn: BnRef, stats, pixels: int, channels: int, *, x2=None,
+                   bn2: Optional[BnRef] = None, stats2=None) -> None:
+    """Backward of the v1 block tail: t = dy * (y > 0) plus the BN-backward sums against x (and x2)."""
+    check(lib().dtf_relu_bwd_stats(ptr(dy), ptr(y), ptr(t_out), ptr(x), C.byref(bn), ptr(stats), ptr(x2),
+                                   C.byref(bn2) if bn2 is not None else None, ptr(stats2), pixels, channels,
+                                   stream_ptr()), "dtf_relu_bwd_stats")
 
 
 def head(p: Head) -> None:

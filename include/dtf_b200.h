@@ -155,6 +155,16 @@ typedef struct {
 int dtf_bn_bwd_apply(const dtf_bf16* t, const dtf_bf16* x, const dtf_bf16* res, dtf_bf16* out,
                      const DtfBnRef* bn, const float* bwd_stats, long long pixels, int C, cudaStream_t stream);
 int dtf_head(const DtfHead* p, cudaStream_t stream);
+/* ResNet v1 (post-activation) block tail (resnet_model.py:127-168, 215-264): out = relu(bn(x) + shortcut) with
+ * shortcut = none (sc NULL) | sc (bn_sc NULL: identity) | bn_sc(sc) (projection conv followed by its own BN);
+ * update_running: the launch also moves the moving averages of the BN layer(s) it applies. */
+int dtf_bn_act_apply(const dtf_bf16* x, const DtfBnRef* bn, const dtf_bf16* sc, const DtfBnRef* bn_sc, dtf_bf16* out,
+                     long long pixels, int C, int update_running, cudaStream_t stream);
+/* Backward of that tail: t_out = dy * (y > 0); stats[0..C) += sum t, stats[C..2C) += sum t * xhat(x; bn)
+ * (= dbeta, dgamma of bn); the same into stats2 against (x2, bn2) when the block has a projection. */
+int dtf_relu_bwd_stats(const dtf_bf16* dy, const dtf_bf16* y, dtf_bf16* t_out, const dtf_bf16* x, const DtfBnRef* bn,
+                       float* stats, const dtf_bf16* x2, const DtfBnRef* bn2, float* stats2, long long pixels, int C,
+                       cudaStream_t stream);
 /* chunks: n_chunks x {segment index, first element} pairs; each CTA handles DTF_OPT_CHUNK elements */
 int dtf_pack_weights(const float* params, dtf_bf16* pack, const DtfOptSegment* segs, const int* chunks,
                      int n_chunks, cudaStream_t stream);
