@@ -49,6 +49,13 @@ def parse():
     p.add_argument("--resnet-size", type=int, default=32)
     p.add_argument("--dp-size", type=int, default=1, choices=[1, 2, 4],
                    help="GPUs per member (BASELINE config 4: population N/D x data-parallel D)")
+    p.add_argument("--mode", choices=["step", "pbt"], default="step",
+                   help="step = bare training steps (+ one PBT event); pbt = a whole PBT run through launch.run "
+                        "(master, workers, control plane, evaluation, score board, exploit, explore, checkpoints)")
+    p.add_argument("--model", choices=["cifar10", "mnist"], default="cifar10", help="--mode pbt: member model")
+    p.add_argument("--rounds", type=int, default=6, help="--mode pbt: timed rounds (one more runs first as warm-up)")
+    p.add_argument("--steps-per-round", type=int, default=100, help="--mode pbt: training steps per member per round")
+    p.add_argument("--eval-batches", type=int, default=8, help="--mode pbt: evaluation batches per member per round")
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--no-graphs", action="store_true")
     return p.parse_args()
@@ -137,9 +144,88 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm), "source": "nvidia-smi"}
 
 
+# --------------------------------------------------------------------------- whole PBT runs
+def pbt_mode(args) -> int:
+    """BASELINE configs 2-4 through the product: `launch.spawn_tcp` starts one worker process per member GPU group
+    (N / dp-size members), the master ranks from the device score board, losers pull winners over NVLink, every
+    member evaluates each round and writes its checkpoint at the end.  One warm-up round (graph capture, peer
+    mappings) runs before the timed rounds.  `value` is device-timed: images trained in the timed rounds divided by
+    the slowest worker's train + eval + exploit device time; `wall` is the master's wall clock for the same rounds
+    (control plane, host bookkeeping and CSV / checkpoint hand-over included)."""
+    import tempfile
+    import torch
+    from distributedtf_b200 import launch
+    from distributedtf_b200.config import RunConfig
+    from distributedtf_b200.hpspace import default_cifar_hparam
+    D = args.dp_size
+    members = max(args.gpus // D, 1)
+    tmp = tempfile.mkdtemp(prefix="dtf_pbt_bench_")
+    hp = default_cifar_hparam()
+    hp["batch_size"] = args.batch
+    if args.model == "mnist":
+        hp = {"opt_case": {"optimizer": "Momentum", "lr": 1e-4, "momentum": 0.9}, "batch_size": args.batch,
+              "initializer": "glorot_normal", "decay_steps": 0, "decay_rate": 1.0, "weight_decay": 0.0,
+              "regularizer": "None"}
+    import json as _json
+    hp_file = os.path.join(tmp, "initial_hp.json")
+    with open(hp_file, "w") as f:
+        _json.dump([{"model_id": i, "accuracy": 0.0, "hparams": hp} for i in range(members)], f)
+    cfg = RunConfig(target_model=args.model, population_size=members, train_round=args.rounds + 1,
+                    epochs_per_round=1, workers=members, transport="tcp" if args.gpus > 1 else "local", master_port=0,
+                    dp_size=D, exploit_path="p2p", engine="native", resnet_size=args.resnet_size,
+                    max_train_steps=args.steps_per_round, eval_batches=args.eval_batches, checkpoint_every=0,
+                    save_root=os.path.join(tmp, "savedata"), results_file=os.path.join(tmp, "res.txt"),
+                    initial_hp=hp_file, verbose=False, seed=1, hooks=[], recv_timeout=600.0).validate()
+    timed = {}
+    orig_train = launch.PBTCluster.train
+
+    def train_with_warmup(self, round_num):
+        """Round 0 untimed (graph capture, peer mappings, first checkpoints of nothing), then the timed rounds."""
+        orig_train(self, 1)
+        before = self.profiling_info()
+        t0 = time.time()
+        out = orig_train(self, round_num - 1)
+        timed["wall"] = time.time() - t0
+        after = self.profiling_info()
+        timed["phases"] = {k: after[k] - before.get(k, 0.0) for k in after if k.startswith("device_") or k in
+                           ("train", "explore", "exploit", "gather_wait")}
+        timed["history"] = len(self.history)
+        timed["fallbacks"] = self.board_fallbacks
+        return out
+    launch.PBTCluster.train = train_with_warmup
+    sampler = ClockSampler(0)
+    sampler.start()
+    try:
+        out = launch.run(cfg)
+    finally:
+        launch.PBTCluster.train = orig_train
+    clocks = sampler.stop()
+    ph = timed["phases"]
+    images = members * args.rounds * args.steps_per_round * args.batch
+    dev_s = ph.get("device_train_max", 0.0) + ph.get("device_eval_max", 0.0) + ph.get("device_exploit_max", 0.0)
+    res = {"metric": METRIC if args.model == "cifar10" else "MNIST deep CNN PBT images/sec (box, max over ranks)",
+           "value": images / max(dev_s, 1e-9), "unit": "images/s", "n_gpus": args.gpus, "steps": args.rounds * args.steps_per_round,
+           "warmup": args.steps_per_round, "ms_per_step": dev_s / (args.rounds * args.steps_per_round) * 1e3,
+           "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "impl": "native", "mode": "pbt",
+           "data": "synthetic uint8 images of the dataset's shape (random), random labels, random-init weights",
+           "config": {"model": f"CIFAR-10 ResNet-{args.resnet_size} v2" if args.model == "cifar10" else "MNIST deep CNN",
+                      "global_batch": args.batch * members, "per_gpu_batch": args.batch // D, "seq_len": None,
+                      "parallelism": f"population {members} x {D} GPU, master + {members} workers over TCP, "
+                                     f"p2p exploit, device score board",
+                      "rounds": args.rounds, "steps_per_round": args.steps_per_round, "eval_batches": args.eval_batches,
+                      "what_is_timed": "train + eval + exploit device time of the slowest worker over the timed rounds"},
+           "wall": {"seconds": timed["wall"], "images_per_s": images / max(timed["wall"], 1e-9)},
+           "phases_s": ph, "exploit_events": timed["history"], "board_fallbacks": timed["fallbacks"],
+           "pop_size_end": out["pop_size"], "clocks": clocks}
+    print(json.dumps(res))
+    return 0
+
+
 # --------------------------------------------------------------------------- main
 def main():
     args = parse()
+    if args.mode == "pbt" and args.impl == "native":
+        return pbt_mode(args)
     if args.impl == "reference":
         # The reference cannot be installed or run here: it has no packaging files at all and needs
         # TensorFlow 1.x + mpi4py + hyperopt (none in the image, no network).  See DESIGN.md.

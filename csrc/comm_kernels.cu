@@ -181,9 +181,12 @@ allreduce_update_kernel(const __grid_constant__ DtfAllreduceUpdate P) {
         __threadfence_system();
         st_release_sys(P.peer_ready[threadIdx.x] + P.rank, epoch);     // my slot in peer's ready[]
     }
+    uint64_t t_begin = 0, t_ready = 0, t_loaded = 0;
+    if (P.timing != nullptr && blockIdx.x == 0 && threadIdx.x == 0) t_begin = globaltimer_ns();
     if (threadIdx.x == 0) hp = *P.hp;
     if (threadIdx.x < W) wait_flag_ge(P.local_ready + threadIdx.x, epoch, 1);
     __syncthreads();
+    if (P.timing != nullptr && blockIdx.x == 0 && threadIdx.x == 0) t_ready = globaltimer_ns();
     const float lr = schedule_lr2(hp, step - 1);
     float lr_adam = lr;
     if (hp.optimizer == DTF_OPT_ADAM) {
@@ -193,14 +196,30 @@ allreduce_update_kernel(const __grid_constant__ DtfAllreduceUpdate P) {
     const int2 ch = reinterpret_cast<const int2*>(P.chunks)[blockIdx.x];
     const DtfOptSegment s = P.segs[ch.x];
     const float gs = P.grad_scale * hp.inv_loss_scale;
-    for (int i = threadIdx.x; i < DTF_OPT_CHUNK; i += blockDim.x) {
-        const int local = ch.y + i;
+    // One-shot: every rank reads all replicas.  A thread owns four consecutive elements so that the remote reads
+    // are 16-byte loads over NVLink (a chunk is 1024 elements = 256 threads x 4); segment offsets are multiples of
+    // four elements, only a segment's last few elements fall back to scalar loads.
+    const int local0 = ch.y + 4 * static_cast<int>(threadIdx.x);
+    const bool vec = ((s.offset | ch.y) & 3) == 0 && local0 + 3 < s.count;
+    float gsum[4] = {0.f, 0.f, 0.f, 0.f};
+    if (vec) {
+#pragma unroll 4
+        for (int w = 0; w < W; ++w) {
+            const float4 r = *reinterpret_cast<const float4*>(P.peer_grads[w] + s.offset + local0);
+            gsum[0] += r.x; gsum[1] += r.y; gsum[2] += r.z; gsum[3] += r.w;
+        }
+    } else {
+        for (int e = 0; e < 4; ++e)
+            if (local0 + e < s.count)
+                for (int w = 0; w < W; ++w) gsum[e] += P.peer_grads[w][s.offset + local0 + e];
+    }
+    if (P.timing != nullptr && blockIdx.x == 0 && threadIdx.x == 0) t_loaded = globaltimer_ns();
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+        const int local = local0 + e;
         if (local >= s.count) break;
         const int idx = s.offset + local;
-        float g = 0.f;
-#pragma unroll 4
-        for (int w = 0; w < W; ++w) g += P.peer_grads[w][idx];        // one-shot: every rank reads all replicas
-        g *= gs;
+        float g = gsum[e] * gs;
         const float w0 = P.params[idx];
         if (s.regularized) {
             if (hp.regularizer == DTF_REG_L1 || hp.regularizer == DTF_REG_L1_L2)
@@ -233,6 +252,16 @@ allreduce_update_kernel(const __grid_constant__ DtfAllreduceUpdate P) {
         P.slot0[idx] = s0;
         P.slot1[idx] = s1;
         if (s.pack) pack_store2(s, P.pack, local, nw);
+    }
+    // device-timestamped accounting of the exchange (CTA 0): time blocked on the peers' ready flags (= exposed
+    // communication: it is zero when every replica's backward finished together), time of the remote loads, and the
+    // whole kernel -- accumulated in nanoseconds, read back by parallel/dp.py
+    if (P.timing != nullptr && blockIdx.x == 0 && threadIdx.x == 0) {
+        const uint64_t t_end = globaltimer_ns();
+        atomicAdd(P.timing + 0, static_cast<unsigned long long>(t_ready - t_begin));
+        atomicAdd(P.timing + 1, static_cast<unsigned long long>(t_loaded - t_ready));
+        atomicAdd(P.timing + 2, static_cast<unsigned long long>(t_end - t_begin));
+        atomicAdd(P.timing + 3, 1ull);
     }
     // ---- exit signal: once every CTA of this rank has consumed the peers' gradients, tell the peers
     // that their gradient arenas may be zeroed for the next step (checked by dtf_dp_step_begin)

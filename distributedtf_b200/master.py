@@ -38,6 +38,7 @@ import time
 from typing import Any, Callable, Dict, List, Optional, Sequence
 
 from . import ckpt, protocol, report
+from .utils import nvtx
 from .hpspace import generate_random_hparam
 from .protocol import WorkerInstruction
 
@@ -164,7 +165,8 @@ class PBTCluster:
                 self._broadcast(protocol.train(self.epochs_per_round, self.epochs_per_round * round_num))
             train_sent_ahead = False
             if self.do_exploit:
-                self.exploit()
+                with nvtx.range(f"master exploit round {rnd}"):
+                    self.exploit()
             if self.do_explore:
                 self.explore()
             if self.board_mode:
@@ -296,6 +298,7 @@ class PBTCluster:
         extra = [v[2] for v in vals if len(v) > 2 and isinstance(v[2], dict)]
         for key in sorted({k for e in extra for k in e}):
             out["device_" + key] = sum(e.get(key, 0.0) for e in extra) / max(len(extra), 1)
+            out["device_" + key + "_max"] = max(e.get(key, 0.0) for e in extra)      # slowest worker
         return out
 
     def print_profiling_info(self) -> Dict[str, float]:

@@ -17,6 +17,7 @@ from typing import Any, Dict, List, Optional
 import torch
 
 from .. import ckpt, report
+from ..utils import nvtx
 from ..model_base import ModelBase
 from ..utils.data import BatchIterator, Dataset
 
@@ -178,7 +179,7 @@ class GpuMember(ModelBase):
         steps = self.steps_per_epoch()
         if self.max_train_steps is not None:
             steps = min(steps, self.max_train_steps)
-        with self._timed("train"):
+        with nvtx.range(f"train epoch member {self.cluster_id}"), self._timed("train"):
             t0 = time.time()
             for _ in range(steps):
                 idx = self._train_iter.next_indices()
@@ -248,7 +249,7 @@ class GpuMember(ModelBase):
         board = self._board_pointer() if self.dp_rank == 0 else None
         direct = board is not None and getattr(self.engine, "board_slot_ptr", 0) != 0
         epoch = self.rounds_trained + 1
-        with self._timed("eval"):
+        with nvtx.range(f"evaluate member {self.cluster_id}"), self._timed("eval"):
             if direct:
                 sb.reset(board, self.cluster_id)
             for b, idx in enumerate(it.epoch_batches()):
@@ -425,7 +426,7 @@ class GpuMember(ModelBase):
         if extras is None:
             return
         from ..parallel import exploit
-        with self._timed("exploit"):
+        with nvtx.range(f"exploit member {self.cluster_id} <- {extras.get('src_id')}"), self._timed("exploit"):
             if extras.get("path") == "p2p" and hasattr(self.engine, "hparams_struct"):
                 new_hp = self.engine.hparams_struct(self.hparams)
                 exploit.receive(self, extras, new_hp=new_hp)
@@ -442,6 +443,7 @@ class GpuMember(ModelBase):
             ckpt.async_writer().wait(t)
 
     def save(self) -> None:
+        nvtx.mark(f"checkpoint member {self.cluster_id}")
         self.flush_exploit()
         meta = {"model": type(self).__name__, "engine": self.engine_kind, "epoches_trained": self.epoches_trained}
         if self.async_checkpoint and self.device.type == "cuda" and hasattr(self.engine, "state"):

@@ -36,7 +36,7 @@ class AllreduceUpdate(C.Structure):
                 ("peer_grads", vp * MAX_DP), ("peer_ready", vp * MAX_DP), ("peer_done", vp * MAX_DP),
                 ("local_ready", vp), ("segs", vp), ("chunks", vp), ("hp", vp), ("step", vp),
                 ("arrive_counter", vp), ("epoch_ctr", vp), ("epoch", ull), ("grad_scale", f32),
-                ("world", i32), ("rank", i32), ("n_chunks", i32)]
+                ("world", i32), ("rank", i32), ("n_chunks", i32), ("timing", vp)]
 
 
 native_ext.register("dtf_allreduce_update", [C.POINTER(AllreduceUpdate), vp])
@@ -101,6 +101,19 @@ class DataParallelGroup:
         return self.flag_buf.ptr + 16 * MAX_DP + 64
 
     @property
+    def timing_ptr(self) -> int:
+        """Four u64 cells the all-reduce kernel accumulates its own device-side clock readings into."""
+        return self.flag_buf.ptr + 16 * MAX_DP + 192
+
+    def comm_stats(self) -> dict:
+        """Device-timestamped accounting of the fused exchange since the group was built: time blocked on the
+        peers' ready flags (the exposed communication), time of the remote gradient loads, kernel time."""
+        cells = self.flag_buf.tensor[16 * MAX_DP + 192: 16 * MAX_DP + 224].view(torch.int64).tolist()
+        calls = max(cells[3], 1)
+        return {"calls": cells[3], "wait_us_per_call": cells[0] / calls / 1e3, "load_us_per_call": cells[1] / calls / 1e3,
+                "kernel_us_per_call": cells[2] / calls / 1e3}
+
+    @property
     def epoch_ctr_ptr(self) -> int:
         """Exchange counter of this replica: counts ``step_begin`` launches since the group was built.  It is
         deliberately not the member's step counter, which exploit and restore overwrite (members run different
@@ -129,6 +142,7 @@ class DataParallelGroup:
         p.epoch = 0
         p.grad_scale = 1.0 / self.world
         p.world, p.rank, p.n_chunks = self.world, self.rank, n_chunks
+        p.timing = self.timing_ptr
         native.check(native.lib().dtf_allreduce_update(C.byref(p), native.stream_ptr()), "dtf_allreduce_update")
 
 

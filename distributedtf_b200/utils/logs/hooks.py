@@ -119,24 +119,56 @@ class LoggingMetricHook(Hook):
 
 class ProfilerHook(Hook):
     """Chrome-trace timeline (one complete event per step) written to ``model_dir/timeline-<step>.json``
-    every ``save_steps`` — the role of ``tf.train.ProfilerHook`` in the reference."""
+    every ``save_steps`` — the role of ``tf.train.ProfilerHook`` in the reference.  On a CUDA device the step
+    durations are DEVICE times: one CUDA event is recorded on the member's stream after every step and the gaps
+    between consecutive events are read when the trace is written (no synchronisation in between); on the CPU they
+    are host times."""
 
     def __init__(self, model_dir: str, save_steps: int = 1000):
         self._dir, self._save_steps = model_dir, save_steps
         self._events: List[Dict[str, Any]] = []
         self._t_prev: Optional[float] = None
+        self._cuda_events: List[Any] = []          # (step, host time, cuda event)
+
+    @staticmethod
+    def _cuda_live() -> bool:
+        try:
+            import torch
+            return torch.cuda.is_available() and torch.cuda.is_initialized()
+        except Exception:
+            return False
 
     def after_step(self, step: int, values: Dict[str, Any]) -> None:
         now = time.time()
-        if self._t_prev is not None:
+        if self._cuda_live():
+            import torch
+            ev = torch.cuda.Event(enable_timing=True)
+            ev.record()
+            self._cuda_events.append((step, now, ev))
+        elif self._t_prev is not None:
             self._events.append({"name": "train_step", "ph": "X", "pid": os.getpid(), "tid": 0,
                                  "ts": self._t_prev * 1e6, "dur": (now - self._t_prev) * 1e6, "args": {"step": step}})
         self._t_prev = now
-        if step % self._save_steps == 0 and self._events:
-            os.makedirs(self._dir, exist_ok=True)
-            with open(os.path.join(self._dir, f"timeline-{step}.json"), "w") as f:
-                json.dump({"traceEvents": self._events}, f)
-            self._events = []
+        if step % self._save_steps == 0:
+            self._flush(step)
+
+    def end(self) -> None:
+        if self._cuda_events or self._events:
+            self._flush(self._cuda_events[-1][0] if self._cuda_events else 0)
+
+    def _flush(self, step: int) -> None:
+        if len(self._cuda_events) > 1:
+            self._cuda_events[-1][2].synchronize()
+            for (s0, t0, e0), (s1, _, e1) in zip(self._cuda_events[:-1], self._cuda_events[1:]):
+                self._events.append({"name": "train_step", "ph": "X", "pid": os.getpid(), "tid": 0, "ts": t0 * 1e6,
+                                     "dur": e0.elapsed_time(e1) * 1e3, "args": {"step": s1, "clock": "device"}})
+            self._cuda_events = self._cuda_events[-1:]
+        if not self._events:
+            return
+        os.makedirs(self._dir, exist_ok=True)
+        with open(os.path.join(self._dir, f"timeline-{step}.json"), "w") as f:
+            json.dump({"traceEvents": self._events}, f)
+        self._events = []
 
 
 def get_logging_tensor_hook(every_n_iter=100, tensors_to_log=None, **kwargs):

@@ -247,6 +247,8 @@ typedef struct {
     unsigned long long epoch;                        /* offset added to *epoch_ctr to form the exchange epoch */
     float grad_scale;
     int world, rank, n_chunks;
+    unsigned long long* timing;                      /* optional [4] device cells: ns blocked on the peers' ready flags,
+                                                        ns of the remote loads, ns of the kernel (all CTA 0), calls */
 } DtfAllreduceUpdate;
 int dtf_allreduce_update(const DtfAllreduceUpdate* p, cudaStream_t stream);
 /* Step begin of a data-parallel member: waits until every peer has consumed this replica's gradients

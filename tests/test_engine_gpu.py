@@ -459,3 +459,41 @@ def test_loss_scale_is_folded_into_head_and_optimizer(nat):
     upd_a = a.slot0[:n]
     upd_b = b.slot0[:n]
     assert ((upd_a - upd_b).norm() / upd_a.norm()).item() < 0.05
+
+
+def test_resnet32_trains_to_the_same_accuracy_as_the_fp32_oracle(nat):
+    """Train-to-accuracy on a learnable synthetic task (the label is encoded in the top rows of the image):
+    native bf16 ResNet-32 vs the fp32 torch oracle from the same initial weights, 320 Momentum steps on the same
+    batches; the held-out accuracies must agree within two points (and both must actually have learned)."""
+    from distributedtf_b200.models import resnet
+    from distributedtf_b200.models.engine_eager import EagerEngine
+    from distributedtf_b200.models.resnet_native import NativeResNetEngine
+    from distributedtf_b200.utils.data import cifar_preprocess_torch
+    cfg = resnet.cifar10_config(32)
+    hp = {"opt_case": {"optimizer": "Momentum", "lr": 0.05, "momentum": 0.9}, "decay_steps": 0, "decay_rate": 0.1,
+          "weight_decay": 1e-4, "regularizer": "l2_regularizer", "initializer": "he_init", "batch_size": 128}
+    eng = NativeResNetEngine(cfg, hp, "cuda", seed=21, use_graphs=True)
+    ref = EagerEngine(resnet.param_specs(cfg), lambda p, x, t: resnet.forward(cfg, p, x, t), eng.export_named(), hp,
+                      "cuda", compute_dtype=torch.float32, lr_schedule=True, channels_last=False)
+    g = torch.Generator().manual_seed(7)
+
+    def make(n):
+        labels = torch.randint(0, 10, (n,), generator=g)
+        imgs = torch.randint(0, 256, (n, 32, 32, 3), generator=g, dtype=torch.uint8)
+        imgs[:, :4, :, 0] = (labels * 25).view(-1, 1, 1).to(torch.uint8)
+        return imgs.cuda(), labels.cuda()
+    tr_x, tr_y = make(4096)
+    ev_x, ev_y = make(1024)
+    for step in range(320):
+        sl = slice((step % 32) * 128, (step % 32) * 128 + 128)
+        eng.train_step_u8(tr_x[sl], tr_y[sl], augment=False)
+        ref.train_step(cifar_preprocess_torch(tr_x[sl], False), tr_y[sl])
+    hits_n = hits_r = 0
+    for b in range(8):
+        sl = slice(b * 128, b * 128 + 128)
+        hits_n += int(eng.eval_batch_u8(ev_x[sl], ev_y[sl]).item())
+        hits_r += int(ref.eval_batch(cifar_preprocess_torch(ev_x[sl], False), ev_y[sl]).item())
+    acc_n, acc_r = hits_n / 1024, hits_r / 1024
+    print(f"held-out accuracy after 320 steps: native bf16 {acc_n:.4f}, eager fp32 {acc_r:.4f}")
+    assert acc_r > 0.5, acc_r
+    assert abs(acc_n - acc_r) <= 0.02, (acc_n, acc_r)
