@@ -338,6 +338,11 @@ def main():
                 side = torch.cuda.Stream()
                 side.wait_stream(torch.cuda.current_stream())
                 with torch.cuda.stream(side):
+                    # a fresh leaf whose gradient-accumulator node is born on this (non-default) stream: autograd
+                    # synchronises backward with the stream that node was created on, and the legacy default
+                    # stream must not be touched during capture
+                    eng.flat = eng.flat.detach().clone().requires_grad_(True)
+                    eng._refresh_views()
                     for _ in range(3):
                         eng.train_step(preprocess_on_device(self.x), self.y)
                 torch.cuda.current_stream().wait_stream(side)

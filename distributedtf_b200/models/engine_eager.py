@@ -56,16 +56,22 @@ class EagerEngine:
                     self.reg_mask[off: off + s.numel] = 1.0
                 off += s.numel
         self.flat.requires_grad_(True)
-        off = 0
-        for s in self.train_specs:
-            self.params[s.name] = self.flat[off: off + s.numel].view(s.shape)
-            off += s.numel
         for s in self.state_specs:
             self.params[s.name] = init[s.name].clone().to(self.device)
+        self._refresh_views()
         self.step = 0
         self.hp: Dict[str, Any] = {}
         self.set_hparams(hparams, reset_slots=True)
         self.last_loss: Optional[torch.Tensor] = None
+
+    def _refresh_views(self) -> None:
+        """Per-parameter views of the flat leaf.  Re-made at the start of every training step: autograd runs a
+        node's backward on the stream its forward ran on, and views made once at construction (on the legacy
+        default stream) would tie every backward pass to that stream -- illegal inside a CUDA-graph capture."""
+        off = 0
+        for s in self.train_specs:
+            self.params[s.name] = self.flat[off: off + s.numel].view(s.shape)
+            off += s.numel
 
     # ------------------------------------------------------------------ hparams
     def set_hparams(self, hp: Dict[str, Any], reset_slots: bool = False) -> None:
@@ -89,14 +95,15 @@ class EagerEngine:
     def train_step(self, images_nhwc: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
         """One optimizer step; returns the (device) mean cross-entropy."""
         self.flat.grad = None
+        self._refresh_views()
         logits = self.forward_fn(self.params, self._prep(images_nhwc), True)
         ce = F.cross_entropy(logits.float(), labels.long())
+        # torch.autograd.grad instead of .backward(): no AccumulateGrad node, hence no synchronisation with the
+        # leaf's (legacy default) stream -- which is what lets the whole step be captured in a CUDA graph
+        # (bench.py --impl restated-graph)
+        g, = torch.autograd.grad(ce * self.loss_scale if self.loss_scale != 1.0 else ce, self.flat)
         if self.loss_scale != 1.0:
-            (ce * self.loss_scale).backward()
-            g = self.flat.grad / self.loss_scale
-        else:
-            ce.backward()
-            g = self.flat.grad
+            g = g / self.loss_scale
         oc = self.hp["opt_case"]
         reg, wd = self.hp.get("regularizer", "None"), float(self.hp.get("weight_decay", 0.0))
         with torch.no_grad():

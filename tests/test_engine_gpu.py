@@ -464,7 +464,9 @@ def test_loss_scale_is_folded_into_head_and_optimizer(nat):
 def test_resnet32_trains_to_the_same_accuracy_as_the_fp32_oracle(nat):
     """Train-to-accuracy on a learnable synthetic task (the label is encoded in the top rows of the image):
     native bf16 ResNet-32 vs the fp32 torch oracle from the same initial weights, 320 Momentum steps on the same
-    batches; the held-out accuracies must agree within two points (and both must actually have learned)."""
+    batches.  Compared: the accuracy over the last pass through the data, measured with batch statistics (after
+    320 steps the moving averages, decay 0.997, have covered only 62 % of the way, so inference-mode accuracy says
+    little about either engine), and the loss.  Both must have learned, and agree within two points."""
     from distributedtf_b200.models import resnet
     from distributedtf_b200.models.engine_eager import EagerEngine
     from distributedtf_b200.models.resnet_native import NativeResNetEngine
@@ -476,24 +478,23 @@ def test_resnet32_trains_to_the_same_accuracy_as_the_fp32_oracle(nat):
     ref = EagerEngine(resnet.param_specs(cfg), lambda p, x, t: resnet.forward(cfg, p, x, t), eng.export_named(), hp,
                       "cuda", compute_dtype=torch.float32, lr_schedule=True, channels_last=False)
     g = torch.Generator().manual_seed(7)
-
-    def make(n):
-        labels = torch.randint(0, 10, (n,), generator=g)
-        imgs = torch.randint(0, 256, (n, 32, 32, 3), generator=g, dtype=torch.uint8)
-        imgs[:, :4, :, 0] = (labels * 25).view(-1, 1, 1).to(torch.uint8)
-        return imgs.cuda(), labels.cuda()
-    tr_x, tr_y = make(4096)
-    ev_x, ev_y = make(1024)
+    labels = torch.randint(0, 10, (4096,), generator=g)
+    imgs = torch.randint(0, 256, (4096, 32, 32, 3), generator=g, dtype=torch.uint8)
+    imgs[:, :4, :, 0] = (labels * 25).view(-1, 1, 1).to(torch.uint8)
+    tr_x, tr_y = imgs.cuda(), labels.cuda()
+    hits_n, hits_r, loss_n, loss_r = [], [], [], []
     for step in range(320):
         sl = slice((step % 32) * 128, (step % 32) * 128 + 128)
-        eng.train_step_u8(tr_x[sl], tr_y[sl], augment=False)
-        ref.train_step(cifar_preprocess_torch(tr_x[sl], False), tr_y[sl])
-    hits_n = hits_r = 0
-    for b in range(8):
-        sl = slice(b * 128, b * 128 + 128)
-        hits_n += int(eng.eval_batch_u8(ev_x[sl], ev_y[sl]).item())
-        hits_r += int(ref.eval_batch(cifar_preprocess_torch(ev_x[sl], False), ev_y[sl]).item())
-    acc_n, acc_r = hits_n / 1024, hits_r / 1024
-    print(f"held-out accuracy after 320 steps: native bf16 {acc_n:.4f}, eager fp32 {acc_r:.4f}")
+        loss_n.append(eng.train_step_u8(tr_x[sl], tr_y[sl], augment=False).clone())
+        hits_n.append(eng.correct_cell.clone())                 # train_accuracy: counted by the head kernel
+        loss_r.append(ref.train_step(cifar_preprocess_torch(tr_x[sl], False), tr_y[sl]).clone())
+        hits_r.append(ref.last_train_accuracy.clone())
+    torch.cuda.synchronize()
+    acc_n = sum(int(h.item()) for h in hits_n[-32:]) / 4096
+    acc_r = sum(float(h.item()) for h in hits_r[-32:]) / 32
+    ln, lr_ = sum(l.item() for l in loss_n[-32:]) / 32, sum(l.item() for l in loss_r[-32:]) / 32
+    print(f"last-epoch training accuracy after 320 steps: native bf16 {acc_n:.4f}, eager fp32 {acc_r:.4f}; "
+          f"loss {ln:.4f} / {lr_:.4f}")
     assert acc_r > 0.5, acc_r
     assert abs(acc_n - acc_r) <= 0.02, (acc_n, acc_r)
+    assert abs(ln - lr_) <= 0.15 * lr_ + 0.02, (ln, lr_)
