@@ -568,6 +568,11 @@ def main():
             "launches_per_step": getattr(eng, "launches_per_step", 0), "exploit_ms": exploit_ms,
             "state_bytes": getattr(eng, "state_bytes", lambda: None)(), "wall_s": wall,
         }
+        if getattr(eng, "dp", None) is not None:
+            # device-timestamped accounting from inside the fused all-reduce + update kernel (CTA 0, %globaltimer):
+            # time blocked on the peers' ready flags = exposed communication
+            st = eng.dp.comm_stats()
+            out["dp_comm"] = dict(st, exposed_fraction_of_step=st["wait_us_per_call"] / 1e3 / (dev_ms / args.steps))
         print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()

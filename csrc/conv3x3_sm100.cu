@@ -798,9 +798,9 @@ extern "C" int dtf_conv3x3_wgrad_try(const DtfConvWgrad* p, cudaStream_t stream)
     if (gx > G.num_tiles) gx = G.num_tiles;
     if (gx < 1) gx = 1;
     dim3 grid(gx, ny);
-    if (G.c8 == 2) dtf_launch_ex(true, conv3x3_wgrad_kernel<2>, dim3(grid), dim3(kHThreads), smem_bytes, stream, *p, G);
-    else if (G.c8 == 4) dtf_launch_ex(true, conv3x3_wgrad_kernel<4>, dim3(grid), dim3(kHThreads), smem_bytes, stream, *p, G);
-    else dtf_launch_ex(true, conv3x3_wgrad_kernel<8>, dim3(grid), dim3(kHThreads), smem_bytes, stream, *p, G);
+    if (G.c8 == 2) dtf_launch_ex(G.bulk != 0, conv3x3_wgrad_kernel<2>, dim3(grid), dim3(kHThreads), smem_bytes, stream, *p, G);
+    else if (G.c8 == 4) dtf_launch_ex(G.bulk != 0, conv3x3_wgrad_kernel<4>, dim3(grid), dim3(kHThreads), smem_bytes, stream, *p, G);
+    else dtf_launch_ex(G.bulk != 0, conv3x3_wgrad_kernel<8>, dim3(grid), dim3(kHThreads), smem_bytes, stream, *p, G);
     return cudaGetLastError() == cudaSuccess ? 1 : DTF_ERR_CUDA;
 }
 
@@ -900,9 +900,9 @@ extern "C" int dtf_conv3x3_bwd_fused_try(const DtfConvGemm* pd, const DtfConvWgr
     if (gx < 1) gx = 1;
     const int grid = n_d + gx * ny;
     const int smem_bytes = smem_d > smem_w ? smem_d : smem_w;
-    if (Gd.c8 == 2) dtf_launch_ex(true, conv3x3_bwd_fused_kernel<2>, dim3(grid), dim3(kHThreads), smem_bytes, stream, *pd, Gd, *pw, Gw, n_d, gx);
-    else if (Gd.c8 == 4) dtf_launch_ex(true, conv3x3_bwd_fused_kernel<4>, dim3(grid), dim3(kHThreads), smem_bytes, stream, *pd, Gd, *pw, Gw, n_d, gx);
-    else dtf_launch_ex(true, conv3x3_bwd_fused_kernel<8>, dim3(grid), dim3(kHThreads), smem_bytes, stream, *pd, Gd, *pw, Gw, n_d, gx);
+    if (Gd.c8 == 2) dtf_launch_ex(Gw.bulk != 0, conv3x3_bwd_fused_kernel<2>, dim3(grid), dim3(kHThreads), smem_bytes, stream, *pd, Gd, *pw, Gw, n_d, gx);
+    else if (Gd.c8 == 4) dtf_launch_ex(Gw.bulk != 0, conv3x3_bwd_fused_kernel<4>, dim3(grid), dim3(kHThreads), smem_bytes, stream, *pd, Gd, *pw, Gw, n_d, gx);
+    else dtf_launch_ex(Gw.bulk != 0, conv3x3_bwd_fused_kernel<8>, dim3(grid), dim3(kHThreads), smem_bytes, stream, *pd, Gd, *pw, Gw, n_d, gx);
     return cudaGetLastError() == cudaSuccess ? 1 : DTF_ERR_CUDA;
 }
 

@@ -27,6 +27,7 @@
 #include <deque>
 #include <mutex>
 #include <set>
+#include <memory>
 #include <string>
 #include <thread>
 #include <vector>
@@ -35,14 +36,36 @@
 
 namespace {
 
+// "The caller's device -> host copy has landed": set by a host function the submitting thread enqueues on its
+// stream behind the copy (cudaLaunchHostFunc), waited for by the writer thread with a plain condition variable.
+// The writer threads make NO CUDA API call at all: an earlier version synchronised a CUDA event here, and a
+// cudaEventSynchronize from a writer thread racing with another member's CUDA-graph capture (members_in_flight)
+// occasionally failed and invalidated that capture.
+struct Landed {
+    std::mutex mu;
+    std::condition_variable cv;
+    bool done = false;
+};
+
 struct Job {
     long long ticket;
     std::string data_path, index_path, index_text, pointer_path, pointer_text;
     const void* host_ptr;
     size_t nbytes;
-    cudaEvent_t event;       // recorded at submit on the caller's stream; null for host-only jobs
+    std::shared_ptr<Landed> landed;      // null for host-only jobs
     int device;
 };
+
+void CUDART_CB landed_callback(void* user) {
+    // runs on a driver thread once everything queued before it on the stream has finished; must not call CUDA
+    auto* keep = static_cast<std::shared_ptr<Landed>*>(user);
+    {
+        std::lock_guard<std::mutex> lk((*keep)->mu);
+        (*keep)->done = true;
+    }
+    (*keep)->cv.notify_all();
+    delete keep;
+}
 
 struct Writer {
     std::mutex mu;
@@ -80,9 +103,9 @@ int write_atomic(const std::string& path, const void* p, size_t n) {
 
 void run_job(Writer* w, const Job& j) {
     int rc = 0;
-    if (j.event != nullptr) {
-        if (cudaEventSynchronize(j.event) != cudaSuccess) rc = -1;
-        cudaEventDestroy(j.event);
+    if (j.landed) {
+        std::unique_lock<std::mutex> lk(j.landed->mu);
+        j.landed->cv.wait(lk, [&] { return j.landed->done; });
     }
     if (rc == 0) rc = write_atomic(j.data_path, j.host_ptr, j.nbytes);
     if (rc == 0 && !j.index_path.empty()) rc = write_atomic(j.index_path, j.index_text.data(), j.index_text.size());
@@ -132,14 +155,13 @@ extern "C" long long dtf_io_submit(void* handle, const char* data_path, const vo
     j.data_path = data_path;
     j.host_ptr = host_ptr;
     j.nbytes = static_cast<size_t>(nbytes);
-    j.event = nullptr;
     j.device = device;
     if (device >= 0) {
-        // The event that marks the end of the caller's device->host copy is created, recorded and destroyed
-        // here and in the writer thread: no handle of the caller's has to outlive this call.
-        if (cudaEventCreateWithFlags(&j.event, cudaEventDisableTiming) != cudaSuccess) return DTF_ERR_CUDA;
-        if (cudaEventRecord(j.event, static_cast<cudaStream_t>(cuda_stream)) != cudaSuccess) {
-            cudaEventDestroy(j.event);
+        // a host function behind the caller's device->host copy marks the staging buffer as complete
+        j.landed = std::make_shared<Landed>();
+        auto* keep = new std::shared_ptr<Landed>(j.landed);
+        if (cudaLaunchHostFunc(static_cast<cudaStream_t>(cuda_stream), landed_callback, keep) != cudaSuccess) {
+            delete keep;
             return DTF_ERR_CUDA;
         }
     }

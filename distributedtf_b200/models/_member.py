@@ -70,7 +70,7 @@ class GpuMember(ModelBase):
                  hooks: Optional[List[Any]] = None, dp_group=None, dp_rank: int = 0, dp_size: int = 1,
                  scoreboard: Optional[Dict[str, Any]] = None, benchmark=None, async_checkpoint: bool = False,
                  checkpoint_every: int = 1, epochs_between_evals: int = 1, stop_threshold: Optional[float] = None,
-                 export_dir: Optional[str] = None, all_reduce_alg: Optional[str] = None, **_):
+                 export_dir: Optional[str] = None, all_reduce_alg: Optional[str] = None, use_graphs: bool = True, **_):
         super().__init__(cluster_id, hparams, save_base_dir)
         self.device = device or pick_device()
         self.dp_group, self.dp_rank, self.dp_size = dp_group, int(dp_rank), int(dp_size)
@@ -96,6 +96,9 @@ class GpuMember(ModelBase):
         self.export_dir = export_dir
         self.stopped_early = False
         self.all_reduce_alg = all_reduce_alg    # data-parallel member: fused_p2p (default) | nccl (library baseline)
+        # native engines replay their step from a CUDA graph unless told otherwise (the launcher turns graphs off
+        # for members that train concurrently inside one process, see launch.model_kwargs)
+        self.use_graphs = bool(use_graphs)
         if benchmark and benchmark[0] == "BenchmarkFileLogger" and benchmark[1]:
             from ..utils.logs import logger as _logger
             self._bench_logger = _logger.BenchmarkFileLogger(os.path.join(benchmark[1], f"model_{cluster_id}"))

@@ -51,7 +51,7 @@ class Cifar10Model(GpuMember):
             try:
                 return cls(self.net_cfg, self.hparams, self.device, seed=seed, dtype=self.dtype,
                            loss_scale=self.loss_scale,
-                           arena_alloc=self.make_symmetric_alloc,
+                           arena_alloc=self.make_symmetric_alloc, use_graphs=self.use_graphs,
                            dp_group=self.dp_group if self.dp_size > 1 else None,
                            all_reduce_alg=self.all_reduce_alg if self.dp_size > 1 else None)
             except NotImplementedError:

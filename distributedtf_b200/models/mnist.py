@@ -47,7 +47,7 @@ class MNISTModel(GpuMember):
                 self.engine_kind = "eager"          # `auto`: the MNIST kernels are not built into this version
             else:
                 return NativeMnistEngine(self.hparams, self.device, seed=seed, dtype=self.dtype,
-                                         arena_alloc=self.make_symmetric_alloc,
+                                         arena_alloc=self.make_symmetric_alloc, use_graphs=self.use_graphs,
                                          dp_group=self.dp_group if self.dp_size > 1 else None,
                                           all_reduce_alg=self.all_reduce_alg if self.dp_size > 1 else None)
         from .engine_eager import EagerEngine

@@ -13,6 +13,7 @@ its activations, and implements ``_train_kernels`` / ``_eval_kernels`` as a sequ
 from __future__ import annotations
 
 import ctypes as C
+import os
 import threading
 from typing import Any, Dict, List, Optional, Tuple
 
@@ -72,7 +73,7 @@ class NativeEngineBase:
         native.require()
         self.device = torch.device(device)
         self.max_batch = max_batch
-        self.use_graphs = use_graphs
+        self.use_graphs = use_graphs and os.environ.get("DTF_NO_GRAPHS") != "1"
         self.hp: Dict[str, Any] = {}
         self._graphs: Dict[Tuple[str, int], torch.cuda.CUDAGraph] = {}
         self.dp_group = dp_group          # torch.distributed group of this member's replicas (None = 1 GPU)

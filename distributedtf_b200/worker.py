@@ -122,8 +122,7 @@ class TrainingWorker:
             acc = g.get_accuracy()
             return not (isinstance(acc, float) and math.isnan(acc))
         except Exception:  # member-level failure: drop it, keep the worker alive
-            if self.verbose:
-                traceback.print_exc()
+            traceback.print_exc()          # always: a dropped member must leave a trace (the reference prints one too)
             marker = getattr(g, "publish_dropped", None)
             if marker is not None:      # device score board: the master must not wait for this member
                 marker()

@@ -13,7 +13,7 @@ def _cfg(tmp_path, **kw):
     base = dict(target_model="cifar10", population_size=4, train_round=2, epochs_per_round=1, workers=1,
                 transport="local", exploit_path="p2p", engine="native", resnet_size=8, max_train_steps=4,
                 eval_batches=2, save_root=str(tmp_path / "savedata"), results_file=str(tmp_path / "res.txt"),
-                verbose=False, seed=3)
+                verbose=bool(os.environ.get("DTF_TEST_VERBOSE")), seed=3)
     base.update(kw)
     return RunConfig(**base).validate()
 
