@@ -502,6 +502,18 @@ def main():
     #      lazy point-to-point connection set-up all happen here, not in the timed region) ----
     for i in range(max(args.warmup, 3)):
         step_resident(i)
+    if args.impl != "native" and world > 1:
+        # library arms: open every NCCL point-to-point connection now (the timed event may pair other ranks than
+        # the warm-up event did, and NCCL sets a connection up lazily on first use: ~300-450 ms)
+        for peer in range(world):
+            if peer == rank:
+                continue
+            t = torch.zeros(1, device=dev)
+            if rank < peer:
+                dist.send(t, dst=peer); dist.recv(t, src=peer)
+            else:
+                dist.recv(t, src=peer); dist.send(t, dst=peer)
+        torch.cuda.synchronize()
     pbt_begin()
     pbt_finish()
     exploit_events.clear()

@@ -91,6 +91,7 @@ class NativeEngineBase:
         self._seed = seed
         self._count = 0
         self._side = None                       # side stream for independent kernels (engine-specific use)
+        self._cap_stream = None                 # stream CUDA graphs are captured on
         self.board_slot_ptr = 0                 # this member's score-board slot (device / peer pointer), 0 = none
         # static loss scale (reference resnet_run_loop.py:284-294): the head kernel multiplies d(loss)/d(logits) by it,
         # the optimizer / all-reduce kernel multiplies the gradients by 1 / scale (DtfHparams.inv_loss_scale)
@@ -265,10 +266,23 @@ class NativeEngineBase:
             _GATE.enter_capture()
             try:
                 fn()                               # first use: a plain run (sets kernel attributes) ...
-                torch.cuda.current_stream(self.device).synchronize()
+                cur = torch.cuda.current_stream(self.device)
+                cur.synchronize()
+                # ... then capture, on a side stream, with the graph object's own begin / end calls: the
+                # torch.cuda.graph context manager would add a device-wide synchronize, gc.collect() and
+                # empty_cache() to every capture (~100 ms in a PBT worker, paid again whenever explore changes a
+                # member's batch size)
                 g = torch.cuda.CUDAGraph()
-                with torch.cuda.graph(g, capture_error_mode="thread_local"):   # ... then capture
-                    fn()
+                if self._cap_stream is None:
+                    self._cap_stream = torch.cuda.Stream(device=self.device)
+                self._cap_stream.wait_stream(cur)
+                with torch.cuda.stream(self._cap_stream):
+                    g.capture_begin(capture_error_mode="thread_local")
+                    try:
+                        fn()
+                    finally:
+                        g.capture_end()
+                cur.wait_stream(self._cap_stream)
             finally:
                 _GATE.exit_capture()
             self._graphs[key] = g
