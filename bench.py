@@ -189,6 +189,7 @@ def pbt_mode(args) -> int:
         after = self.profiling_info()
         timed["phases"] = {k: after[k] - before.get(k, 0.0) for k in after if k.startswith("device_") or k in
                            ("train", "explore", "exploit", "gather_wait")}
+        timed["workers"] = len(self.worker_ranks)
         timed["history"] = len(self.history)
         timed["fallbacks"] = self.board_fallbacks
         return out
@@ -201,7 +202,11 @@ def pbt_mode(args) -> int:
         launch.PBTCluster.train = orig_train
     clocks = sampler.stop()
     ph = timed["phases"]
-    images = members * args.rounds * args.steps_per_round * args.batch
+    # images actually trained: explore perturbs batch sizes, so members leave the nominal batch after round 1
+    # (the master's profile holds the mean over the workers it talks to)
+    nominal = members * args.rounds * args.steps_per_round * args.batch
+    images = ph.pop("device_images", 0.0) * timed["workers"] or nominal
+    ph.pop("device_images_max", None)
     dev_s = ph.get("device_train_max", 0.0) + ph.get("device_eval_max", 0.0) + ph.get("device_exploit_max", 0.0)
     res = {"metric": METRIC if args.model == "cifar10" else "MNIST deep CNN PBT images/sec (box, max over ranks)",
            "value": images / max(dev_s, 1e-9), "unit": "images/s", "n_gpus": args.gpus, "steps": args.rounds * args.steps_per_round,
@@ -213,6 +218,7 @@ def pbt_mode(args) -> int:
                       "parallelism": f"population {members} x {D} GPU, master + {members} workers over TCP, "
                                      f"p2p exploit, device score board",
                       "rounds": args.rounds, "steps_per_round": args.steps_per_round, "eval_batches": args.eval_batches,
+                      "images_trained": images, "images_at_nominal_batch": nominal,
                       "what_is_timed": "train + eval + exploit device time of the slowest worker over the timed rounds"},
            "wall": {"seconds": timed["wall"], "images_per_s": images / max(timed["wall"], 1e-9)},
            "phases_s": ph, "exploit_events": timed["history"], "board_fallbacks": timed["fallbacks"],

@@ -201,7 +201,8 @@ class GpuMember(ModelBase):
                             "train_accuracy": _TrainAccuracy(self.engine, int(idx.numel()))}
                     for h in self.hooks:
                         h.after_step(self._global_step, vals)
-        dt = max(self.device_times["train"], 1e-9)
+        # counted on replica 0 only, so that a data-parallel group reports its global batch once
+        self.device_times["images"] = self.device_times.get("images", 0.0) + (steps * bs if self.dp_rank == 0 else 0)
         self.last_images_per_sec = steps * bs / max(time.time() - t0, 1e-9)
         return steps
 
