@@ -47,6 +47,8 @@ def parse():
                         "TF-1 graph executor amounts to; the strong library baseline); reference = unavailable here")
     p.add_argument("--batch", type=int, default=BATCH)
     p.add_argument("--resnet-size", type=int, default=32)
+    p.add_argument("--resnet-version", type=int, default=2, choices=[1, 2])
+    p.add_argument("--bottleneck", action="store_true", help="bottleneck blocks (resnet-size 9n + 2); not the headline")
     p.add_argument("--dp-size", type=int, default=1, choices=[1, 2, 4],
                    help="GPUs per member (BASELINE config 4: population N/D x data-parallel D)")
     p.add_argument("--mode", choices=["step", "pbt"], default="step",
@@ -277,10 +279,14 @@ def main():
 
     # ---- member under test ----
     from distributedtf_b200.models import resnet
-    cfg = resnet.cifar10_config(args.resnet_size)
+    cfg = resnet.cifar10_config(args.resnet_size, args.resnet_version, bottleneck=args.bottleneck)
     symm_buf = None
     if args.impl == "native":
         from distributedtf_b200.models.resnet_native import NativeResNetEngine
+        if args.bottleneck or args.resnet_version == 1:
+            from distributedtf_b200.models import resnet_native_bottleneck as _rb, resnet_native_v1 as _r1
+            NativeResNetEngine = {(2, True): _rb.NativeResNetBottleneckEngine, (1, True): _rb.NativeResNetBottleneckV1Engine,
+                                  (1, False): _r1.NativeResNetV1Engine}[(args.resnet_version, args.bottleneck)]
         from distributedtf_b200.parallel import exploit, symm
 
         def alloc(n):
@@ -572,7 +578,8 @@ def main():
             "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
             "data": "synthetic uint8 CIFAR-10-shaped images (random), random labels, random-init weights",
             "impl": args.impl,
-            "config": {"model": f"CIFAR-10 ResNet-{args.resnet_size} v2 (resnet_model, 6n+2)",
+            "config": {"model": f"CIFAR-10 ResNet-{args.resnet_size} v{args.resnet_version} (resnet_model, "
+                                + ("bottleneck blocks, 9n+2)" if args.bottleneck else "6n+2)"),
                        "global_batch": args.batch * members, "per_gpu_batch": B, "seq_len": None,
                        "parallelism": f"population {members} x {D} GPU" + (f" (pbt{members})" if D == 1 else f" (pbt{members} x dp{D}, fused all-reduce+update)"),
                        "optimizer": "Momentum 0.9 + l2 2e-4",

@@ -289,7 +289,7 @@ DTF_DEVINL void gather_taps_t(const DtfGather& g, const int8_t* tap_dy, const in
 #undef DTF_BATCH
 }
 
-// Fallback for wide channel counts (> 64): one chunk at a time.
+// Fallback (strides > 2): one chunk at a time.
 DTF_DEVINL void gather_chunks_slow(const DtfGather& g, const int8_t* tap_dy, const int8_t* tap_dx,
                                    const float* p0, const float* p1, const float* p2, const RowCoord& rc,
                                    int jbeg, int jend, uint32_t dst) {
@@ -297,11 +297,34 @@ DTF_DEVINL void gather_chunks_slow(const DtfGather& g, const int8_t* tap_dy, con
         sts16(dst + (j - jbeg) * (kTileM * 16), gather16(g, tap_dy, tap_dx, p0, p1, p2, rc, j));
 }
 
+// Wide channel counts (128 / 256: the 1x1 convolutions of bottleneck blocks): the chunks of a row are taken in
+// batches whose loads are all in flight before the first one is consumed (8 x 16 bytes per source, 4 with the
+// second source of the BN-backward prologue).
+template <bool TWO>
+DTF_DEVINL void gather_chunks_wide(const DtfGather& g, const int8_t* tap_dy, const int8_t* tap_dx,
+                                   const float* p0, const float* p1, const float* p2, const RowCoord& rc,
+                                   int jbeg, int jend, uint32_t dst) {
+    constexpr int B = TWO ? 4 : 8;
+    for (int j = jbeg; j < jend; j += B) {
+        GatherLoad L[B];
+#pragma unroll
+        for (int u = 0; u < B; ++u) gather_issue<TWO>(g, tap_dy, tap_dx, rc, j + u < jend ? j + u : g.kchunks_real, L[u]);
+#pragma unroll
+        for (int u = 0; u < B; ++u)
+            if (j + u < jend) sts16(dst + (j + u - jbeg) * (kTileM * 16), gather_finish(g, p0, p1, p2, L[u]));
+    }
+}
+
 DTF_DEVINL void gather_row(const DtfGather& g, const int8_t* tap_dy, const int8_t* tap_dx,
                            const float* p0, const float* p1, const float* p2, const RowCoord& rc,
                            int jbeg, int jend, uint32_t dst) {
-    if (g.cpt_shift > 3 || g.stride > 2) {
+    if (g.stride > 2) {
         gather_chunks_slow(g, tap_dy, tap_dx, p0, p1, p2, rc, jbeg, jend, dst);
+        return;
+    }
+    if (g.cpt_shift > 3) {
+        if (g.mode == DTF_PRO_BN_BWD) gather_chunks_wide<true>(g, tap_dy, tap_dx, p0, p1, p2, rc, jbeg, jend, dst);
+        else gather_chunks_wide<false>(g, tap_dy, tap_dx, p0, p1, p2, rc, jbeg, jend, dst);
         return;
     }
     const RowPre rp = row_pre(g, rc);

@@ -197,8 +197,10 @@ conv_wgrad_kernel(const __grid_constant__ DtfConvWgrad P) {
     const int j0 = blockIdx.y * P.chunks_per_cta;
     const int nj = min(P.chunks_per_cta, P.kchunks - j0);            // real+pad chunks of this CTA (even)
     const int ncols = nj * 8;                                         // UMMA N
-    const int gy_chunks = P.Cout / 8;
-    const uint32_t buf_bytes = static_cast<uint32_t>(gy_chunks + P.chunks_per_cta) * kChunkBytes;
+    // blockIdx.z selects 128 output channels (Cout up to 256: the expanding 1x1 convolutions of bottleneck blocks)
+    const int co_chunk0 = blockIdx.z * 16;
+    const int gy_chunks = min(P.Cout / 8 - co_chunk0, 16);
+    const uint32_t buf_bytes = static_cast<uint32_t>(min(P.Cout / 8, 16) + P.chunks_per_cta) * kChunkBytes;
     const uint32_t acc_cols = tmem_cols_pow2(ncols);
 
     if (tid == 0) {
@@ -270,14 +272,15 @@ conv_wgrad_kernel(const __grid_constant__ DtfConvWgrad P) {
                 const RowCoord rc = row_coord(tile * kTileM + row, M, P.Ho, P.Wo);
                 mbar_wait(smem_u32(&hdr->empty[buf]), ((it >> 1) & 1) ^ 1, 9);
                 const uint32_t a_dst = smem_u32(smem_ab) + buf * buf_bytes + row * 16;
-                gather_row(P.gy, hdr->tap_dy + 31, hdr->tap_dx + 31, cst->q0, cst->q1, cst->q2, rc, 0, gy_chunks, a_dst);
+                gather_row(P.gy, hdr->tap_dy + 31, hdr->tap_dx + 31, cst->q0, cst->q1, cst->q2, rc, co_chunk0,
+                           co_chunk0 + gy_chunks, a_dst);
                 fence_proxy_async_smem();
                 mbar_arrive(smem_u32(&hdr->full[buf]));
             }
         }
         mbar_wait(smem_u32(&hdr->acc_full[0]), 0, 8);
         tc_fence_after_sync();
-        const int co = warp * 32 + lane;                   // TMEM lane = output channel
+        const int co = co_chunk0 * 8 + warp * 32 + lane;   // TMEM lane = output channel
         const int kreal = P.kchunks_real * 8;
         for (int cg = 0; cg < ncols; cg += 8) {
             float v[8];
@@ -391,7 +394,7 @@ extern "C" int dtf_conv_wgrad(DtfConvWgrad* p, cudaStream_t stream) {
     p->gy.Hs = p->Ho; p->gy.Ws = p->Wo; p->gy.C = p->Cout;
     rc = prep_gather(&p->gy);
     if (rc != DTF_OK) return rc;
-    if (p->Cout % 8 != 0 || p->Cout > 128) return DTF_ERR_SHAPE;
+    if (p->Cout % 8 != 0 || p->Cout > 256) return DTF_ERR_SHAPE;
     p->kchunks_real = p->x.kchunks_real;
     p->kchunks = (p->kchunks_real + 1) & ~1;
     rc = dtf_conv3x3_wgrad_try(p, stream);
@@ -404,14 +407,15 @@ extern "C" int dtf_conv_wgrad(DtfConvWgrad* p, cudaStream_t stream) {
     ny = (p->kchunks + per - 1) / per;
     const int header = 1024 + static_cast<int>(sizeof(SmemConsts));
     const int a_off = (header + 1023) & ~1023;
-    const int buf_bytes = (p->Cout / 8 + per) * kChunkBytes;
+    const int nz = (p->Cout + 127) / 128;              // 128 output channels per CTA (blockIdx.z)
+    const int buf_bytes = ((p->Cout < 128 ? p->Cout : 128) / 8 + per) * kChunkBytes;
     // the A descriptor always spans 16 channel chunks: keep 32 KB of slack after the last buffer
     const int smem_bytes = a_off + 2 * buf_bytes + 16 * kChunkBytes;
     if (smem_bytes > 227 * 1024) return DTF_ERR_SMEM;
     p->smem_a_off = a_off;
     const int M = p->NB * p->Ho * p->Wo;
     const int tiles = (M + kTileM - 1) / kTileM;
-    int gx = num_sms() / ny;
+    int gx = num_sms() / (ny * nz);
     if (gx < 1) gx = 1;
     if (gx > tiles) gx = tiles;
     static int set = 0;
@@ -420,7 +424,7 @@ extern "C" int dtf_conv_wgrad(DtfConvWgrad* p, cudaStream_t stream) {
         if (e != cudaSuccess) return DTF_ERR_CUDA;
         set = 1;
     }
-    dim3 grid(gx, ny);
+    dim3 grid(gx, ny, nz);
     dtf_launch(conv_wgrad_kernel, grid, dim3(kThreads), smem_bytes, stream, *p);
     return cudaGetLastError() == cudaSuccess ? DTF_OK : DTF_ERR_CUDA;
 }

@@ -47,6 +47,7 @@ class RunConfig:
     # --- model / data ---
     resnet_size: int = 32
     resnet_version: int = 2
+    resnet_bottleneck: bool = False       # bottleneck blocks (resnet_model.py:215-320); resnet_size is then 9n + 2
     synthetic: bool = True
     data_dir: str = "./datasets"
     max_train_steps: Optional[int] = None  # cap steps per epoch (synthetic / smoke runs)
@@ -78,8 +79,8 @@ class RunConfig:
             raise ValueError("dp_size must be 1, 2 or 4")
         if self.target_model not in ("toy", "mnist", "cifar10"):
             raise ValueError("target_model must be toy | mnist | cifar10")
-        if self.resnet_size % 6 != 2:
-            raise ValueError("resnet_size must be 6n + 2")
+        if self.resnet_size % (9 if self.resnet_bottleneck else 6) != 2:
+            raise ValueError("resnet_size must be 6n + 2 (9n + 2 with bottleneck blocks)")
         if self.resnet_version not in (1, 2):
             raise ValueError("resnet_version must be 1 or 2")
         if self.resnet_version == 1 and self.dtype == "fp16":
@@ -147,6 +148,9 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--engine", choices=["auto", "native", "eager"], default="auto")
     p.add_argument("--resnet-size", "--resnet_size", dest="resnet_size", type=int, default=32)
     p.add_argument("--resnet-version", "--resnet_version", dest="resnet_version", type=int, choices=[1, 2], default=2)
+    p.add_argument("--resnet-bottleneck", "--resnet_bottleneck", dest="resnet_bottleneck",
+                   action=argparse.BooleanOptionalAction, default=False,
+                   help="build the three stages from bottleneck blocks (resnet_size = 9n + 2)")
     p.add_argument("--synthetic", "--use_synthetic_data", dest="synthetic", action=argparse.BooleanOptionalAction,
                    default=True)
     p.add_argument("--eval-batches", type=int, default=None)

@@ -56,7 +56,8 @@ def model_kwargs(cfg: RunConfig, dp_group=None, dp_rank: int = 0) -> Dict[str, A
     kw.update(epochs_between_evals=cfg.epochs_between_evals, stop_threshold=cfg.stop_threshold,
               export_dir=cfg.export_dir)
     if cfg.target_model == "cifar10":
-        kw.update(resnet_size=cfg.resnet_size, resnet_version=cfg.resnet_version, loss_scale=cfg.loss_scale)
+        kw.update(resnet_size=cfg.resnet_size, resnet_version=cfg.resnet_version, loss_scale=cfg.loss_scale,
+                  resnet_bottleneck=cfg.resnet_bottleneck)
     # reference distribution_utils.get_distribution_strategy: one device, or a mirrored (data-parallel) member
     from .utils.misc.distribution_utils import get_distribution_strategy
     strategy = get_distribution_strategy(cfg.dp_size if cfg.target_model != "toy" else 1, cfg.all_reduce_alg)

@@ -28,8 +28,9 @@ class Cifar10Model(GpuMember):
                   "initializer", "regularizer", "weight_decay", "batch_size", "model_id"]
 
     def __init__(self, cluster_id: int, hparams: Dict[str, Any], save_base_dir: str, *,
-                 resnet_size: int = 32, resnet_version: int = 2, loss_scale: Optional[float] = None, **kw):
-        self.net_cfg = resnet.cifar10_config(resnet_size, resnet_version)
+                 resnet_size: int = 32, resnet_version: int = 2, loss_scale: Optional[float] = None,
+                 resnet_bottleneck: bool = False, **kw):
+        self.net_cfg = resnet.cifar10_config(resnet_size, resnet_version, bottleneck=resnet_bottleneck)
         self.loss_scale = loss_scale            # None: 128 for fp16, 1 otherwise (flags.get_loss_scale)
         super().__init__(cluster_id, hparams, save_base_dir, **kw)
 
@@ -46,8 +47,11 @@ class Cifar10Model(GpuMember):
         seed = 7919 * (self.cluster_id + 1)
         if self.engine_kind == "native":
             from .resnet_native import NativeResNetEngine
+            from .resnet_native_bottleneck import NativeResNetBottleneckEngine, NativeResNetBottleneckV1Engine
             from .resnet_native_v1 import NativeResNetV1Engine
-            cls = NativeResNetEngine if self.net_cfg.resnet_version == 2 else NativeResNetV1Engine
+            cls = {(2, False): NativeResNetEngine, (1, False): NativeResNetV1Engine,
+                   (2, True): NativeResNetBottleneckEngine, (1, True): NativeResNetBottleneckV1Engine}[
+                       (self.net_cfg.resnet_version, self.net_cfg.bottleneck)]
             try:
                 return cls(self.net_cfg, self.hparams, self.device, seed=seed, dtype=self.dtype,
                            loss_scale=self.loss_scale,
@@ -55,8 +59,8 @@ class Cifar10Model(GpuMember):
                            dp_group=self.dp_group if self.dp_size > 1 else None,
                            all_reduce_alg=self.all_reduce_alg if self.dp_size > 1 else None)
             except NotImplementedError:
-                # bottleneck blocks and fp32 / tf32 are served by the eager engine; an explicit request for
-                # the native engine is an error, `auto` degrades.
+                # fp32 / tf32 compute is served by the eager engine; an explicit request for the native
+                # engine is an error, `auto` degrades.
                 if self._engine_requested == "native":
                     raise
                 self.engine_kind, self.symm = "eager", None

@@ -49,14 +49,20 @@ class ResNetConfig:
         return self.resnet_version == 2
 
 
-def cifar10_config(resnet_size: int = 32, resnet_version: int = 2, num_classes: int = 10) -> ResNetConfig:
-    if resnet_size % 6 != 2:
-        raise ValueError("resnet_size must be 6n + 2:", resnet_size)
+def cifar10_config(resnet_size: int = 32, resnet_version: int = 2, num_classes: int = 10,
+                   bottleneck: bool = False) -> ResNetConfig:
+    """The reference's CIFAR-10 model (``cifar10_main.py:167-199``: building blocks, 6n + 2 layers).  With
+    ``bottleneck=True`` the same three stages are built from bottleneck blocks (``resnet_model.py:215-320``; 9n + 2
+    layers, the dense layer sees 4 x 64 channels) -- the reference's ``Model`` takes the switch, its CIFAR main
+    never sets it."""
+    per_block = 9 if bottleneck else 6
+    if resnet_size % per_block != 2:
+        raise ValueError("resnet_size must be {}n + 2:".format(per_block), resnet_size)
     if resnet_version not in (1, 2):
         raise ValueError("Resnet version should be 1 or 2.")
-    n = (resnet_size - 2) // 6
-    return ResNetConfig(resnet_size=resnet_size, block_sizes=(n, n, n), resnet_version=resnet_version,
-                        num_classes=num_classes)
+    n = (resnet_size - 2) // per_block
+    return ResNetConfig(resnet_size=resnet_size, bottleneck=bottleneck, block_sizes=(n, n, n),
+                        final_size=256 if bottleneck else 64, resnet_version=resnet_version, num_classes=num_classes)
 
 
 @dataclass(frozen=True)

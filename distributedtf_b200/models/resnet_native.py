@@ -1,11 +1,11 @@
-"""The B200 training engine for the CIFAR ResNet (v2, building blocks).
+"""The B200 training engine for the CIFAR ResNet (v2, building blocks; v1 and bottleneck blocks: sibling modules).
 
 Everything a step does runs in hand-written sm_100a kernels (``csrc/``): the input
 preprocessing, every convolution forward / dgrad / wgrad as a tcgen05 implicit GEMM with
 BatchNorm+ReLU applied in the operand gather and BN statistics / residual add in the
 epilogue, the classifier head (final BN + ReLU + pool + dense + softmax-CE, fwd+bwd in one
 launch), the BN-backward apply, and a single multi-tensor optimizer launch that also
-re-emits the bf16 GEMM-ready weights.  The ~110 launches of a step are captured once per
+re-emits the bf16 GEMM-ready weights.  The launches of a step (93 for ResNet-32) are captured once per
 batch size in a CUDA graph; hyper-parameters, LR schedule and the step counter live in
 device memory, so explore / exploit never force a re-capture.
 
@@ -82,8 +82,7 @@ class NativeResNetEngine(NativeEngineBase):
     def __init__(self, cfg: resnet.ResNetConfig, hparams: Dict[str, Any], device, *, seed: int = 0,
                  dtype: str = "bf16", max_batch: int = MAX_BATCH, use_graphs: bool = True,
                  arena_alloc=None, dp_group=None, all_reduce_alg=None, loss_scale: Optional[float] = None):
-        if cfg.resnet_version != self.version or cfg.bottleneck or cfg.first_pool_size:
-            raise NotImplementedError("native engines cover the CIFAR configuration: building blocks, v1 or v2")
+        self._check_config(cfg)
         if dtype not in ("bf16", "fp16"):
             raise NotImplementedError("native engine computes with 16-bit operands, fp32 accumulation and fp32 master "
                                       "weights; fp32 / tf32 runs on the eager engine")
@@ -100,6 +99,11 @@ class NativeResNetEngine(NativeEngineBase):
         self._alloc()
         self._init_params(hparams.get("initializer", "None"), seed)
         self.set_hparams(hparams, reset_slots=True)
+
+    def _check_config(self, cfg) -> None:
+        if cfg.resnet_version != self.version or cfg.bottleneck or cfg.first_pool_size:
+            raise NotImplementedError("building-block engine: CIFAR configuration (no bottleneck, no initial "
+                                      "max-pool); bottleneck blocks: resnet_native_bottleneck.py")
 
     def lr_schedule(self, hp):
         return reference.cifar_lr_schedule(hp)

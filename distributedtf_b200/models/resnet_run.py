@@ -23,7 +23,7 @@ from ..utils.flags import core as flags_core
 from ..utils.logs import logger as _logger
 from ..utils.misc import distribution_utils, model_helpers
 
-RESNET_SIZES = [str(6 * n + 2) for n in range(1, 34)]
+RESNET_SIZES = sorted({str(6 * n + 2) for n in range(1, 34)} | {str(9 * n + 2) for n in range(1, 23)}, key=int)
 
 
 def define_cifar_flags(hp: Optional[Dict[str, Any]] = None, model_id: int = 0, model_dir: str = "/tmp/cifar10_model",
@@ -46,6 +46,7 @@ def define_cifar_flags(hp: Optional[Dict[str, Any]] = None, model_id: int = 0, m
     fs.define("total_epochs", "ttep", total_epochs, "The total epochs the model will be trained (default: "
               "epoch_index + train_epochs as parsed; the reference takes the unparsed default, SURVEY 2.8)", type=int)
     fs.define("epoch_index", "epi", epoch_index, "The epoch index written to the csv", type=int)
+    fs.define("resnet_bottleneck", "rb", False, "Bottleneck blocks (resnet_size is then 9n + 2).", type=bool)
     fs.define("engine", None, "auto", "native (sm_100a kernels) | eager (torch oracle) | auto",
               choices=["auto", "native", "eager"])
     fs.set_defaults(data_dir=data_dir, model_dir=model_dir, resnet_size="32", train_epochs=train_epochs,
@@ -80,6 +81,7 @@ def resnet_main(ns) -> Tuple[float, int]:
                           data_dir=ns.data_dir, max_train_steps=ns.max_train_steps,
                           eval_batches=4 if ns.max_train_steps else None,
                           resnet_size=int(ns.resnet_size), resnet_version=int(ns.resnet_version),
+                          resnet_bottleneck=bool(ns.resnet_bottleneck),
                           loss_scale=flags_core.get_loss_scale(ns) if ns.dtype == "fp16" or ns.loss_scale else None,
                           epochs_between_evals=ns.epochs_between_evals, stop_threshold=ns.stop_threshold,
                           export_dir=ns.export_dir, resume=os.path.isdir(save_base + str(ns.model_id)),

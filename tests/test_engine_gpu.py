@@ -432,6 +432,65 @@ def test_native_v1_step_matches_oracle(nat, size, nb):
     assert 0 <= eng2.eval_batch_u8(imgs, labels).item() <= nb
 
 
+@pytest.mark.parametrize("version,size,nb", [(2, 11, 32), (2, 20, 64), (1, 11, 32), (1, 20, 48)])
+def test_native_bottleneck_step_matches_oracle(nat, version, size, nb):
+    """Bottleneck blocks (1x1 reduce -> 3x3 -> 1x1 expand to 4 x filters, up to 256 channels), v1 and v2, on the
+    native engines: one full step against autograd on the torch oracle (reference resnet_model.py:215-320)."""
+    from distributedtf_b200.models import resnet
+    from distributedtf_b200.models.resnet_native_bottleneck import (NativeResNetBottleneckEngine,
+                                                                    NativeResNetBottleneckV1Engine)
+    from distributedtf_b200.utils.data import cifar_preprocess_torch
+    cls = NativeResNetBottleneckEngine if version == 2 else NativeResNetBottleneckV1Engine
+    cfg = resnet.cifar10_config(size, resnet_version=version, bottleneck=True)
+    hp = {"opt_case": {"optimizer": "Momentum", "lr": 0.1, "momentum": 0.9}, "decay_steps": 20, "decay_rate": 0.1,
+          "weight_decay": 2e-4, "regularizer": "l2_regularizer", "initializer": "he_init", "batch_size": nb}
+    eng = cls(cfg, hp, "cuda", seed=5, use_graphs=False)
+    named = {k: v.clone() for k, v in eng.export_named().items()}
+    assert sorted(named) == sorted(s.name for s in resnet.param_specs(cfg))
+    assert named["dense/kernel"].shape == (10, 256)
+    g = torch.Generator().manual_seed(1)
+    imgs = torch.randint(0, 256, (nb, 32, 32, 3), dtype=torch.uint8, generator=g).cuda()
+    labels = torch.randint(0, 10, (nb,), generator=g).cuda()
+    loss = eng.train_step_u8(imgs, labels, augment=False)
+    torch.cuda.synchronize()
+    x = cifar_preprocess_torch(imgs, False).bfloat16().float().permute(0, 3, 1, 2)
+    params = {k: v.clone().requires_grad_(v.dtype.is_floating_point and "moving" not in k) for k, v in named.items()}
+    logits = resnet.forward(cfg, params, x, True, emulate_bf16=True)
+    ref_loss = F.cross_entropy(logits, labels)
+    ref_loss.backward()
+    close(eng.logits[:nb], logits.detach(), 5e-2, 5e-2, "logits")
+    close(loss, ref_loss.detach().reshape(1), 2e-2, 2e-2, "loss")
+    grads = eng.export_named(eng.grads)
+    cosines, report = [], []
+    for k, p in params.items():
+        if not p.requires_grad:
+            continue
+        err = ((grads[k] - p.grad).norm() / (p.grad.norm() + 1e-8)).item()
+        cos = F.cosine_similarity(grads[k].reshape(1, -1), p.grad.reshape(1, -1)).item()
+        cosines.append(cos)
+        report.append(f"{k}:{err:.3f}/{cos:.3f}")
+    print(f"bottleneck v{version} relative gradient errors / cosines:", " ".join(report))
+    for k in ("dense/kernel", "dense/bias"):
+        assert ((grads[k] - params[k].grad).norm() / params[k].grad.norm()).item() < 0.02, k
+    # same envelope as the building-block engines (ReLU-mask flips of bf16 pre-activations, see the v2 test)
+    assert min(cosines) > 0.6 and sum(cosines) / len(cosines) > 0.9, " ".join(report)
+    after = eng.export_named()
+    for k in named:
+        if "moving" in k:
+            close(after[k], params[k], 2e-2, 2e-3, k)
+    for k, p in params.items():                      # Momentum + l2 applied to the engine's own gradients
+        if p.requires_grad:
+            gtot = grads[k] + (2e-4 * named[k] if "conv" in k else 0)
+            close(after[k], named[k] - 0.1 * nb / 128 * gtot, 1e-4, 1e-6, f"updated {k}")
+    # graph replay keeps training and eval counts hits
+    eng2 = cls(cfg, hp, "cuda", seed=5, use_graphs=True)
+    losses = [eng2.train_step_u8(imgs, labels, augment=False).clone() for _ in range(25)]
+    torch.cuda.synchronize()
+    assert losses[-1].item() < 0.7 * losses[0].item(), [l.item() for l in losses]
+    assert 0 <= eng2.eval_batch_u8(imgs, labels).item() <= nb
+    print(f"bottleneck v{version} resnet-{size}: {eng.launches_per_step} launches per step")
+
+
 def test_loss_scale_is_folded_into_head_and_optimizer(nat):
     """dtype='fp16' = the reference's mixed-precision mode: static loss scale 128 applied in the head kernel and
     taken out again by the optimizer kernel (resnet_run_loop.py:284-294).  The gradients in the arena are 128 x

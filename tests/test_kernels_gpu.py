@@ -80,6 +80,11 @@ FWD_CASES = [
     (128, 32, 16, 16, 3, 1, "bn", "residual"),
     (128, 16, 32, 32, 3, 1, "bn", "residual"),
     (256, 8, 64, 64, 3, 1, "bn", "residual"),
+    # bottleneck blocks: 1x1 reduce / expand with up to 256 channels, strided projection, 3x3 stride 2 with Cin == Cout
+    (3, 8, 256, 64, 1, 1, "bn", "store"),
+    (3, 8, 64, 256, 1, 1, "bn", "residual"),
+    (3, 16, 128, 256, 1, 2, "bn", "store"),
+    (4, 16, 32, 32, 3, 2, "bn", "store"),
     (128, 32, 16, 32, 3, 2, "bn", "store"),
     (128, 32, 16, 16, 1, 1, "bn", "store"),
 ]
@@ -163,6 +168,11 @@ DGRAD_CASES = [
     (128, 16, 32, 32, 3, 1),
     (256, 8, 64, 64, 3, 1),
     (128, 32, 16, 32, 3, 2),
+    (3, 8, 256, 64, 1, 1),       # bottleneck blocks: wide 1x1 layers, strided projection, 3x3 stride 2 with Cin == Cout
+    (3, 8, 64, 256, 1, 1),
+    (3, 16, 128, 256, 1, 2),
+    (4, 16, 32, 32, 3, 2),
+    (4, 16, 64, 64, 3, 2),
 ]
 
 
@@ -241,6 +251,10 @@ WGRAD_CASES = [
     (128, 16, 32, 32, 3, 1),
     (256, 8, 64, 64, 3, 1),
     (128, 16, 32, 64, 3, 2),
+    (3, 8, 256, 64, 1, 1),       # bottleneck blocks; Cout 256 = two 128-channel halves (blockIdx.z)
+    (3, 8, 64, 256, 1, 1),
+    (3, 16, 128, 256, 1, 2),
+    (4, 16, 64, 64, 3, 2),
 ]
 
 
