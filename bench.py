@@ -48,6 +48,8 @@ def parse():
     p.add_argument("--batch", type=int, default=BATCH)
     p.add_argument("--resnet-size", type=int, default=32)
     p.add_argument("--resnet-version", type=int, default=2, choices=[1, 2])
+    p.add_argument("--dtype", default="bf16", choices=["bf16", "tf32"],
+                   help="native arm: bf16 operands (headline) or fp32 tensors with tf32 tensor-core math")
     p.add_argument("--bottleneck", action="store_true", help="bottleneck blocks (resnet-size 9n + 2); not the headline")
     p.add_argument("--dp-size", type=int, default=1, choices=[1, 2, 4],
                    help="GPUs per member (BASELINE config 4: population N/D x data-parallel D)")
@@ -296,7 +298,7 @@ def main():
             return symm_buf.alloc_state(n)
 
         eng = NativeResNetEngine(cfg, hp, dev, seed=1234 + member_id, use_graphs=not args.no_graphs,
-                                 arena_alloc=alloc, dp_group=dp_group)
+                                 arena_alloc=alloc, dp_group=dp_group, dtype=args.dtype)
         if world > 1:
             symm.exchange_directory({rank: symm_buf.buf})
             for r in range(world):                       # map every peer's buffer now (cudaIpcOpenMemHandle is
@@ -575,7 +577,7 @@ def main():
         out = {
             "metric": METRIC, "value": value, "unit": "images/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
+            "scaling": "weak", "vs_baseline": None, "dtype": args.dtype if args.impl == "native" else "bf16",
             "data": "synthetic uint8 CIFAR-10-shaped images (random), random labels, random-init weights",
             "impl": args.impl,
             "config": {"model": f"CIFAR-10 ResNet-{args.resnet_size} v{args.resnet_version} (resnet_model, "

@@ -156,6 +156,18 @@ DTF_DEVINL void pack_store2(const DtfOptSegment& s, dtf_bf16* pack, int local, f
     const int rest = local / s.Cin;
     const int tap = rest % s.taps;
     const int co = rest / s.taps;
+    if (s.pack == 3) {            // fp32 operands (tf32 MMA): [K/4][N][4] floats (elementwise.cu: pack_store)
+        float* pf = reinterpret_cast<float*>(pack);
+        if (s.fwd_pack_off >= 0) {
+            const int k = tap * s.Cin + ci;
+            pf[s.fwd_pack_off + ((k >> 2) * s.Cout + co) * 4 + (k & 3)] = w;
+        }
+        if (s.dgrad_pack_off >= 0) {
+            const int k = tap * s.Cout + co;
+            pf[s.dgrad_pack_off + ((k >> 2) * s.Cin + ci) * 4 + (k & 3)] = w;
+        }
+        return;
+    }
     const dtf_bf16 h = __float2bfloat16(w);
     if (s.fwd_pack_off >= 0) {
         const int k = tap * s.Cin + ci;

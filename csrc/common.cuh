@@ -153,6 +153,19 @@ __host__ __device__ constexpr uint32_t umma_idesc_bf16(uint32_t m, uint32_t n, b
     return (1u << 4) | (1u << 7) | (1u << 10) | ((a_mn ? 1u : 0u) << 15) | ((b_mn ? 1u : 0u) << 16) |
            ((n >> 3) << 17) | ((m >> 4) << 24);
 }
+// Instruction descriptor for kind::tf32 (fp32 storage, tf32 multiply, fp32 accumulate): a/b format 2.  One MMA
+// covers K = 8 elements = the same 32 bytes per row as 16 bf16, so the operand byte layouts are shared.
+__host__ __device__ constexpr uint32_t umma_idesc_tf32(uint32_t m, uint32_t n, bool a_mn, bool b_mn) {
+    return (1u << 4) | (2u << 7) | (2u << 10) | ((a_mn ? 1u : 0u) << 15) | ((b_mn ? 1u : 0u) << 16) |
+           ((n >> 3) << 17) | ((m >> 4) << 24);
+}
+DTF_DEVINL void umma_tf32(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
+}
 // D[tmem] (+)= A[smem] * B[smem]   — issued by ONE thread.
 DTF_DEVINL void umma_bf16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
     asm volatile(

@@ -763,6 +763,7 @@ static int prep_fwd(const DtfConvGemm* p, dtf::HaloGeom* Gout, int* smem_out) {
     const DtfGather& a = p->a;
     if (halo_disabled()) return 0;
     if (a.KH != 3 || a.KW != 3 || a.stride != 1 || a.pad != 1) return 0;
+    if (a.dtype != DTF_BF16) return 0;                           // fp32 tensors: generic kernels (conv_sm100.cu)
     if (a.C % 16 != 0 || a.C > 64 || p->N != a.C) return 0;      // kernel is specialised for Cout == Cin
     if (a.Hs != p->Ho || a.Ws != p->Wo) return 0;
     HaloGeom G{};
@@ -809,6 +810,7 @@ static int prep_wgrad(const DtfConvWgrad* p, dtf::HaloGeom* Gout, int* smem_out,
     const DtfGather& x = p->x;
     if (halo_disabled()) return 0;
     if (x.KH != 3 || x.KW != 3 || x.stride != 1 || x.pad != 1) return 0;
+    if (x.dtype != DTF_BF16) return 0;
     if (x.C % 16 != 0 || x.C > 64 || p->Cout % 8 != 0 || p->Cout > 128) return 0;
     if (x.Hs != p->Ho || x.Ws != p->Wo) return 0;
     HaloGeom G{};

@@ -116,7 +116,44 @@ struct GatherLoad {
     bool ok;          // false: padding / out-of-range chunk, stays zero
 };
 
-template <bool TWO>
+// E = elements per 16-byte chunk: 8 (bf16) or 4 (fp32 storage, tf32 MMA).  The structs type every tensor pointer
+// as dtf_bf16*; elem_ptr<E> turns an element offset into the address for the launch's element type.
+template <int E>
+DTF_DEVINL const dtf_bf16* elem_ptr(const dtf_bf16* base, size_t elem) {
+    return reinterpret_cast<const dtf_bf16*>(reinterpret_cast<const char*>(base) + elem * (16 / E));
+}
+template <int E>
+DTF_DEVINL dtf_bf16* elem_ptr(dtf_bf16* base, size_t elem) {
+    return reinterpret_cast<dtf_bf16*>(reinterpret_cast<char*>(base) + elem * (16 / E));
+}
+template <int E>
+DTF_DEVINL void unpack_chunk(const uint4& q, float* f) {
+    if (E == 8) {
+        unpack8(q, f);
+    } else {
+        f[0] = __uint_as_float(q.x); f[1] = __uint_as_float(q.y);
+        f[2] = __uint_as_float(q.z); f[3] = __uint_as_float(q.w);
+    }
+}
+template <int E>
+DTF_DEVINL uint4 pack_chunk(const float* f) {
+    if (E == 8) return pack8(f);
+    return make_uint4(__float_as_uint(f[0]), __float_as_uint(f[1]), __float_as_uint(f[2]), __float_as_uint(f[3]));
+}
+// 16 consecutive elements <-> 16 floats (two chunks of bf16, four of fp32)
+template <int E>
+DTF_DEVINL void load16(const dtf_bf16* base, size_t elem, float* f) {
+#pragma unroll
+    for (int i = 0; i < 16 / E; ++i) unpack_chunk<E>(ldg16(elem_ptr<E>(base, elem + i * E)), f + i * E);
+}
+template <int E>
+DTF_DEVINL void store16(dtf_bf16* base, size_t elem, const float* f) {
+    uint4* o = reinterpret_cast<uint4*>(elem_ptr<E>(base, elem));
+#pragma unroll
+    for (int i = 0; i < 16 / E; ++i) o[i] = pack_chunk<E>(f + i * E);
+}
+
+template <bool TWO, int E = 8>
 DTF_DEVINL void gather_issue(const DtfGather& g, const int8_t* tap_dy, const int8_t* tap_dx,
                              const RowCoord& rc, int jg, GatherLoad& L) {
     L.raw = make_uint4(0, 0, 0, 0);
@@ -139,29 +176,30 @@ DTF_DEVINL void gather_issue(const DtfGather& g, const int8_t* tap_dy, const int
         sx = tx / g.stride;
     }
     if (sy < 0 || sy >= g.Hs || sx < 0 || sx >= g.Ws) return;
-    const size_t off = ((static_cast<size_t>(rc.n) * g.Hs + sy) * g.Ws + sx) * g.C + c8 * 8;
-    L.raw = ldg16(g.src + off);
-    if (TWO) L.x = ldg16(g.src2 + off);
-    L.cb = c8 * 8;
+    const size_t off = ((static_cast<size_t>(rc.n) * g.Hs + sy) * g.Ws + sx) * g.C + c8 * E;
+    L.raw = ldg16(elem_ptr<E>(g.src, off));
+    if (TWO) L.x = ldg16(elem_ptr<E>(g.src2, off));
+    L.cb = c8 * E;
     L.ok = true;
 }
 
+template <int E = 8>
 DTF_DEVINL uint4 gather_finish(const DtfGather& g, const float* p0, const float* p1, const float* p2,
                                const GatherLoad& L) {
     if (!L.ok || g.mode == DTF_PRO_NONE) return L.raw;
-    float f[8];
-    unpack8(L.raw, f);
+    float f[E];
+    unpack_chunk<E>(L.raw, f);
     const int cb = L.cb;
     if (g.mode == DTF_PRO_BN_RELU) {
 #pragma unroll
-        for (int i = 0; i < 8; ++i) f[i] = fmaxf(fmaf(f[i], p0[cb + i], p1[cb + i]), 0.f);
+        for (int i = 0; i < E; ++i) f[i] = fmaxf(fmaf(f[i], p0[cb + i], p1[cb + i]), 0.f);
     } else {
-        float x[8];
-        unpack8(L.x, x);
+        float x[E];
+        unpack_chunk<E>(L.x, x);
 #pragma unroll
-        for (int i = 0; i < 8; ++i) f[i] = fmaf(f[i], p0[cb + i], fmaf(x[i], p1[cb + i], p2[cb + i]));
+        for (int i = 0; i < E; ++i) f[i] = fmaf(f[i], p0[cb + i], fmaf(x[i], p1[cb + i], p2[cb + i]));
     }
-    return pack8(f);
+    return pack_chunk<E>(f);
 }
 
 DTF_DEVINL uint4 gather16(const DtfGather& g, const int8_t* tap_dy, const int8_t* tap_dx,
@@ -170,7 +208,7 @@ DTF_DEVINL uint4 gather16(const DtfGather& g, const int8_t* tap_dy, const int8_t
     GatherLoad L;
     if (g.mode == DTF_PRO_BN_BWD) gather_issue<true>(g, tap_dy, tap_dx, rc, jg, L);
     else gather_issue<false>(g, tap_dy, tap_dx, rc, jg, L);
-    return gather_finish(g, p0, p1, p2, L);
+    return gather_finish<8>(g, p0, p1, p2, L);
 }
 
 // ---- row gather, tap-major ---------------------------------------------------------------
@@ -300,7 +338,7 @@ DTF_DEVINL void gather_chunks_slow(const DtfGather& g, const int8_t* tap_dy, con
 // Wide channel counts (128 / 256: the 1x1 convolutions of bottleneck blocks): the chunks of a row are taken in
 // batches whose loads are all in flight before the first one is consumed (8 x 16 bytes per source, 4 with the
 // second source of the BN-backward prologue).
-template <bool TWO>
+template <bool TWO, int E = 8>
 DTF_DEVINL void gather_chunks_wide(const DtfGather& g, const int8_t* tap_dy, const int8_t* tap_dx,
                                    const float* p0, const float* p1, const float* p2, const RowCoord& rc,
                                    int jbeg, int jend, uint32_t dst) {
@@ -308,16 +346,23 @@ DTF_DEVINL void gather_chunks_wide(const DtfGather& g, const int8_t* tap_dy, con
     for (int j = jbeg; j < jend; j += B) {
         GatherLoad L[B];
 #pragma unroll
-        for (int u = 0; u < B; ++u) gather_issue<TWO>(g, tap_dy, tap_dx, rc, j + u < jend ? j + u : g.kchunks_real, L[u]);
+        for (int u = 0; u < B; ++u)
+            gather_issue<TWO, E>(g, tap_dy, tap_dx, rc, j + u < jend ? j + u : g.kchunks_real, L[u]);
 #pragma unroll
         for (int u = 0; u < B; ++u)
-            if (j + u < jend) sts16(dst + (j + u - jbeg) * (kTileM * 16), gather_finish(g, p0, p1, p2, L[u]));
+            if (j + u < jend) sts16(dst + (j + u - jbeg) * (kTileM * 16), gather_finish<E>(g, p0, p1, p2, L[u]));
     }
 }
 
+template <int E = 8>
 DTF_DEVINL void gather_row(const DtfGather& g, const int8_t* tap_dy, const int8_t* tap_dx,
                            const float* p0, const float* p1, const float* p2, const RowCoord& rc,
                            int jbeg, int jend, uint32_t dst) {
+    if (E != 8) {          // fp32 tensors: every layer takes the batched generic path
+        if (g.mode == DTF_PRO_BN_BWD) gather_chunks_wide<true, E>(g, tap_dy, tap_dx, p0, p1, p2, rc, jbeg, jend, dst);
+        else gather_chunks_wide<false, E>(g, tap_dy, tap_dx, p0, p1, p2, rc, jbeg, jend, dst);
+        return;
+    }
     if (g.stride > 2) {
         gather_chunks_slow(g, tap_dy, tap_dx, p0, p1, p2, rc, jbeg, jend, dst);
         return;
@@ -423,6 +468,7 @@ DTF_DEVINL const dtf_bf16* epilogue_aux_ptr(const DtfConvGemm& P) {
 
 // acc1/acc2 (optional): per-thread running sums of the two statistics for THIS 16-column group;
 // when given, the warp butterfly is skipped here and done once per CTA by the caller.
+template <int E = 8>
 DTF_DEVINL void epilogue_group(const DtfConvGemm& P, SmemConsts* cst, float* v, bool valid, size_t obase,
                                int cg, int lane, const uint4* aux = nullptr, float* acc1 = nullptr,
                                float* acc2 = nullptr, float* wb = nullptr) {
@@ -430,8 +476,8 @@ DTF_DEVINL void epilogue_group(const DtfConvGemm& P, SmemConsts* cst, float* v, 
     if (P.epi_mode == DTF_EPI_RESIDUAL) {
         if (valid) {
             float r[16];
-            unpack8(aux ? aux[0] : ldg16(P.epi_res + obase + cg), r);
-            unpack8(aux ? aux[1] : ldg16(P.epi_res + obase + cg + 8), r + 8);
+            if (E == 8 && aux) { unpack8(aux[0], r); unpack8(aux[1], r + 8); }
+            else load16<E>(P.epi_res, obase + cg, r);
 #pragma unroll
             for (int i = 0; i < 16; ++i) v[i] += r[i];
         }
@@ -444,14 +490,11 @@ DTF_DEVINL void epilogue_group(const DtfConvGemm& P, SmemConsts* cst, float* v, 
     } else if (P.epi_mode == DTF_EPI_RELU_MASK) {
         float x[16];
         if (valid) {
-            unpack8(aux ? aux[0] : ldg16(P.epi_x + obase + cg), x);
-            unpack8(aux ? aux[1] : ldg16(P.epi_x + obase + cg + 8), x + 8);
+            if (E == 8 && aux) { unpack8(aux[0], x); unpack8(aux[1], x + 8); }
+            else load16<E>(P.epi_x, obase + cg, x);
         }
         float old[16];
-        if (P.epi_accumulate && valid) {
-            unpack8(ldg16(P.out + obase + cg), old);
-            unpack8(ldg16(P.out + obase + cg + 8), old + 8);
-        }
+        if (P.epi_accumulate && valid) load16<E>(P.out, obase + cg, old);
         float s1[16];
 #pragma unroll
         for (int i = 0; i < 16; ++i) {
@@ -487,11 +530,7 @@ DTF_DEVINL void epilogue_group(const DtfConvGemm& P, SmemConsts* cst, float* v, 
             flush_stats16(cst, s1, s2, cg, lane, wb);
         }
     }
-    if (valid) {
-        uint4* o = reinterpret_cast<uint4*>(P.out + obase + cg);
-        o[0] = pack8(v);
-        o[1] = pack8(v + 8);
-    }
+    if (valid) store16<E>(P.out, obase + cg, v);
 }
 
 // 32-bit division by a runtime constant (host-precomputed): q = (mulhi(n, m) + n) >> s for n < 2^31

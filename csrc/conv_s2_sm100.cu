@@ -315,7 +315,7 @@ extern "C" int dtf_conv_s2_dgrad_try(const DtfConvGemm* p, cudaStream_t stream) 
     if (disabled < 0) disabled = getenv("DTF_CONV_GENERIC") != nullptr ? 1 : 0;
     if (disabled) return 0;
     const DtfGather& g = p->a;
-    if (!g.transposed || g.stride != 2 || g.KH != g.KW) return 0;
+    if (g.dtype != DTF_BF16 || !g.transposed || g.stride != 2 || g.KH != g.KW) return 0;
     const bool k3 = g.KH == 3 && g.pad == 1, k1 = g.KH == 1 && g.pad == 0;
     if (!k3 && !k1) return 0;
     if (k1 && !(p->epi_mode == DTF_EPI_RELU_MASK && p->epi_accumulate)) return 0;   // 3/4 of `out` is not written

@@ -30,6 +30,9 @@ namespace dtf {
 // =========================================================================================
 // forward / dgrad kernel:  out[M][N] = epilogue( gather(A)[M][K] * Wpacked[N][K]^T )
 // =========================================================================================
+// E = elements per 16-byte chunk: 8 = bf16 tensors (kind::f16), 4 = fp32 tensors (kind::tf32).  Both consume two
+// chunks (32 bytes of K per row) per MMA, so the shared-memory layouts and descriptors are the same.
+template <int E>
 __global__ void __launch_bounds__(kThreads, 1)
 conv_gemm_kernel(const __grid_constant__ DtfConvGemm P) {
     extern __shared__ __align__(1024) uint8_t smem[];
@@ -85,7 +88,7 @@ conv_gemm_kernel(const __grid_constant__ DtfConvGemm P) {
         }
         __syncwarp();
         mbar_wait(smem_u32(&hdr->bfull), 0, 1);
-        const uint32_t idesc = umma_idesc_bf16(kTileM, N, false, false);
+        const uint32_t idesc = E == 8 ? umma_idesc_bf16(kTileM, N, false, false) : umma_idesc_tf32(kTileM, N, false, false);
         uint32_t it = 0, local_tile = 0;
         for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local_tile) {
             const uint32_t a = local_tile & 1;
@@ -102,7 +105,10 @@ conv_gemm_kernel(const __grid_constant__ DtfConvGemm P) {
                 for (int ks = 0; ks < nch / 2; ++ks) {
                     const uint64_t adesc = umma_desc(a_base + ks * 2 * kChunkBytes, kChunkBytes, 128);
                     const uint64_t bdesc = umma_desc(b_base + ks * 2 * N * 16, N * 16, 128);
-                    if (elect_one()) umma_bf16(d_tmem, adesc, bdesc, idesc, (kb | ks) != 0);
+                    if (elect_one()) {
+                        if (E == 8) umma_bf16(d_tmem, adesc, bdesc, idesc, (kb | ks) != 0);
+                        else umma_tf32(d_tmem, adesc, bdesc, idesc, (kb | ks) != 0);
+                    }
                 }
                 if (elect_one()) {
                     umma_commit(smem_u32(&hdr->empty[buf]));
@@ -124,8 +130,8 @@ conv_gemm_kernel(const __grid_constant__ DtfConvGemm P) {
                 mbar_wait(smem_u32(&hdr->empty[group]), ((it >> 1) & 1) ^ 1, 4);
                 const int nch = min(kb_chunks, P.kchunks - kb * kb_chunks);
                 const uint32_t dst = smem_u32(smem_a) + group * kb_chunks * kChunkBytes + row * 16;
-                gather_row(P.a, hdr->tap_dy, hdr->tap_dx, cst->p0, cst->p1, cst->p2, rc, kb * kb_chunks,
-                           kb * kb_chunks + nch, dst);
+                gather_row<E>(P.a, hdr->tap_dy, hdr->tap_dx, cst->p0, cst->p1, cst->p2, rc, kb * kb_chunks,
+                              kb * kb_chunks + nch, dst);
                 fence_proxy_async_smem();
                 mbar_arrive(smem_u32(&hdr->full[group]));
             }
@@ -150,12 +156,12 @@ conv_gemm_kernel(const __grid_constant__ DtfConvGemm P) {
             if (reg_stats) {
                 float v[16];
                 tmem_ld16(tmem_base + ((warp * 32u) << 16) + a * N, v);
-                epilogue_group(P, cst, v, valid, obase, 0, lane, nullptr, acc1, acc2);
+                epilogue_group<E>(P, cst, v, valid, obase, 0, lane, nullptr, acc1, acc2);
             } else {
                 for (int cg = 0; cg < N; cg += 16) {
                     float v[16];
                     tmem_ld16(tmem_base + ((warp * 32u) << 16) + a * N + cg, v);
-                    epilogue_group(P, cst, v, valid, obase, cg, lane);
+                    epilogue_group<E>(P, cst, v, valid, obase, cg, lane);
                 }
             }
             tc_fence_before_sync();
@@ -182,8 +188,11 @@ conv_gemm_kernel(const __grid_constant__ DtfConvGemm P) {
 // wgrad kernel:  dW[co][j*8+e] += sum over pixels  gy'[pixel][co] * im2col(act(x))[pixel][j*8+e]
 //   blockIdx.y selects a contiguous range of im2col chunks (<= 32 chunks = 256 columns).
 // =========================================================================================
+template <int E>
 __global__ void __launch_bounds__(kThreads, 1)
 conv_wgrad_kernel(const __grid_constant__ DtfConvWgrad P) {
+    constexpr int kCoChunks = 128 / E;          // channel chunks of one 128-channel M block
+    constexpr int kStepRows = E == 8 ? 16 : 8;  // pixels (K) per MMA: 32 bytes of K per channel
     extern __shared__ __align__(1024) uint8_t smem[];
     SmemHeader* hdr = reinterpret_cast<SmemHeader*>(smem);
     SmemConsts* cst = reinterpret_cast<SmemConsts*>(smem + 1024);
@@ -196,11 +205,11 @@ conv_wgrad_kernel(const __grid_constant__ DtfConvWgrad P) {
     const int num_tiles = (M + kTileM - 1) / kTileM;
     const int j0 = blockIdx.y * P.chunks_per_cta;
     const int nj = min(P.chunks_per_cta, P.kchunks - j0);            // real+pad chunks of this CTA (even)
-    const int ncols = nj * 8;                                         // UMMA N
+    const int ncols = nj * E;                                         // UMMA N
     // blockIdx.z selects 128 output channels (Cout up to 256: the expanding 1x1 convolutions of bottleneck blocks)
-    const int co_chunk0 = blockIdx.z * 16;
-    const int gy_chunks = min(P.Cout / 8 - co_chunk0, 16);
-    const uint32_t buf_bytes = static_cast<uint32_t>(min(P.Cout / 8, 16) + P.chunks_per_cta) * kChunkBytes;
+    const int co_chunk0 = blockIdx.z * kCoChunks;
+    const int gy_chunks = min(P.Cout / E - co_chunk0, kCoChunks);
+    const uint32_t buf_bytes = static_cast<uint32_t>(min(P.Cout / E, kCoChunks) + P.chunks_per_cta) * kChunkBytes;
     const uint32_t acc_cols = tmem_cols_pow2(ncols);
 
     if (tid == 0) {
@@ -226,7 +235,7 @@ conv_wgrad_kernel(const __grid_constant__ DtfConvWgrad P) {
     if (warp == kMmaWarp) {
         if (has_work) {
             // A = gy' viewed MN-major (M index = channel, 8 per 16-byte row), B = im2col MN-major.
-            const uint32_t idesc = umma_idesc_bf16(kTileM, ncols, true, true);
+            const uint32_t idesc = E == 8 ? umma_idesc_bf16(kTileM, ncols, true, true) : umma_idesc_tf32(kTileM, ncols, true, true);
             uint32_t it = 0;
             for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
                 const uint32_t buf = it & 1;
@@ -234,11 +243,15 @@ conv_wgrad_kernel(const __grid_constant__ DtfConvWgrad P) {
                 tc_fence_after_sync();
                 const uint32_t a_base = smem_u32(smem_ab) + buf * buf_bytes;
                 const uint32_t b_base = a_base + gy_chunks * kChunkBytes;
-                for (int ks = 0; ks < kTileM / 16; ++ks) {
-                    // K step = 16 pixels = 2 groups of 8 rows (LBO = 128); channel chunks SBO apart
-                    const uint64_t adesc = umma_desc(a_base + ks * 256, 128, kChunkBytes);
-                    const uint64_t bdesc = umma_desc(b_base + ks * 256, 128, kChunkBytes);
-                    if (elect_one()) umma_bf16(tmem_base, adesc, bdesc, idesc, (it | ks) != 0);
+                for (int ks = 0; ks < kTileM / kStepRows; ++ks) {
+                    // K step = 16 pixels = 2 groups of 8 rows (LBO = 128) for bf16, one group of 8 rows for tf32;
+                    // channel chunks SBO apart
+                    const uint64_t adesc = umma_desc(a_base + ks * kStepRows * 16, 128, kChunkBytes);
+                    const uint64_t bdesc = umma_desc(b_base + ks * kStepRows * 16, 128, kChunkBytes);
+                    if (elect_one()) {
+                        if (E == 8) umma_bf16(tmem_base, adesc, bdesc, idesc, (it | ks) != 0);
+                        else umma_tf32(tmem_base, adesc, bdesc, idesc, (it | ks) != 0);
+                    }
                 }
                 if (elect_one()) umma_commit(smem_u32(&hdr->empty[buf]));
                 __syncwarp();
@@ -257,7 +270,7 @@ conv_wgrad_kernel(const __grid_constant__ DtfConvWgrad P) {
             mbar_wait(smem_u32(&hdr->empty[group]), ((it >> 1) & 1) ^ 1, 7);
             const uint32_t a_dst = smem_u32(smem_ab) + group * buf_bytes + row * 16;
             const uint32_t b_dst = a_dst + gy_chunks * kChunkBytes;
-            gather_row(P.x, hdr->tap_dy, hdr->tap_dx, cst->p0, cst->p1, cst->p2, rc, j0, j0 + nj, b_dst);
+            gather_row<E>(P.x, hdr->tap_dy, hdr->tap_dx, cst->p0, cst->p1, cst->p2, rc, j0, j0 + nj, b_dst);
             fence_proxy_async_smem();
             mbar_arrive(smem_u32(&hdr->full[group]));
         }
@@ -272,21 +285,21 @@ conv_wgrad_kernel(const __grid_constant__ DtfConvWgrad P) {
                 const RowCoord rc = row_coord(tile * kTileM + row, M, P.Ho, P.Wo);
                 mbar_wait(smem_u32(&hdr->empty[buf]), ((it >> 1) & 1) ^ 1, 9);
                 const uint32_t a_dst = smem_u32(smem_ab) + buf * buf_bytes + row * 16;
-                gather_row(P.gy, hdr->tap_dy + 31, hdr->tap_dx + 31, cst->q0, cst->q1, cst->q2, rc, co_chunk0,
-                           co_chunk0 + gy_chunks, a_dst);
+                gather_row<E>(P.gy, hdr->tap_dy + 31, hdr->tap_dx + 31, cst->q0, cst->q1, cst->q2, rc, co_chunk0,
+                              co_chunk0 + gy_chunks, a_dst);
                 fence_proxy_async_smem();
                 mbar_arrive(smem_u32(&hdr->full[buf]));
             }
         }
         mbar_wait(smem_u32(&hdr->acc_full[0]), 0, 8);
         tc_fence_after_sync();
-        const int co = co_chunk0 * 8 + warp * 32 + lane;   // TMEM lane = output channel
-        const int kreal = P.kchunks_real * 8;
+        const int co = co_chunk0 * E + warp * 32 + lane;   // TMEM lane = output channel
+        const int kreal = P.kchunks_real * E;
         for (int cg = 0; cg < ncols; cg += 8) {
             float v[8];
             tmem_ld8(tmem_base + ((warp * 32u) << 16) + cg, v);   // whole warp executes the load
             if (co < P.Cout) {
-                const int k = j0 * 8 + cg;
+                const int k = j0 * E + cg;
 #pragma unroll
                 for (int i = 0; i < 8; ++i)
                     if (k + i < kreal) atomicAdd(P.dw + static_cast<size_t>(co) * kreal + k + i, v[i]);
@@ -332,8 +345,10 @@ static int ilog2_exact(int v) {
 }
 
 static int prep_gather(DtfGather* g) {
-    if (g->C % 8 != 0) return DTF_ERR_SHAPE;
-    const int cpt = g->C / 8;
+    if (g->dtype != DTF_BF16 && g->dtype != DTF_F32) return DTF_ERR_ARG;
+    const int E = g->dtype == DTF_F32 ? 4 : 8;           // elements per 16-byte chunk
+    if (g->C % E != 0) return DTF_ERR_SHAPE;
+    const int cpt = g->C / E;
     g->cpt_shift = ilog2_exact(cpt);
     if (g->cpt_shift < 0) return DTF_ERR_SHAPE;
     if (g->KH * g->KW > 31) return DTF_ERR_SHAPE;
@@ -352,12 +367,15 @@ extern "C" int dtf_conv_gemm(DtfConvGemm* p, cudaStream_t stream) {
     if (rc != DTF_OK) return rc;
     if (p->N % 16 != 0 || p->N < 16 || p->N > 256) return DTF_ERR_SHAPE;
     p->kchunks = (p->a.kchunks_real + 1) & ~1;
-    // 3x3 / stride 1: halo-tile kernel with shifted descriptor views (conv3x3_sm100.cu)
-    rc = dtf_conv3x3_try(p, stream);
-    if (rc != 0) return rc > 0 ? DTF_OK : rc;
-    // stride-2 input gradient: parity-class kernel (conv_s2_sm100.cu)
-    rc = dtf_conv_s2_dgrad_try(p, stream);
-    if (rc != 0) return rc > 0 ? DTF_OK : rc;
+    const bool f32 = p->a.dtype == DTF_F32;
+    if (!f32) {
+        // 3x3 / stride 1: halo-tile kernel with shifted descriptor views (conv3x3_sm100.cu)
+        rc = dtf_conv3x3_try(p, stream);
+        if (rc != 0) return rc > 0 ? DTF_OK : rc;
+        // stride-2 input gradient: parity-class kernel (conv_s2_sm100.cu)
+        rc = dtf_conv_s2_dgrad_try(p, stream);
+        if (rc != 0) return rc > 0 ? DTF_OK : rc;
+    }
     // operand buffer: as many chunks as fit next to the weights, even, <= kchunks
     const int header = 1024 + static_cast<int>(sizeof(SmemConsts));
     const int b_off = (header + 1023) & ~1023;
@@ -376,12 +394,14 @@ extern "C" int dtf_conv_gemm(DtfConvGemm* p, cudaStream_t stream) {
     const int tiles = (M + kTileM - 1) / kTileM;
     const int grid = tiles < num_sms() ? tiles : num_sms();
     static int max_set = 0;
-    if (smem_bytes > max_set) {
-        cudaError_t e = cudaFuncSetAttribute(conv_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-        if (e != cudaSuccess) return DTF_ERR_CUDA;
-        max_set = 227 * 1024;
+    if (!max_set) {
+        if (cudaFuncSetAttribute(conv_gemm_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess ||
+            cudaFuncSetAttribute(conv_gemm_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess)
+            return DTF_ERR_CUDA;
+        max_set = 1;
     }
-    dtf_launch(conv_gemm_kernel, dim3(grid), dim3(kThreads), smem_bytes, stream, *p);
+    if (f32) dtf_launch(conv_gemm_kernel<4>, dim3(grid), dim3(kThreads), smem_bytes, stream, *p);
+    else dtf_launch(conv_gemm_kernel<8>, dim3(grid), dim3(kThreads), smem_bytes, stream, *p);
     return cudaGetLastError() == cudaSuccess ? DTF_OK : DTF_ERR_CUDA;
 }
 
@@ -391,26 +411,33 @@ extern "C" int dtf_conv_wgrad(DtfConvWgrad* p, cudaStream_t stream) {
     if (rc != DTF_OK) return rc;
     // gy side: 1x1 gather at the output pixel
     p->gy.KH = p->gy.KW = 1; p->gy.stride = 1; p->gy.pad = 0; p->gy.transposed = 0;
-    p->gy.Hs = p->Ho; p->gy.Ws = p->Wo; p->gy.C = p->Cout;
+    p->gy.Hs = p->Ho; p->gy.Ws = p->Wo; p->gy.C = p->Cout; p->gy.dtype = p->x.dtype;
     rc = prep_gather(&p->gy);
     if (rc != DTF_OK) return rc;
+    const bool f32 = p->x.dtype == DTF_F32;
+    const int E = f32 ? 4 : 8;
     if (p->Cout % 8 != 0 || p->Cout > 256) return DTF_ERR_SHAPE;
     p->kchunks_real = p->x.kchunks_real;
-    p->kchunks = (p->kchunks_real + 1) & ~1;
-    rc = dtf_conv3x3_wgrad_try(p, stream);
-    if (rc != 0) return rc > 0 ? DTF_OK : rc;
-    // columns per CTA: <= 24 chunks (192 columns), even, N % 16 == 0 holds for even chunk counts
+    // UMMA N = chunks * E must be a multiple of 16: even chunk counts for bf16, multiples of four for fp32
+    const int cmask = f32 ? 3 : 1;
+    p->kchunks = (p->kchunks_real + cmask) & ~cmask;
+    if (!f32) {
+        rc = dtf_conv3x3_wgrad_try(p, stream);
+        if (rc != 0) return rc > 0 ? DTF_OK : rc;
+    }
+    // columns per CTA: <= 24 chunks of bf16 (192 columns) / 16 chunks of fp32 (64 columns)
+    const int per_max = f32 ? 16 : 24;
     int per = p->kchunks;
     int ny = 1;
-    while (per > 24) { ++ny; per = (((p->kchunks + ny - 1) / ny) + 1) & ~1; }
+    while (per > per_max) { ++ny; per = (((p->kchunks + ny - 1) / ny) + cmask) & ~cmask; }
     p->chunks_per_cta = per;
     ny = (p->kchunks + per - 1) / per;
     const int header = 1024 + static_cast<int>(sizeof(SmemConsts));
     const int a_off = (header + 1023) & ~1023;
     const int nz = (p->Cout + 127) / 128;              // 128 output channels per CTA (blockIdx.z)
-    const int buf_bytes = ((p->Cout < 128 ? p->Cout : 128) / 8 + per) * kChunkBytes;
-    // the A descriptor always spans 16 channel chunks: keep 32 KB of slack after the last buffer
-    const int smem_bytes = a_off + 2 * buf_bytes + 16 * kChunkBytes;
+    const int buf_bytes = ((p->Cout < 128 ? p->Cout : 128) / E + per) * kChunkBytes;
+    // the A descriptor always spans 128 channels (16 / 32 chunks): keep that much slack after the last buffer
+    const int smem_bytes = a_off + 2 * buf_bytes + (128 / E) * kChunkBytes;
     if (smem_bytes > 227 * 1024) return DTF_ERR_SMEM;
     p->smem_a_off = a_off;
     const int M = p->NB * p->Ho * p->Wo;
@@ -420,12 +447,14 @@ extern "C" int dtf_conv_wgrad(DtfConvWgrad* p, cudaStream_t stream) {
     if (gx > tiles) gx = tiles;
     static int set = 0;
     if (!set) {
-        cudaError_t e = cudaFuncSetAttribute(conv_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-        if (e != cudaSuccess) return DTF_ERR_CUDA;
+        if (cudaFuncSetAttribute(conv_wgrad_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess ||
+            cudaFuncSetAttribute(conv_wgrad_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess)
+            return DTF_ERR_CUDA;
         set = 1;
     }
     dim3 grid(gx, ny, nz);
-    dtf_launch(conv_wgrad_kernel, grid, dim3(kThreads), smem_bytes, stream, *p);
+    if (f32) dtf_launch(conv_wgrad_kernel<4>, grid, dim3(kThreads), smem_bytes, stream, *p);
+    else dtf_launch(conv_wgrad_kernel<8>, grid, dim3(kThreads), smem_bytes, stream, *p);
     return cudaGetLastError() == cudaSuccess ? DTF_OK : DTF_ERR_CUDA;
 }
 
@@ -441,13 +470,16 @@ extern "C" int dtf_conv_bwd(DtfConvGemm* dgrad, DtfConvWgrad* wgrad, cudaStream_
     rc = prep_gather(&wgrad->x);
     if (rc != DTF_OK) return rc;
     wgrad->gy.KH = wgrad->gy.KW = 1; wgrad->gy.stride = 1; wgrad->gy.pad = 0; wgrad->gy.transposed = 0;
-    wgrad->gy.Hs = wgrad->Ho; wgrad->gy.Ws = wgrad->Wo; wgrad->gy.C = wgrad->Cout;
+    wgrad->gy.Hs = wgrad->Ho; wgrad->gy.Ws = wgrad->Wo; wgrad->gy.C = wgrad->Cout; wgrad->gy.dtype = wgrad->x.dtype;
     rc = prep_gather(&wgrad->gy);
     if (rc != DTF_OK) return rc;
+    if (dgrad->a.dtype != wgrad->x.dtype) return DTF_ERR_ARG;
     wgrad->kchunks_real = wgrad->x.kchunks_real;
     wgrad->kchunks = (wgrad->kchunks_real + 1) & ~1;
-    rc = dtf_conv3x3_bwd_fused_try(dgrad, wgrad, stream);
-    if (rc != 0) return rc > 0 ? DTF_OK : rc;
+    if (wgrad->x.dtype == DTF_BF16) {
+        rc = dtf_conv3x3_bwd_fused_try(dgrad, wgrad, stream);
+        if (rc != 0) return rc > 0 ? DTF_OK : rc;
+    }
     rc = dtf_conv_wgrad(wgrad, stream);
     if (rc != DTF_OK) return rc;
     return dtf_conv_gemm(dgrad, stream);

@@ -30,6 +30,19 @@ DTF_DEVINL void bn_consts(const DtfBnRef& bn, int c, float& scale, float& shift,
 // ---------------------------------------------------------------------------------------
 // g[p][c] = p0[c]*t + p1[c]*x + p2[c] (+ res)      BN backward, given (sum t, sum t*xhat)
 // ---------------------------------------------------------------------------------------
+// E = elements per 16-byte vector: 8 (bf16 tensors) or 4 (fp32 tensors)
+template <int E>
+DTF_DEVINL void unpack_vec(const uint4& q, float* f) {
+    if (E == 8) unpack8(q, f);
+    else { f[0] = __uint_as_float(q.x); f[1] = __uint_as_float(q.y); f[2] = __uint_as_float(q.z); f[3] = __uint_as_float(q.w); }
+}
+template <int E>
+DTF_DEVINL uint4 pack_vec(const float* f) {
+    if (E == 8) return pack8(f);
+    return make_uint4(__float_as_uint(f[0]), __float_as_uint(f[1]), __float_as_uint(f[2]), __float_as_uint(f[3]));
+}
+
+template <int E>
 __global__ void __launch_bounds__(256)
 bn_bwd_apply_kernel(const dtf_bf16* __restrict__ t, const dtf_bf16* __restrict__ x,
                     const dtf_bf16* __restrict__ res, dtf_bf16* __restrict__ out,
@@ -47,22 +60,26 @@ bn_bwd_apply_kernel(const dtf_bf16* __restrict__ t, const dtf_bf16* __restrict__
         p2[c] = scale * (mean * invstd * mtx - mt);
     }
     __syncthreads();
-    const int cvec = C / 8;
+    const int cvec = C / E;
+    const uint4* tv = reinterpret_cast<const uint4*>(t);
+    const uint4* xv = reinterpret_cast<const uint4*>(x);
+    const uint4* rv = reinterpret_cast<const uint4*>(res);
+    uint4* ov = reinterpret_cast<uint4*>(out);
     for (long long v = blockIdx.x * (long long)blockDim.x + threadIdx.x; v < total_vec;
          v += (long long)gridDim.x * blockDim.x) {
-        const int cb = static_cast<int>(v % cvec) * 8;
-        float ft[8], fx[8];
-        unpack8(ldg16(t + v * 8), ft);
-        unpack8(ldg16(x + v * 8), fx);
+        const int cb = static_cast<int>(v % cvec) * E;
+        float ft[E], fx[E];
+        unpack_vec<E>(ldg16(tv + v), ft);
+        unpack_vec<E>(ldg16(xv + v), fx);
 #pragma unroll
-        for (int i = 0; i < 8; ++i) ft[i] = fmaf(ft[i], p0[cb + i], fmaf(fx[i], p1[cb + i], p2[cb + i]));
+        for (int i = 0; i < E; ++i) ft[i] = fmaf(ft[i], p0[cb + i], fmaf(fx[i], p1[cb + i], p2[cb + i]));
         if (res != nullptr) {
-            float fr[8];
-            unpack8(ldg16(res + v * 8), fr);
+            float fr[E];
+            unpack_vec<E>(ldg16(rv + v), fr);
 #pragma unroll
-            for (int i = 0; i < 8; ++i) ft[i] += fr[i];
+            for (int i = 0; i < E; ++i) ft[i] += fr[i];
         }
-        *reinterpret_cast<uint4*>(out + v * 8) = pack8(ft);
+        ov[v] = pack_vec<E>(ft);
     }
 }
 
@@ -218,14 +235,17 @@ head_kernel(const __grid_constant__ DtfHead P) {
         }
     }
     __syncthreads();
-    const dtf_bf16* xn = P.x + static_cast<size_t>(n) * HW * C;
+    // element type of x / t_out: bf16, or fp32 for the tf32 engine (P.dtype)
+    const bool f32 = P.dtype == DTF_F32;
+    const dtf_bf16* xn = P.x + static_cast<size_t>(n) * HW * C * (f32 ? 2 : 1);
+    const float* xnf = reinterpret_cast<const float*>(xn);
     // forward: activation + average pool (thread owns channel c = idx % C for all its elements
     // when C divides the thread count, which holds for C in {64, 128, 256})
     if (kHeadThreads % C == 0) {        // a thread keeps one channel for all its elements
         const int c = tid % C;
         float acc = 0.f;
         for (int idx = tid; idx < HW * C; idx += kHeadThreads) {
-            const float v = __bfloat162float(xn[idx]);
+            const float v = f32 ? xnf[idx] : __bfloat162float(xn[idx]);
             float a = fmaf(v, s_scale[c], s_shift[c]);
             if (P.has_bn) a = fmaxf(a, 0.f);
             acc += a;
@@ -234,7 +254,7 @@ head_kernel(const __grid_constant__ DtfHead P) {
     } else {
         for (int idx = tid; idx < HW * C; idx += kHeadThreads) {
             const int c = idx % C;
-            const float v = __bfloat162float(xn[idx]);
+            const float v = f32 ? xnf[idx] : __bfloat162float(xn[idx]);
             float a = fmaf(v, s_scale[c], s_shift[c]);
             if (P.has_bn) a = fmaxf(a, 0.f);
             atomicAdd(&pooled[c], a);
@@ -284,15 +304,16 @@ head_kernel(const __grid_constant__ DtfHead P) {
     }
     __syncthreads();
     {
-        dtf_bf16* tn = P.t_out + static_cast<size_t>(n) * HW * C;
+        dtf_bf16* tn = P.t_out + static_cast<size_t>(n) * HW * C * (f32 ? 2 : 1);
+        float* tnf = reinterpret_cast<float*>(tn);
         const bool fixed_c = kHeadThreads % C == 0;
         float a1 = 0.f, a2 = 0.f;
         for (int idx = tid; idx < HW * C; idx += kHeadThreads) {
             const int c = fixed_c ? tid % C : idx % C;
-            const float v = __bfloat162float(xn[idx]);
+            const float v = f32 ? xnf[idx] : __bfloat162float(xn[idx]);
             const bool on = !P.has_bn || fmaf(v, s_scale[c], s_shift[c]) > 0.f;
             const float t = on ? gpool[c] : 0.f;
-            tn[idx] = __float2bfloat16(t);
+            if (f32) tnf[idx] = t; else tn[idx] = __float2bfloat16(t);
             if (fixed_c) { a1 += t; a2 += t * (v - s_mean[c]) * s_invstd[c]; }
             else if (P.bwd_stats_out != nullptr) { atomicAdd(&st1[c], t); atomicAdd(&st2[c], t * (v - s_mean[c]) * s_invstd[c]); }
         }
@@ -319,6 +340,18 @@ DTF_DEVINL void pack_store(const DtfOptSegment& s, dtf_bf16* pack, int local, fl
     const int rest = local / s.Cin;
     const int tap = rest % s.taps;
     const int co = rest / s.taps;
+    if (s.pack == 3) {            // fp32 operands (tf32 MMA): [K/4][N][4] floats, offsets in floats
+        float* pf = reinterpret_cast<float*>(pack);
+        if (s.fwd_pack_off >= 0) {
+            const int k = tap * s.Cin + ci;
+            pf[s.fwd_pack_off + ((k >> 2) * s.Cout + co) * 4 + (k & 3)] = w;
+        }
+        if (s.dgrad_pack_off >= 0) {
+            const int k = tap * s.Cout + co;
+            pf[s.dgrad_pack_off + ((k >> 2) * s.Cin + ci) * 4 + (k & 3)] = w;
+        }
+        return;
+    }
     const dtf_bf16 h = __float2bfloat16(w);
     if (s.fwd_pack_off >= 0) {
         const int k = tap * s.Cin + ci;
@@ -455,6 +488,7 @@ DTF_DEVINL uint64_t splitmix64(uint64_t x) {
     return x ^ (x >> 31);
 }
 
+template <int E>
 __global__ void __launch_bounds__(256)
 preprocess_kernel(const uint8_t* __restrict__ images, const int* __restrict__ indices,
                   dtf_bf16* __restrict__ out, const int* __restrict__ crop_flip,
@@ -503,7 +537,7 @@ preprocess_kernel(const uint8_t* __restrict__ images, const int* __restrict__ in
         }
         __syncthreads();
     }
-    dtf_bf16* o = out + static_cast<size_t>(n) * H * W * 8;
+    uint4* o = reinterpret_cast<uint4*>(out) + static_cast<size_t>(n) * H * W * (8 / E);   // 8 channels per pixel
     for (int p = threadIdx.x; p < H * W; p += blockDim.x) {
         const int x = p % W, y = p / W;
         const int sx = (mode == 2) ? ((flip ? (W - 1 - x) : x) + ox - 4) : x;
@@ -519,7 +553,8 @@ preprocess_kernel(const uint8_t* __restrict__ images, const int* __restrict__ in
             }
             f[c] = v;
         }
-        *reinterpret_cast<uint4*>(o + p * 8) = pack8(f);
+#pragma unroll
+        for (int q = 0; q < 8 / E; ++q) o[p * (8 / E) + q] = pack_vec<E>(f + q * E);
     }
 }
 
@@ -530,15 +565,25 @@ preprocess_kernel(const uint8_t* __restrict__ images, const int* __restrict__ in
 // =========================================================================================
 #define DTF_CHECK_LAUNCH() (cudaGetLastError() == cudaSuccess ? DTF_OK : DTF_ERR_CUDA)
 
+extern "C" int dtf_bn_bwd_apply_dt(const dtf_bf16* t, const dtf_bf16* x, const dtf_bf16* res, dtf_bf16* out,
+                                   const DtfBnRef* bn, const float* bwd_stats, long long pixels, int C, int dtype,
+                                   cudaStream_t stream) {
+    if (C % 8 != 0 || C > 256) return DTF_ERR_SHAPE;
+    if (dtype != DTF_BF16 && dtype != DTF_F32) return DTF_ERR_ARG;
+    const long long total_vec = pixels * (C / (dtype == DTF_F32 ? 4 : 8));
+    long long blocks = (total_vec + 255) / 256;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    if (dtype == DTF_F32)
+        dtf_launch(dtf::bn_bwd_apply_kernel<4>, dim3(static_cast<int>(blocks)), dim3(256), 0, stream, t, x, res, out, *bn, bwd_stats, total_vec, C);
+    else
+        dtf_launch(dtf::bn_bwd_apply_kernel<8>, dim3(static_cast<int>(blocks)), dim3(256), 0, stream, t, x, res, out, *bn, bwd_stats, total_vec, C);
+    return DTF_CHECK_LAUNCH();
+}
+
 extern "C" int dtf_bn_bwd_apply(const dtf_bf16* t, const dtf_bf16* x, const dtf_bf16* res, dtf_bf16* out,
                                 const DtfBnRef* bn, const float* bwd_stats, long long pixels, int C,
                                 cudaStream_t stream) {
-    if (C % 8 != 0 || C > 256) return DTF_ERR_SHAPE;
-    const long long total_vec = pixels * (C / 8);
-    long long blocks = (total_vec + 255) / 256;
-    if (blocks > 148 * 8) blocks = 148 * 8;
-    dtf_launch(dtf::bn_bwd_apply_kernel, dim3(static_cast<int>(blocks)), dim3(256), 0, stream, t, x, res, out, *bn, bwd_stats, total_vec, C);
-    return DTF_CHECK_LAUNCH();
+    return dtf_bn_bwd_apply_dt(t, x, res, out, bn, bwd_stats, pixels, C, DTF_BF16, stream);
 }
 
 extern "C" int dtf_bn_act_apply(const dtf_bf16* x, const DtfBnRef* bn, const dtf_bf16* sc, const DtfBnRef* bn_sc,
@@ -614,8 +659,14 @@ extern "C" int dtf_preprocess(const uint8_t* images, const int* indices, dtf_bf1
                               int n, int H, int W, int C, int mode, unsigned long long seed,
                               unsigned long long counter, const long long* step, cudaStream_t stream) {
     if (C > 8 || n < 1) return DTF_ERR_SHAPE;
-    dtf_launch(dtf::preprocess_kernel, dim3(n), dim3(256), 0, stream, images, indices, out, crop_flip, H, W, C, mode, seed, counter,
-               static_cast<const int*>(nullptr), static_cast<int*>(nullptr), step);
+    const int dtype = mode >> 8;                  // DTF_PP_F32 in the mode word selects fp32 output
+    mode &= 0xff;
+    if (dtype == DTF_F32)
+        dtf_launch(dtf::preprocess_kernel<4>, dim3(n), dim3(256), 0, stream, images, indices, out, crop_flip, H, W, C, mode, seed, counter,
+                   static_cast<const int*>(nullptr), static_cast<int*>(nullptr), step);
+    else
+        dtf_launch(dtf::preprocess_kernel<8>, dim3(n), dim3(256), 0, stream, images, indices, out, crop_flip, H, W, C, mode, seed, counter,
+                   static_cast<const int*>(nullptr), static_cast<int*>(nullptr), step);
     return DTF_CHECK_LAUNCH();
 }
 
@@ -626,7 +677,13 @@ extern "C" int dtf_preprocess_indexed(const uint8_t* images, const int* indices,
                                       unsigned long long seed, unsigned long long counter, const long long* step,
                                       cudaStream_t stream) {
     if (C > 8 || n < 1 || indices == nullptr || labels_all == nullptr || labels_out == nullptr) return DTF_ERR_ARG;
-    dtf_launch(dtf::preprocess_kernel, dim3(n), dim3(256), 0, stream, images, indices, out, crop_flip, H, W, C, mode, seed, counter,
-               labels_all, labels_out, step);
+    const int dtype = mode >> 8;
+    mode &= 0xff;
+    if (dtype == DTF_F32)
+        dtf_launch(dtf::preprocess_kernel<4>, dim3(n), dim3(256), 0, stream, images, indices, out, crop_flip, H, W, C, mode, seed, counter,
+                   labels_all, labels_out, step);
+    else
+        dtf_launch(dtf::preprocess_kernel<8>, dim3(n), dim3(256), 0, stream, images, indices, out, crop_flip, H, W, C, mode, seed, counter,
+                   labels_all, labels_out, step);
     return DTF_CHECK_LAUNCH();
 }

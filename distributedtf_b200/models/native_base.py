@@ -136,7 +136,8 @@ class NativeEngineBase:
         self.slot0 = view("slot0", torch.float32, P)
         self.slot1 = view("slot1", torch.float32, P)
         self.running = view("running", torch.float32, self.n_running)
-        self.pack = torch.zeros(max(self.n_pack, 8), dtype=torch.bfloat16, device=dev)
+        # GEMM-ready copies of the conv kernels in the operand type of the engine (bf16, or fp32 for tf32 math)
+        self.pack = torch.zeros(max(self.n_pack, 8), dtype=getattr(self, "act_dtype", torch.bfloat16), device=dev)
         # per-step zeroed region: grads | batch statistics | loss, correct
         zfloats = P + _align(max(self.n_stats, 1) * 4) // 4 + 64
         if self.dp_group is not None and self.all_reduce_alg == "fused_p2p":

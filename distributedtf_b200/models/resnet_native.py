@@ -78,20 +78,29 @@ class Block:
 
 class NativeResNetEngine(NativeEngineBase):
     version = 2
+    supports_f32 = True
+    act_dtype = torch.bfloat16
+    E = 8
 
     def __init__(self, cfg: resnet.ResNetConfig, hparams: Dict[str, Any], device, *, seed: int = 0,
                  dtype: str = "bf16", max_batch: int = MAX_BATCH, use_graphs: bool = True,
                  arena_alloc=None, dp_group=None, all_reduce_alg=None, loss_scale: Optional[float] = None):
         self._check_config(cfg)
-        if dtype not in ("bf16", "fp16"):
-            raise NotImplementedError("native engine computes with 16-bit operands, fp32 accumulation and fp32 master "
-                                      "weights; fp32 / tf32 runs on the eager engine")
+        if dtype not in ("bf16", "fp16", "tf32", "fp32"):
+            raise NotImplementedError(f"native engine: dtype {dtype!r}")
+        if dtype in ("tf32", "fp32") and not self.supports_f32:
+            raise NotImplementedError("fp32 / tf32 tensors: v2 engines only (the v1 block-tail kernels are bf16)")
         super().__init__(device, max_batch=max_batch, use_graphs=use_graphs, arena_alloc=arena_alloc,
                          dp_group=dp_group, seed=seed, all_reduce_alg=all_reduce_alg)
         # dtype "fp16" = the reference's mixed-precision mode (fp32 master weights, static loss scale 128,
         # resnet_model.py:439-474): on B200 the 16-bit operand type is bf16 (same tensor-core rate, fp32's exponent
         # range), the loss scaling is applied exactly as specified.
-        self.compute_dtype = "bf16"
+        # dtype "fp32" / "tf32" = the reference's default dtype (flags/_performance.py:107): activations, gradients
+        # and packed weights are stored in fp32 and the convolutions run as kind::tf32 tcgen05 MMAs (10-bit mantissa
+        # products, fp32 accumulation) on the generic implicit-GEMM kernels (csrc/conv_sm100.cu, E = 4).
+        self.compute_dtype = "tf32" if dtype in ("tf32", "fp32") else "bf16"
+        self.act_dtype = torch.float32 if self.compute_dtype == "tf32" else torch.bfloat16
+        self.E = 4 if self.compute_dtype == "tf32" else 8          # elements per 16-byte operand chunk
         self.loss_scale = float(loss_scale) if loss_scale else (128.0 if dtype == "fp16" else 1.0)
         self.cfg = cfg
         self.image_size, self.image_channels = cfg.image_size, cfg.in_channels
@@ -150,16 +159,17 @@ class NativeResNetEngine(NativeEngineBase):
         for c in self.convs:
             c.w_off = off
             n = c.cout * c.k * c.k * c.cin
-            kch = c.k * c.k * c.cin // 8
+            E = self.E
+            kch = c.k * c.k * c.cin // E
             c.fwd_pack = pack
-            pack += _align(((kch + 1) & ~1) * c.cout * 8, 128)
+            pack += _align(((kch + 1) & ~1) * c.cout * E, 128)
             if c is not self.conv0:
-                kchd = c.k * c.k * c.cout // 8
+                kchd = c.k * c.k * c.cout // E
                 c.dgrad_pack = pack
-                pack += _align(((kchd + 1) & ~1) * c.cin * 8, 128)
+                pack += _align(((kchd + 1) & ~1) * c.cin * E, 128)
             c.seg = len(self.segments)
-            self.segments.append(native.OptSegment(off, n, 1, 1, c.cout, c.k * c.k, c.cin, c.fwd_pack,
-                                                   c.dgrad_pack))
+            self.segments.append(native.OptSegment(off, n, 1, 1 if E == 8 else 3, c.cout, c.k * c.k, c.cin,
+                                                   c.fwd_pack, c.dgrad_pack))
             off += n
         self.n_conv_params = off
         stat = run = 0
@@ -187,10 +197,10 @@ class NativeResNetEngine(NativeEngineBase):
         mb = self.max_batch
         cfg = self.cfg
         S = cfg.image_size
-        self.image = torch.zeros(mb, S, S, IMG_C, dtype=torch.bfloat16, device=dev)
+        self.image = torch.zeros(mb, S, S, IMG_C, dtype=self.act_dtype, device=dev)
 
         def act(h, c):
-            return torch.empty(mb, h, h, c, dtype=torch.bfloat16, device=dev)
+            return torch.empty(mb, h, h, c, dtype=self.act_dtype, device=dev)
 
         self.r0 = act(self.conv0.hout, self.conv0.cout)
         self.acts = []
@@ -198,8 +208,8 @@ class NativeResNetEngine(NativeEngineBase):
             self.acts.append({"c1": act(b.hout, b.cout), "out": act(b.hout, b.cout),
                               "sc": act(b.hout, b.cout) if b.proj else None})
         big = max(b.hin * b.hin * b.cin for b in self.blocks)
-        self.gbuf = [torch.empty(mb * big, dtype=torch.bfloat16, device=dev) for _ in range(2)]
-        self.tbuf = [torch.empty(mb * big, dtype=torch.bfloat16, device=dev) for _ in range(2)]
+        self.gbuf = [torch.empty(mb * big, dtype=self.act_dtype, device=dev) for _ in range(2)]
+        self.tbuf = [torch.empty(mb * big, dtype=self.act_dtype, device=dev) for _ in range(2)]
         self.logits = torch.zeros(mb, cfg.num_classes, dtype=torch.float32, device=dev)
 
     # ------------------------------------------------------------------ params
@@ -332,6 +342,7 @@ class NativeResNetEngine(NativeEngineBase):
         h.batch, h.HW, h.C, h.classes = nb, b.h * b.h, b.c, self.cfg.num_classes
         h.has_bn, h.training, h.update_running = 1, int(training), int(training)
         h.board_hits = 0 if training else self.board_slot_ptr     # evaluation hits go straight to the score board
+        h.dtype = native.dtype_code(x)
         native.head(h)
         self._count += 1
 

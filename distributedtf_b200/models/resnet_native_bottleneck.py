@@ -107,17 +107,17 @@ class NativeResNetBottleneckEngine(NativeResNetEngine):
         self._alloc_arena()
         dev, mb, cfg = self.device, self.max_batch, self.cfg
         S = cfg.image_size
-        self.image = torch.zeros(mb, S, S, IMG_C, dtype=torch.bfloat16, device=dev)
+        self.image = torch.zeros(mb, S, S, IMG_C, dtype=self.act_dtype, device=dev)
 
         def act(h, c):
-            return torch.empty(mb, h, h, c, dtype=torch.bfloat16, device=dev)
+            return torch.empty(mb, h, h, c, dtype=self.act_dtype, device=dev)
 
         self.r0 = act(self.conv0.hout, self.conv0.cout)
         self.acts = [{"m1": act(b.hin, b.mid), "m2": act(b.hout, b.mid), "out": act(b.hout, b.cout),
                       "sc": act(b.hout, b.cout) if b.proj else None} for b in self.blocks]
         big = max(max(b.hin * b.hin * max(b.cin, b.mid), b.hout * b.hout * b.cout) for b in self.blocks)
-        self.gbuf = [torch.empty(mb * big, dtype=torch.bfloat16, device=dev) for _ in range(2)]
-        self.tbuf = [torch.empty(mb * big, dtype=torch.bfloat16, device=dev) for _ in range(2)]
+        self.gbuf = [torch.empty(mb * big, dtype=self.act_dtype, device=dev) for _ in range(2)]
+        self.tbuf = [torch.empty(mb * big, dtype=self.act_dtype, device=dev) for _ in range(2)]
         self.logits = torch.zeros(mb, cfg.num_classes, dtype=torch.float32, device=dev)
 
     # ------------------------------------------------------------------ forward / backward
@@ -180,6 +180,7 @@ class NativeResNetBottleneckV1Engine(NativeResNetV1Engine):
     """ResNet v1 with bottleneck blocks (post-activation; the block output is written by the tail kernel)."""
     version = 1
     bottleneck = True
+    supports_f32 = False
 
     def _check_config(self, cfg) -> None:
         if cfg.resnet_version != 1:
@@ -230,18 +231,18 @@ class NativeResNetBottleneckV1Engine(NativeResNetV1Engine):
         self._alloc_arena()
         dev, mb, cfg = self.device, self.max_batch, self.cfg
         S = cfg.image_size
-        self.image = torch.zeros(mb, S, S, IMG_C, dtype=torch.bfloat16, device=dev)
+        self.image = torch.zeros(mb, S, S, IMG_C, dtype=self.act_dtype, device=dev)
 
         def act(h, c):
-            return torch.empty(mb, h, h, c, dtype=torch.bfloat16, device=dev)
+            return torch.empty(mb, h, h, c, dtype=self.act_dtype, device=dev)
 
         self.c0 = act(self.conv0.hout, self.conv0.cout)
         self.y0 = act(self.conv0.hout, self.conv0.cout)
         self.acts = [{"c1": act(b.hin, b.mid), "c2": act(b.hout, b.mid), "c3": act(b.hout, b.cout),
                       "y": act(b.hout, b.cout), "p": act(b.hout, b.cout) if b.proj else None} for b in self.blocks]
         big = max(max(b.hin * b.hin * max(b.cin, b.mid), b.hout * b.hout * b.cout) for b in self.blocks)
-        self.gbuf = [torch.empty(mb * big, dtype=torch.bfloat16, device=dev) for _ in range(2)]
-        self.tbuf = [torch.empty(mb * big, dtype=torch.bfloat16, device=dev) for _ in range(3)]
+        self.gbuf = [torch.empty(mb * big, dtype=self.act_dtype, device=dev) for _ in range(2)]
+        self.tbuf = [torch.empty(mb * big, dtype=self.act_dtype, device=dev) for _ in range(3)]
         self.logits = torch.zeros(mb, cfg.num_classes, dtype=torch.float32, device=dev)
 
     def _forward(self, nb: int, training: bool) -> torch.Tensor:

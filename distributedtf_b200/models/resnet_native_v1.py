@@ -42,6 +42,7 @@ class BlockV1:
 
 class NativeResNetV1Engine(NativeResNetEngine):
     version = 1
+    supports_f32 = False
 
     # ------------------------------------------------------------------ plan (parameter order = models/resnet.py)
     def _build_plan(self) -> None:
@@ -91,15 +92,17 @@ class NativeResNetV1Engine(NativeResNetEngine):
         for c in self.convs:
             c.w_off = off
             n = c.cout * c.k * c.k * c.cin
-            kch = c.k * c.k * c.cin // 8
+            E = self.E                                      # 8 (bf16 operands) or 4 (fp32 operands, v2 engines only)
+            kch = c.k * c.k * c.cin // E
             c.fwd_pack = pack
-            pack += _align(((kch + 1) & ~1) * c.cout * 8, 128)
+            pack += _align(((kch + 1) & ~1) * c.cout * E, 128)
             if c is not self.conv0:
-                kchd = c.k * c.k * c.cout // 8
+                kchd = c.k * c.k * c.cout // E
                 c.dgrad_pack = pack
-                pack += _align(((kchd + 1) & ~1) * c.cin * 8, 128)
+                pack += _align(((kchd + 1) & ~1) * c.cin * E, 128)
             c.seg = len(self.segments)
-            self.segments.append(native.OptSegment(off, n, 1, 1, c.cout, c.k * c.k, c.cin, c.fwd_pack, c.dgrad_pack))
+            self.segments.append(native.OptSegment(off, n, 1, 1 if E == 8 else 3, c.cout, c.k * c.k, c.cin, c.fwd_pack,
+                                                   c.dgrad_pack))
             off += n
         self.n_conv_params = off
         stat = run = 0
@@ -124,18 +127,18 @@ class NativeResNetV1Engine(NativeResNetEngine):
         self._alloc_arena()
         dev, mb, cfg = self.device, self.max_batch, self.cfg
         S = cfg.image_size
-        self.image = torch.zeros(mb, S, S, IMG_C, dtype=torch.bfloat16, device=dev)
+        self.image = torch.zeros(mb, S, S, IMG_C, dtype=self.act_dtype, device=dev)
 
         def act(h, c):
-            return torch.empty(mb, h, h, c, dtype=torch.bfloat16, device=dev)
+            return torch.empty(mb, h, h, c, dtype=self.act_dtype, device=dev)
 
         self.c0 = act(self.conv0.hout, self.conv0.cout)        # raw conv0 output
         self.y0 = act(self.conv0.hout, self.conv0.cout)        # relu(bn0(c0)): input of the first block
         self.acts = [{"c1": act(b.hout, b.cout), "c2": act(b.hout, b.cout), "y": act(b.hout, b.cout),
                       "p": act(b.hout, b.cout) if b.proj else None} for b in self.blocks]
         big = max(b.hin * b.hin * b.cin for b in self.blocks)
-        self.gbuf = [torch.empty(mb * big, dtype=torch.bfloat16, device=dev) for _ in range(2)]   # dL/dy, ping-pong
-        self.tbuf = [torch.empty(mb * big, dtype=torch.bfloat16, device=dev) for _ in range(2)]   # masked gradients
+        self.gbuf = [torch.empty(mb * big, dtype=self.act_dtype, device=dev) for _ in range(2)]   # dL/dy, ping-pong
+        self.tbuf = [torch.empty(mb * big, dtype=self.act_dtype, device=dev) for _ in range(2)]   # masked gradients
         self.logits = torch.zeros(mb, cfg.num_classes, dtype=torch.float32, device=dev)
 
     # ------------------------------------------------------------------ forward

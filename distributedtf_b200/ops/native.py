@@ -86,7 +86,7 @@ class Gather(C.Structure):
                 ("mode", C.c_int), ("update_running", C.c_int),
                 ("Hs", C.c_int), ("Ws", C.c_int), ("C", C.c_int),
                 ("KH", C.c_int), ("KW", C.c_int), ("stride", C.c_int), ("pad", C.c_int),
-                ("transposed", C.c_int), ("cpt_shift", C.c_int), ("kchunks_real", C.c_int)]
+                ("transposed", C.c_int), ("dtype", C.c_int), ("cpt_shift", C.c_int), ("kchunks_real", C.c_int)]
 
 
 class ConvGemm(C.Structure):
@@ -111,7 +111,7 @@ class Head(C.Structure):
                 ("bwd_stats_out", C.c_void_p), ("loss_scale", C.c_float),
                 ("batch", C.c_int), ("HW", C.c_int), ("C", C.c_int), ("classes", C.c_int),
                 ("has_bn", C.c_int), ("training", C.c_int), ("update_running", C.c_int),
-                ("board_hits", C.c_void_p)]
+                ("board_hits", C.c_void_p), ("dtype", C.c_int)]
 
 
 class Hparams(C.Structure):
@@ -135,6 +135,8 @@ def _declare(l: C.CDLL) -> None:
     l.dtf_conv_bwd.argtypes = [C.POINTER(ConvGemm), C.POINTER(ConvWgrad), vp]
     l.dtf_conv_bwd.restype = i
     l.dtf_bn_bwd_apply.argtypes = [vp, vp, vp, vp, C.POINTER(BnRef), vp, ll, i, vp]
+    l.dtf_bn_bwd_apply_dt.argtypes = [vp, vp, vp, vp, C.POINTER(BnRef), vp, ll, i, i, vp]
+    l.dtf_bn_bwd_apply_dt.restype = i
     l.dtf_head.argtypes = [C.POINTER(Head), vp]
     l.dtf_bn_act_apply.argtypes = [vp, C.POINTER(BnRef), vp, C.POINTER(BnRef), vp, ll, i, i, vp]
     l.dtf_bn_act_apply.restype = i
@@ -221,10 +223,19 @@ def bn_ref(channels: int, count: int, *, stats=None, gamma=None, beta=None, run_
                  1.0 / float(count), eps, decay, channels, int(use_running))
 
 
+BF16, F32 = 0, 1               # DTF_BF16 / DTF_F32: element type of the tensors of a launch
+PP_F32 = F32 << 8              # DTF_PP_F32: preprocess writes fp32
+
+
+def dtype_code(t: Optional[torch.Tensor]) -> int:
+    return F32 if t is not None and t.dtype == torch.float32 else BF16
+
+
 def gather(src: torch.Tensor, Hs: int, Ws: int, Cc: int, *, KH=1, KW=1, stride=1, pad=0, transposed=False,
            mode=PRO_NONE, bn: Optional[BnRef] = None, src2=None, bwd_stats=None, update_running=False) -> Gather:
+    """The element type of the launch follows the source tensor: bf16, or fp32 (tf32 tensor-core math)."""
     return Gather(ptr(src), ptr(src2), ptr(bwd_stats), bn if bn is not None else BnRef(), mode,
-                  int(update_running), Hs, Ws, Cc, KH, KW, stride, pad, int(transposed), 0, 0)
+                  int(update_running), Hs, Ws, Cc, KH, KW, stride, pad, int(transposed), dtype_code(src), 0, 0)
 
 
 def conv_gemm(a: Gather, wpk: torch.Tensor, out: torch.Tensor, *, NB: int, Ho: int, Wo: int, N: int,
@@ -255,8 +266,8 @@ def conv_wgrad(x: Gather, gy: Gather, dw: torch.Tensor, *, NB: int, Ho: int, Wo:
 
 
 def bn_bwd_apply(t, x, res, out, bn: BnRef, bwd_stats, pixels: int, channels: int) -> None:
-    check(lib().dtf_bn_bwd_apply(ptr(t), ptr(x), ptr(res), ptr(out), C.byref(bn), ptr(bwd_stats),
-                                 pixels, channels, stream_ptr()), "dtf_bn_bwd_apply")
+    check(lib().dtf_bn_bwd_apply_dt(ptr(t), ptr(x), ptr(res), ptr(out), C.byref(bn), ptr(bwd_stats),
+                                    pixels, channels, dtype_code(out), stream_ptr()), "dtf_bn_bwd_apply")
 
 
 def bn_act_apply(x, bn: BnRef, out, pixels: int, channels: int, *, sc=None, bn_sc: Optional[BnRef] = None,
@@ -314,6 +325,8 @@ def preprocess(images_u8: torch.Tensor, indices: Optional[torch.Tensor], out: to
                labels_out: Optional[torch.Tensor] = None, step: Optional[torch.Tensor] = None) -> None:
     _, H, W, Cc = images_u8.shape
     count = int(n if n is not None else (indices.numel() if indices is not None else images_u8.shape[0]))
+    if out.dtype == torch.float32:
+        mode |= PP_F32
     if labels_all is not None:          # batch gathered inside the kernel (images and labels)
         check(lib().dtf_preprocess_indexed(ptr(images_u8), ptr(indices), ptr(labels_all), ptr(labels_out), ptr(out),
                                            ptr(crop_flip), count, H, W, Cc, mode, seed & (2 ** 64 - 1),
@@ -329,9 +342,19 @@ def struct_to_tensor(s: C.Structure, device) -> torch.Tensor:
     return torch.frombuffer(bytearray(raw), dtype=torch.uint8).to(device)
 
 
-def pack_weight_host(w_ohwi: torch.Tensor, transpose_for_dgrad: bool = False) -> torch.Tensor:
-    """Host restatement of the packing: OHWI fp32 -> bf16 [K/8 (even)][N][8] (oracle + tests)."""
+def pack_weight_host(w_ohwi: torch.Tensor, transpose_for_dgrad: bool = False, dtype=torch.bfloat16) -> torch.Tensor:
+    """Host restatement of the packing: OHWI fp32 -> bf16 [K/8 (even)][N][8], or fp32 [K/4 (even)][N][4] for the
+    tf32 kernels (oracle + tests)."""
     cout, kh, kw, cin = w_ohwi.shape
+    if dtype == torch.float32:
+        taps = kh * kw
+        w = w_ohwi.reshape(cout, taps, cin)
+        mat = w.permute(2, 1, 0).reshape(cin, taps * cout) if transpose_for_dgrad else w.reshape(cout, taps * cin)
+        n, k = mat.shape
+        kch_pad = (((k + 3) // 4) + 1) & ~1
+        buf = torch.zeros(kch_pad * 4, n, dtype=torch.float32, device=w_ohwi.device)
+        buf[:k] = mat.t()
+        return buf.reshape(kch_pad, 4, n).permute(0, 2, 1).contiguous()
     taps = kh * kw
     w = w_ohwi.reshape(cout, taps, cin)
     if transpose_for_dgrad:

@@ -45,7 +45,13 @@ typedef struct {
     int use_running;     /* 1 = inference: normalise with run_mean / run_var */
 } DtfBnRef;
 
-/* One gathered GEMM operand: an NHWC bf16 tensor read through a (KH x KW, stride, pad) window. */
+/* Element type of the activation / gradient tensors and packed weights of a launch.  DTF_BF16: bf16 operands,
+ * kind::f16 MMA.  DTF_F32: fp32 storage, kind::tf32 MMA (10-bit mantissa products, fp32 accumulation) -- the
+ * reference's default dtype=fp32 mode (official/utils/flags/_performance.py:107) on tensor cores.  Pointers stay
+ * typed dtf_bf16* in the structs; with DTF_F32 they address floats and channel counts must be multiples of 4. */
+enum { DTF_BF16 = 0, DTF_F32 = 1 };
+
+/* One gathered GEMM operand: an NHWC tensor read through a (KH x KW, stride, pad) window. */
 typedef struct {
     const dtf_bf16* src;     /* [NB, Hs, Ws, C] */
     const dtf_bf16* src2;    /* DTF_PRO_BN_BWD: the BN input x (src is then t = dL/d(bn out) masked) */
@@ -56,6 +62,7 @@ typedef struct {
     int Hs, Ws, C;
     int KH, KW, stride, pad;
     int transposed;          /* 1 = gradient gather of a strided conv (dgrad) */
+    int dtype;               /* DTF_BF16 | DTF_F32: element type of src / src2 (and of every tensor of the launch) */
     int cpt_shift;           /* filled by the launcher */
     int kchunks_real;        /* filled by the launcher */
 } DtfGather;
@@ -115,6 +122,7 @@ typedef struct {
                                   peer pointer when the master sits on another GPU.  Every hit is added to slot->hits and
                                   the batch size to slot->seen with system-scope reductions, so the eval score reaches the
                                   master without a host round trip (pbt_cluster.py:114-128 gathered it over MPI). */
+    int dtype;               /* DTF_BF16 | DTF_F32: element type of x and t_out */
 } DtfHead;
 
 /* ---- optimizer ------------------------------------------------------------------------ */
@@ -145,7 +153,8 @@ typedef struct {
 typedef struct {
     int offset, count;       /* elements, in params / grads / slot0 / slot1 */
     int regularized;         /* conv kernels only (resnet_model.py:91) */
-    int pack;                /* 1 = conv kernel: emit GEMM-ready bf16 copies; 2 = dense: plain bf16 copy */
+    int pack;                /* 1 = conv kernel: emit GEMM-ready bf16 copies [K/8][N][8]; 2 = dense: plain bf16 copy;
+                                3 = conv kernel, fp32 operands (DTF_F32): [K/4][N][4] floats, pack offsets in floats */
     int Cout, taps, Cin;     /* OHWI dims of a conv kernel */
     int fwd_pack_off;        /* element offsets in the bf16 pack arena, -1 = none */
     int dgrad_pack_off;
@@ -154,6 +163,10 @@ typedef struct {
 
 int dtf_bn_bwd_apply(const dtf_bf16* t, const dtf_bf16* x, const dtf_bf16* res, dtf_bf16* out,
                      const DtfBnRef* bn, const float* bwd_stats, long long pixels, int C, cudaStream_t stream);
+/* Same for tensors of element type `dtype` (DTF_BF16 | DTF_F32). */
+int dtf_bn_bwd_apply_dt(const dtf_bf16* t, const dtf_bf16* x, const dtf_bf16* res, dtf_bf16* out,
+                        const DtfBnRef* bn, const float* bwd_stats, long long pixels, int C, int dtype,
+                        cudaStream_t stream);
 int dtf_head(const DtfHead* p, cudaStream_t stream);
 /* ResNet v1 (post-activation) block tail (resnet_model.py:127-168, 215-264): out = relu(bn(x) + shortcut) with
  * shortcut = none (sc NULL) | sc (bn_sc NULL: identity) | bn_sc(sc) (projection conv followed by its own BN);
@@ -176,7 +189,9 @@ int dtf_optimizer_step(float* params, const float* grads, float* slot0, float* s
 int dtf_step_begin(float* zero_base, long long zero_floats, long long* step, int bump, cudaStream_t stream);
 int dtf_fill(float* p, long long n, float v, cudaStream_t stream);
 /* uint8 NHWC -> bf16 NHWC (channels padded to 8); mode 0 cast, 1 standardise, 2 crop+flip+standardise
- * (cifar10_main.py:96-109).  crop_flip: optional [n][3] = (oy, ox, flip) overriding the RNG. */
+ * (cifar10_main.py:96-109).  crop_flip: optional [n][3] = (oy, ox, flip) overriding the RNG.
+ * mode | DTF_PP_F32 writes fp32 instead of bf16 (same 8 channels per pixel). */
+#define DTF_PP_F32 (DTF_F32 << 8)
 int dtf_preprocess(const uint8_t* images, const int* indices, dtf_bf16* out, const int* crop_flip, int n,
                    int H, int W, int C, int mode, unsigned long long seed, unsigned long long counter,
                    const long long* step, cudaStream_t stream);
