@@ -338,10 +338,25 @@ DTF_DEVINL void gather_chunks_slow(const DtfGather& g, const int8_t* tap_dy, con
 // Wide channel counts (128 / 256: the 1x1 convolutions of bottleneck blocks): the chunks of a row are taken in
 // batches whose loads are all in flight before the first one is consumed (8 x 16 bytes per source, 4 with the
 // second source of the BN-backward prologue).
-template <bool TWO, int E = 8>
+// Shared-memory address of chunk jj (counted from the first chunk of the call) of one row.
+//   SW = false: chunk-major, [chunk][128 rows][16 bytes] (K-major operands, and MN-major bf16 operands);
+//                `dst` = buffer + row * 16.
+//   SW = true : the one MN-major layout kind::tf32 accepts (measured with bench/probe_umma.py: no-swizzle, 32B, 64B
+//                and plain 128B MN-major descriptors read zeros for tf32): layout type 1, "128-byte swizzle with a
+//                32-byte base".  Rows of 128 bytes = 32 channels at a 128-byte pitch, blocks of 32 channels 16 KB
+//                apart, and within a row the 32-byte unit index is XOR-ed with (row & 3).
+//                `dst` = buffer + row * 128, `sw` = (row & 3) << 1 in units of 16-byte chunks.
+constexpr uint32_t kSwBlockBytes = kTileM * 128;       // one 32-channel block of a 128-row tile
+template <bool SW>
+DTF_DEVINL uint32_t chunk_addr(uint32_t dst, int jj, uint32_t sw) {
+    if (SW) return dst + (static_cast<uint32_t>(jj >> 3) * kSwBlockBytes) + (((static_cast<uint32_t>(jj) & 7u) ^ sw) << 4);
+    return dst + jj * (kTileM * 16);
+}
+
+template <bool TWO, int E = 8, bool SW = false>
 DTF_DEVINL void gather_chunks_wide(const DtfGather& g, const int8_t* tap_dy, const int8_t* tap_dx,
                                    const float* p0, const float* p1, const float* p2, const RowCoord& rc,
-                                   int jbeg, int jend, uint32_t dst) {
+                                   int jbeg, int jend, uint32_t dst, uint32_t sw = 0) {
     constexpr int B = TWO ? 4 : 8;
     for (int j = jbeg; j < jend; j += B) {
         GatherLoad L[B];
@@ -350,17 +365,19 @@ DTF_DEVINL void gather_chunks_wide(const DtfGather& g, const int8_t* tap_dy, con
             gather_issue<TWO, E>(g, tap_dy, tap_dx, rc, j + u < jend ? j + u : g.kchunks_real, L[u]);
 #pragma unroll
         for (int u = 0; u < B; ++u)
-            if (j + u < jend) sts16(dst + (j + u - jbeg) * (kTileM * 16), gather_finish<E>(g, p0, p1, p2, L[u]));
+            if (j + u < jend) sts16(chunk_addr<SW>(dst, j + u - jbeg, sw), gather_finish<E>(g, p0, p1, p2, L[u]));
     }
 }
 
-template <int E = 8>
+template <int E = 8, bool SW = false>
 DTF_DEVINL void gather_row(const DtfGather& g, const int8_t* tap_dy, const int8_t* tap_dx,
                            const float* p0, const float* p1, const float* p2, const RowCoord& rc,
-                           int jbeg, int jend, uint32_t dst) {
+                           int jbeg, int jend, uint32_t dst, uint32_t sw = 0) {
     if (E != 8) {          // fp32 tensors: every layer takes the batched generic path
-        if (g.mode == DTF_PRO_BN_BWD) gather_chunks_wide<true, E>(g, tap_dy, tap_dx, p0, p1, p2, rc, jbeg, jend, dst);
-        else gather_chunks_wide<false, E>(g, tap_dy, tap_dx, p0, p1, p2, rc, jbeg, jend, dst);
+        if (g.mode == DTF_PRO_BN_BWD)
+            gather_chunks_wide<true, E, SW>(g, tap_dy, tap_dx, p0, p1, p2, rc, jbeg, jend, dst, sw);
+        else
+            gather_chunks_wide<false, E, SW>(g, tap_dy, tap_dx, p0, p1, p2, rc, jbeg, jend, dst, sw);
         return;
     }
     if (g.stride > 2) {

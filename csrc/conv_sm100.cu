@@ -209,7 +209,13 @@ conv_wgrad_kernel(const __grid_constant__ DtfConvWgrad P) {
     // blockIdx.z selects 128 output channels (Cout up to 256: the expanding 1x1 convolutions of bottleneck blocks)
     const int co_chunk0 = blockIdx.z * kCoChunks;
     const int gy_chunks = min(P.Cout / E - co_chunk0, kCoChunks);
-    const uint32_t buf_bytes = static_cast<uint32_t>(min(P.Cout / E, kCoChunks) + P.chunks_per_cta) * kChunkBytes;
+    // bf16: both operands chunk-major ([chunk][128 pixels][16 bytes]), gy' first.  fp32: MN-major tf32 operands exist
+    // only in the swizzled 128-byte-row layout (conv_common.cuh: chunk_addr), blocks of 32 channels / columns of
+    // 16 KB each, im2col blocks first, then the gy' blocks.
+    const uint32_t b_blocks = (P.chunks_per_cta + 7) >> 3;
+    const uint32_t a_blocks = (min(P.Cout / E, kCoChunks) + 7) >> 3;
+    const uint32_t buf_bytes = E == 8 ? static_cast<uint32_t>(min(P.Cout / E, kCoChunks) + P.chunks_per_cta) * kChunkBytes
+                                      : (a_blocks + b_blocks) * kSwBlockBytes;
     const uint32_t acc_cols = tmem_cols_pow2(ncols);
 
     if (tid == 0) {
@@ -241,13 +247,21 @@ conv_wgrad_kernel(const __grid_constant__ DtfConvWgrad P) {
                 const uint32_t buf = it & 1;
                 mbar_wait(smem_u32(&hdr->full[buf]), (it >> 1) & 1, 6);
                 tc_fence_after_sync();
-                const uint32_t a_base = smem_u32(smem_ab) + buf * buf_bytes;
-                const uint32_t b_base = a_base + gy_chunks * kChunkBytes;
+                const uint32_t buf_base = smem_u32(smem_ab) + buf * buf_bytes;
+                const uint32_t a_base = E == 8 ? buf_base : buf_base + b_blocks * kSwBlockBytes;
+                const uint32_t b_base = E == 8 ? buf_base + gy_chunks * kChunkBytes : buf_base;
                 for (int ks = 0; ks < kTileM / kStepRows; ++ks) {
-                    // K step = 16 pixels = 2 groups of 8 rows (LBO = 128) for bf16, one group of 8 rows for tf32;
-                    // channel chunks SBO apart
-                    const uint64_t adesc = umma_desc(a_base + ks * kStepRows * 16, 128, kChunkBytes);
-                    const uint64_t bdesc = umma_desc(b_base + ks * kStepRows * 16, 128, kChunkBytes);
+                    uint64_t adesc, bdesc;
+                    if (E == 8) {
+                        // K step = 16 pixels = 2 groups of 8 rows (LBO = 128); channel chunks SBO apart
+                        adesc = umma_desc(a_base + ks * 256, 128, kChunkBytes);
+                        bdesc = umma_desc(b_base + ks * 256, 128, kChunkBytes);
+                    } else {
+                        // K step = 8 pixels = 8 rows of 128 bytes (two 4-row swizzle atoms, SBO = 512 apart);
+                        // 32-channel blocks LBO = 16 KB apart; layout type 1 in descriptor bits 61..63
+                        adesc = umma_desc(a_base + ks * 1024, kSwBlockBytes, 512) | (1ull << 61);
+                        bdesc = umma_desc(b_base + ks * 1024, kSwBlockBytes, 512) | (1ull << 61);
+                    }
                     if (elect_one()) {
                         if (E == 8) umma_bf16(tmem_base, adesc, bdesc, idesc, (it | ks) != 0);
                         else umma_tf32(tmem_base, adesc, bdesc, idesc, (it | ks) != 0);
@@ -268,9 +282,14 @@ conv_wgrad_kernel(const __grid_constant__ DtfConvWgrad P) {
             if ((it & 1) != group) continue;
             const RowCoord rc = row_coord(tile * kTileM + row, M, P.Ho, P.Wo);
             mbar_wait(smem_u32(&hdr->empty[group]), ((it >> 1) & 1) ^ 1, 7);
-            const uint32_t a_dst = smem_u32(smem_ab) + group * buf_bytes + row * 16;
-            const uint32_t b_dst = a_dst + gy_chunks * kChunkBytes;
-            gather_row<E>(P.x, hdr->tap_dy, hdr->tap_dx, cst->p0, cst->p1, cst->p2, rc, j0, j0 + nj, b_dst);
+            if (E == 8) {
+                const uint32_t b_dst = smem_u32(smem_ab) + group * buf_bytes + gy_chunks * kChunkBytes + row * 16;
+                gather_row<E>(P.x, hdr->tap_dy, hdr->tap_dx, cst->p0, cst->p1, cst->p2, rc, j0, j0 + nj, b_dst);
+            } else {
+                const uint32_t b_dst = smem_u32(smem_ab) + group * buf_bytes + row * 128;
+                gather_row<E, true>(P.x, hdr->tap_dy, hdr->tap_dx, cst->p0, cst->p1, cst->p2, rc, j0, j0 + nj, b_dst,
+                                    (row & 3) << 1);
+            }
             fence_proxy_async_smem();
             mbar_arrive(smem_u32(&hdr->full[group]));
         }
@@ -284,9 +303,15 @@ conv_wgrad_kernel(const __grid_constant__ DtfConvWgrad P) {
                 const uint32_t buf = it & 1;
                 const RowCoord rc = row_coord(tile * kTileM + row, M, P.Ho, P.Wo);
                 mbar_wait(smem_u32(&hdr->empty[buf]), ((it >> 1) & 1) ^ 1, 9);
-                const uint32_t a_dst = smem_u32(smem_ab) + buf * buf_bytes + row * 16;
-                gather_row<E>(P.gy, hdr->tap_dy + 31, hdr->tap_dx + 31, cst->q0, cst->q1, cst->q2, rc, co_chunk0,
-                              co_chunk0 + gy_chunks, a_dst);
+                if (E == 8) {
+                    const uint32_t a_dst = smem_u32(smem_ab) + buf * buf_bytes + row * 16;
+                    gather_row<E>(P.gy, hdr->tap_dy + 31, hdr->tap_dx + 31, cst->q0, cst->q1, cst->q2, rc, co_chunk0,
+                                  co_chunk0 + gy_chunks, a_dst);
+                } else {
+                    const uint32_t a_dst = smem_u32(smem_ab) + buf * buf_bytes + b_blocks * kSwBlockBytes + row * 128;
+                    gather_row<E, true>(P.gy, hdr->tap_dy + 31, hdr->tap_dx + 31, cst->q0, cst->q1, cst->q2, rc, co_chunk0,
+                                        co_chunk0 + gy_chunks, a_dst, (row & 3) << 1);
+                }
                 fence_proxy_async_smem();
                 mbar_arrive(smem_u32(&hdr->full[buf]));
             }
@@ -435,9 +460,18 @@ extern "C" int dtf_conv_wgrad(DtfConvWgrad* p, cudaStream_t stream) {
     const int header = 1024 + static_cast<int>(sizeof(SmemConsts));
     const int a_off = (header + 1023) & ~1023;
     const int nz = (p->Cout + 127) / 128;              // 128 output channels per CTA (blockIdx.z)
-    const int buf_bytes = ((p->Cout < 128 ? p->Cout : 128) / E + per) * kChunkBytes;
-    // the A descriptor always spans 128 channels (16 / 32 chunks): keep that much slack after the last buffer
-    const int smem_bytes = a_off + 2 * buf_bytes + (128 / E) * kChunkBytes;
+    const int co_chunks = (p->Cout < 128 ? p->Cout : 128) / E;
+    int buf_bytes, smem_bytes;
+    if (!f32) {
+        buf_bytes = (co_chunks + per) * kChunkBytes;
+        // the A descriptor always spans 16 channel chunks: keep 32 KB of slack after the last buffer
+        smem_bytes = a_off + 2 * buf_bytes + 16 * kChunkBytes;
+    } else {
+        // swizzled MN-major blocks of 32 channels / columns (16 KB each); the A descriptor spans four blocks
+        const int a_blocks = (co_chunks + 7) / 8, b_blocks = (per + 7) / 8;
+        buf_bytes = (a_blocks + b_blocks) * static_cast<int>(kSwBlockBytes);
+        smem_bytes = a_off + 2 * buf_bytes + (4 - a_blocks) * static_cast<int>(kSwBlockBytes);
+    }
     if (smem_bytes > 227 * 1024) return DTF_ERR_SMEM;
     p->smem_a_off = a_off;
     const int M = p->NB * p->Ho * p->Wo;

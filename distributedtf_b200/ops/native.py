@@ -219,8 +219,12 @@ def _declare_optional(l: C.CDLL) -> None:
 # --------------------------------------------------------------------------- builders
 def bn_ref(channels: int, count: int, *, stats=None, gamma=None, beta=None, run_mean=None, run_var=None,
            use_running: bool = False, eps: float = BN_EPS, decay: float = BN_DECAY) -> BnRef:
-    return BnRef(ptr(stats), ptr(gamma), ptr(beta), ptr(run_mean), ptr(run_var),
-                 1.0 / float(count), eps, decay, channels, int(use_running))
+    r = BnRef(ptr(stats), ptr(gamma), ptr(beta), ptr(run_mean), ptr(run_var),
+              1.0 / float(count), eps, decay, channels, int(use_running))
+    # the struct holds raw device pointers: keep the tensors alive as long as it lives, so that a temporary passed
+    # here cannot be recycled by the caching allocator before the launch that reads it has been enqueued
+    r._keep = (stats, gamma, beta, run_mean, run_var)
+    return r
 
 
 BF16, F32 = 0, 1               # DTF_BF16 / DTF_F32: element type of the tensors of a launch
@@ -234,8 +238,10 @@ def dtype_code(t: Optional[torch.Tensor]) -> int:
 def gather(src: torch.Tensor, Hs: int, Ws: int, Cc: int, *, KH=1, KW=1, stride=1, pad=0, transposed=False,
            mode=PRO_NONE, bn: Optional[BnRef] = None, src2=None, bwd_stats=None, update_running=False) -> Gather:
     """The element type of the launch follows the source tensor: bf16, or fp32 (tf32 tensor-core math)."""
-    return Gather(ptr(src), ptr(src2), ptr(bwd_stats), bn if bn is not None else BnRef(), mode,
-                  int(update_running), Hs, Ws, Cc, KH, KW, stride, pad, int(transposed), dtype_code(src), 0, 0)
+    g = Gather(ptr(src), ptr(src2), ptr(bwd_stats), bn if bn is not None else BnRef(), mode,
+               int(update_running), Hs, Ws, Cc, KH, KW, stride, pad, int(transposed), dtype_code(src), 0, 0)
+    g._keep = (src, src2, bwd_stats, getattr(bn, "_keep", None))       # see bn_ref
+    return g
 
 
 def conv_gemm(a: Gather, wpk: torch.Tensor, out: torch.Tensor, *, NB: int, Ho: int, Wo: int, N: int,
