@@ -108,7 +108,16 @@ class DataParallelGroup:
     def comm_stats(self) -> dict:
         """Device-timestamped accounting of the fused exchange since the group was built: time blocked on the
         peers' ready flags (the exposed communication), time of the remote gradient loads, kernel time."""
-        cells = self.flag_buf.tensor[16 * MAX_DP + 192: 16 * MAX_DP + 224].view(torch.int64).tolist()
+        return self.comm_stats_between(None, self.comm_raw())
+
+    def comm_raw(self) -> list:
+        """The four device counters of the exchange: ns blocked on ready flags, ns of remote loads, ns in the kernel,
+        calls (accumulated by CTA 0 of every launch)."""
+        return self.flag_buf.tensor[16 * MAX_DP + 192: 16 * MAX_DP + 224].view(torch.int64).tolist()
+
+    @staticmethod
+    def comm_stats_between(before, after) -> dict:
+        cells = [a - (b if before is not None else 0) for a, b in zip(after, before or after)]
         calls = max(cells[3], 1)
         return {"calls": cells[3], "wait_us_per_call": cells[0] / calls / 1e3, "load_us_per_call": cells[1] / calls / 1e3,
                 "kernel_us_per_call": cells[2] / calls / 1e3}

@@ -38,6 +38,22 @@ def test_cifar_population_one_gpu_p2p(tmp_path):
     assert 0 <= best["best_acc"] <= 1
 
 
+@pytest.mark.parametrize("kw", [dict(resnet_bottleneck=True, resnet_size=11),
+                                dict(resnet_bottleneck=True, resnet_size=11, resnet_version=1),
+                                dict(dtype="tf32"), dict(dtype="fp32", resnet_bottleneck=True, resnet_size=11)],
+                         ids=["bottleneck-v2", "bottleneck-v1", "tf32", "fp32-bottleneck"])
+def test_population_of_the_other_native_engines(tmp_path, kw):
+    """Bottleneck blocks (v1, v2) and fp32 / tf32 compute stay on the native engines through a whole PBT run with
+    exploit + explore (`engine="native"` raises if a configuration had to fall back to the torch engine)."""
+    from distributedtf_b200.launch import run_local
+    out = run_local(_cfg(tmp_path, population_size=3, **kw))
+    assert out["pop_size"] == 3 and len(out["history"]) == 2
+    for i in range(3):
+        rows = open(tmp_path / "savedata" / f"model_{i}" / "learning_curve.csv").read().strip().splitlines()
+        assert len(rows) == 3 and 0.0 <= float(rows[-1].split(",")[1]) <= 1.0
+    assert out["profiling"]["device_train"] > 0
+
+
 def test_cifar_file_exploit_restores_bit_identical_state(tmp_path):
     """Reference mechanism (checkpoint files copied by the master): loser == winner after restore."""
     from distributedtf_b200 import ckpt
