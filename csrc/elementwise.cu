@@ -475,6 +475,53 @@ __global__ void fill_kernel(float* __restrict__ p, long long n, float v) {
 }
 
 // ---------------------------------------------------------------------------------------
+// parameter initialisation on the device (reference: the tf.layers initialisers a member is built with --
+// glorot_uniform by default, variance_scaling he / glorot-normal as truncated normals, cifar10_main.py:167-199 via
+// resnet_model.py:81-92; constants for BatchNorm and biases).  Counter-based Philox4x32-10: element i of segment s
+// draws from counter (i / 4, s) under key (seed), so the result depends on (seed, layout) only, not on the launch
+// shape.  One thread produces four consecutive elements.
+// ---------------------------------------------------------------------------------------
+DTF_DEVINL uint4 philox4x32_10(uint4 ctr, uint2 key) {
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        const uint32_t hi0 = __umulhi(0xD2511F53u, ctr.x), lo0 = 0xD2511F53u * ctr.x;
+        const uint32_t hi1 = __umulhi(0xCD9E8D57u, ctr.z), lo1 = 0xCD9E8D57u * ctr.z;
+        ctr = make_uint4(hi1 ^ ctr.y ^ key.x, lo1, hi0 ^ ctr.w ^ key.y, lo0);
+        key.x += 0x9E3779B9u;
+        key.y += 0xBB67AE85u;
+    }
+    return ctr;
+}
+
+__global__ void __launch_bounds__(256)
+init_params_kernel(float* __restrict__ params, const DtfInitSegment* __restrict__ segs, int n_segs,
+                   unsigned long long seed) {
+    const int si = blockIdx.y;
+    if (si >= n_segs) return;
+    const DtfInitSegment s = segs[si];
+    const uint2 key = make_uint2(static_cast<uint32_t>(seed), static_cast<uint32_t>(seed >> 32));
+    // P(|z| < 2) of a standard normal: the truncated normal is drawn by inverting the CDF on that interval
+    const float lo = 0.0227501319f, span = 0.9544997361f;
+    for (int q = blockIdx.x * blockDim.x + threadIdx.x; q * 4 < s.count; q += gridDim.x * blockDim.x) {
+        const uint4 r = philox4x32_10(make_uint4(static_cast<uint32_t>(q), 0u, static_cast<uint32_t>(si), 0x0d7fu), key);
+        const uint32_t bits[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            const int i = q * 4 + e;
+            if (i >= s.count) break;
+            const float u = (static_cast<float>(bits[e] >> 8) + 0.5f) * (1.0f / 16777216.0f);     // (0, 1)
+            float v;
+            if (s.kind == DTF_INIT_CONST) v = s.scale;
+            else if (s.kind == DTF_INIT_UNIFORM) v = (2.f * u - 1.f) * s.scale;
+            else v = normcdfinvf(lo + span * u) * s.scale;                                          // DTF_INIT_TRUNC_NORMAL
+            // zero the padded input channels of a kernel stored [.., c_pad] with c_real < c_pad real ones
+            if (s.c_pad > 0 && (i % s.c_pad) >= s.c_real) v = 0.f;
+            params[s.offset + i] = v;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------
 // input preprocessing: uint8 NHWC -> bf16 NHWC with channels padded to 8
 //   mode 0: plain cast (MNIST: pixels stay 0..255)
 //   mode 1: per-image standardisation (CIFAR eval)
@@ -652,6 +699,16 @@ extern "C" int dtf_fill(float* p, long long n, float v, cudaStream_t stream) {
     if (blocks > 148 * 4) blocks = 148 * 4;
     if (blocks < 1) blocks = 1;
     dtf::fill_kernel<<<static_cast<int>(blocks), 256, 0, stream>>>(p, n, v);
+    return DTF_CHECK_LAUNCH();
+}
+
+extern "C" int dtf_init_params(float* params, const DtfInitSegment* segs_dev, int n_segs, int max_count,
+                               unsigned long long seed, cudaStream_t stream) {
+    if (n_segs < 1 || max_count < 1 || params == nullptr || segs_dev == nullptr) return DTF_ERR_ARG;
+    int gx = (max_count / 4 + 255) / 256;
+    if (gx > 64) gx = 64;
+    if (gx < 1) gx = 1;
+    dtf::init_params_kernel<<<dim3(gx, n_segs), 256, 0, stream>>>(params, segs_dev, n_segs, seed);
     return DTF_CHECK_LAUNCH();
 }
 

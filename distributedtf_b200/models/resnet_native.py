@@ -220,7 +220,39 @@ class NativeResNetEngine(NativeEngineBase):
         return base[b.p_off: b.p_off + b.c], base[b.p_off + b.c: b.p_off + 2 * b.c]      # (beta, gamma)
 
     def _init_params(self, initializer: str, seed: int) -> None:
-        self.load_named_params(resnet.init_params(self.cfg, initializer, seed))
+        """Initial weights are drawn on the device (``dtf_init_params``: Philox keyed by the member's seed) for the
+        uniform / truncated-normal initialisers; ``orthogonal`` needs a QR factorisation and comes from the host
+        restatement (``models/resnet.py init_params``), as does everything when ``DTF_HOST_INIT=1``."""
+        import os
+        if initializer == "orthogonal" or os.environ.get("DTF_HOST_INIT") == "1":
+            self.load_named_params(resnet.init_params(self.cfg, initializer, seed))
+            return
+        segs = []
+        for c in self.convs:
+            cin_real = self.cfg.in_channels if c is self.conv0 else c.cin
+            fan_in, fan_out = c.k * c.k * cin_real, c.k * c.k * c.cout
+            n = c.cout * c.k * c.k * c.cin
+            if initializer == "glorot_normal":
+                kind, scale = native.INIT_TRUNC_NORMAL, math.sqrt(2.0 / (fan_in + fan_out))
+            elif initializer == "he_init":
+                kind, scale = native.INIT_TRUNC_NORMAL, math.sqrt(2.0 / fan_in)
+            else:                                   # layer default: glorot_uniform
+                kind, scale = native.INIT_UNIFORM, math.sqrt(6.0 / (fan_in + fan_out))
+            pad = (c.cin, cin_real) if cin_real != c.cin else (0, 0)
+            segs.append(native.InitSegment(c.w_off, n, kind, scale, pad[0], pad[1]))
+        for b in self.bns:
+            segs.append(native.InitSegment(b.p_off, b.c, native.INIT_CONST, 0.0, 0, 0))            # beta
+            segs.append(native.InitSegment(b.p_off + b.c, b.c, native.INIT_CONST, 1.0, 0, 0))      # gamma
+        nd = self.cfg.num_classes * self.final_c                                                   # dense: glorot_uniform
+        segs.append(native.InitSegment(self.dense_w_off, nd, native.INIT_UNIFORM,
+                                       math.sqrt(6.0 / (self.final_c + self.cfg.num_classes)), 0, 0))
+        segs.append(native.InitSegment(self.dense_b_off, self.cfg.num_classes, native.INIT_CONST, 0.0, 0, 0))
+        with torch.cuda.device(self.device):
+            native.init_params(self.params, segs, 0x9E3779B97F4A7C15 * (seed + 1))
+            for b in self.bns:
+                self.running[b.run_off: b.run_off + b.c].zero_()
+                self.running[b.run_off + b.c: b.run_off + 2 * b.c].fill_(1.0)
+            self.repack()
 
     @torch.no_grad()
     def load_named_params(self, named: Dict[str, torch.Tensor]) -> None:

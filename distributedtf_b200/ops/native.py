@@ -128,6 +128,14 @@ class OptSegment(C.Structure):
                 ("fwd_pack_off", C.c_int), ("dgrad_pack_off", C.c_int), ("reserved", C.c_int * 3)]
 
 
+class InitSegment(C.Structure):
+    _fields_ = [("offset", C.c_int), ("count", C.c_int), ("kind", C.c_int), ("scale", C.c_float),
+                ("c_pad", C.c_int), ("c_real", C.c_int), ("reserved", C.c_int * 2)]
+
+
+INIT_CONST, INIT_UNIFORM, INIT_TRUNC_NORMAL = 0, 1, 2
+
+
 def _declare(l: C.CDLL) -> None:
     vp, i, ll, f = C.c_void_p, C.c_int, C.c_longlong, C.c_float
     l.dtf_conv_gemm.argtypes = [C.POINTER(ConvGemm), vp]
@@ -146,6 +154,8 @@ def _declare(l: C.CDLL) -> None:
     l.dtf_optimizer_step.argtypes = [vp, vp, vp, vp, vp, vp, vp, i, vp, vp, f, vp]
     l.dtf_step_begin.argtypes = [vp, ll, vp, i, vp]
     l.dtf_fill.argtypes = [vp, ll, f, vp]
+    l.dtf_init_params.argtypes = [vp, vp, i, i, C.c_ulonglong, vp]
+    l.dtf_init_params.restype = i
     l.dtf_preprocess.argtypes = [vp, vp, vp, vp, i, i, i, i, i, C.c_ulonglong, C.c_ulonglong, vp, vp]
     l.dtf_preprocess_indexed.argtypes = [vp, vp, vp, vp, vp, vp, i, i, i, i, i, C.c_ulonglong, C.c_ulonglong, vp, vp]
     l.dtf_gemm.argtypes = [C.POINTER(Gemm), vp]
@@ -323,6 +333,15 @@ def sm_count() -> int:
 
 def fill(t: torch.Tensor, value: float) -> None:
     check(lib().dtf_fill(ptr(t), t.numel(), float(value), stream_ptr()), "dtf_fill")
+
+
+def init_params(params: torch.Tensor, segments, seed: int) -> None:
+    """Device-side initialisation of the flat parameter arena: `segments` = InitSegment list (Philox, keyed by seed)."""
+    arr = (InitSegment * len(segments))(*segments)
+    dev = struct_to_tensor(arr, params.device)
+    check(lib().dtf_init_params(ptr(params), ptr(dev), len(segments), max(s.count for s in segments),
+                                seed & (2 ** 64 - 1), stream_ptr()), "dtf_init_params")
+    del dev
 
 
 def preprocess(images_u8: torch.Tensor, indices: Optional[torch.Tensor], out: torch.Tensor, *, mode: int,

@@ -188,6 +188,19 @@ int dtf_optimizer_step(float* params, const float* grads, float* slot0, float* s
                        const long long* step, float grad_scale, cudaStream_t stream);
 int dtf_step_begin(float* zero_base, long long zero_floats, long long* step, int bump, cudaStream_t stream);
 int dtf_fill(float* p, long long n, float v, cudaStream_t stream);
+/* Parameter initialisation on the device (reference: tf.layers initialisers chosen per member,
+ * cifar10_main.py:167-199).  One segment per tensor of the flat arena; Philox4x32-10 keyed by `seed`, counter =
+ * (element / 4, segment), so a member's weights depend on (seed, layout) only. */
+enum { DTF_INIT_CONST = 0, DTF_INIT_UNIFORM = 1, DTF_INIT_TRUNC_NORMAL = 2 };
+typedef struct {
+    int offset, count;       /* elements in params */
+    int kind;                /* DTF_INIT_*: scale = the constant | half-width a of U(-a, a) | std of N(0, std) cut at 2 std */
+    float scale;
+    int c_pad, c_real;       /* innermost (input-channel) dim padded from c_real to c_pad: the padding is zeroed; 0 = none */
+    int reserved[2];
+} DtfInitSegment;
+int dtf_init_params(float* params, const DtfInitSegment* segs_dev, int n_segs, int max_count, unsigned long long seed,
+                    cudaStream_t stream);
 /* uint8 NHWC -> bf16 NHWC (channels padded to 8); mode 0 cast, 1 standardise, 2 crop+flip+standardise
  * (cifar10_main.py:96-109).  crop_flip: optional [n][3] = (oy, ox, flip) overriding the RNG.
  * mode | DTF_PP_F32 writes fp32 instead of bf16 (same 8 channels per pixel). */

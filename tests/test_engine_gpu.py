@@ -174,6 +174,46 @@ def test_lr_schedule_on_device(nat):
         close(w0 - eng.params[:n], torch.full((n,), lr, device="cuda"), 1e-4, 1e-7, f"lr at step {step}")
 
 
+@pytest.mark.parametrize("initializer", ["None", "he_init", "glorot_normal", "orthogonal"])
+def test_device_initialisers(nat, initializer):
+    """K15: initial weights drawn on the device (Philox, keyed by the member's seed) follow the distributions of the
+    host restatement of the tf.layers initialisers; `orthogonal` (QR) stays on the host."""
+    from distributedtf_b200.models import resnet
+    from distributedtf_b200.models.resnet_native import NativeResNetEngine
+    cfg = resnet.cifar10_config(14)
+    hp = {"opt_case": {"optimizer": "Momentum", "lr": 0.1, "momentum": 0.9}, "decay_steps": 20, "decay_rate": 0.1,
+          "weight_decay": 2e-4, "regularizer": "l2_regularizer", "initializer": initializer, "batch_size": 64}
+    a = NativeResNetEngine(cfg, hp, "cuda", seed=5, use_graphs=False)
+    b = NativeResNetEngine(cfg, hp, "cuda", seed=5, use_graphs=False)
+    c = NativeResNetEngine(cfg, hp, "cuda", seed=6, use_graphs=False)
+    assert torch.equal(a.params, b.params) and not torch.equal(a.params, c.params)
+    assert torch.equal(a.pack, b.pack)
+    named = a.export_named()
+    for k, v in named.items():
+        if k.endswith("/gamma") or k.endswith("moving_variance"):
+            assert (v == 1).all(), k
+        elif k.endswith("/beta") or k.endswith("moving_mean") or k == "dense/bias":
+            assert (v == 0).all(), k
+    assert (a.conv_weight(a.conv0)[..., 3:] == 0).all()                   # padded input channels of the first conv
+    lim = math.sqrt(6.0 / (64 + 10))
+    d = named["dense/kernel"]
+    assert d.abs().max().item() <= lim and abs(d.std().item() - lim / math.sqrt(3)) < 0.1 * lim
+    if initializer == "orthogonal":
+        return
+    w = torch.cat([named[f"conv{i}/kernel"].reshape(-1) for i in range(13, 16)])      # the three 64 -> 64 3x3 kernels
+    assert all(tuple(named[f"conv{i}/kernel"].shape) == (64, 3, 3, 64) for i in range(13, 16))
+    fan_in = fan_out = 9 * 64
+    assert abs(w.mean().item()) < 1e-3
+    if initializer == "None":
+        limit = math.sqrt(6.0 / (fan_in + fan_out))
+        assert w.abs().max().item() <= limit and abs(w.std().item() - limit / math.sqrt(3)) < 0.02 * limit
+    else:
+        std = math.sqrt(2.0 / fan_in) if initializer == "he_init" else math.sqrt(2.0 / (fan_in + fan_out))
+        assert w.abs().max().item() <= 2 * std * 1.0001
+        assert abs(w.std().item() - 0.8796 * std) < 0.02 * std                        # normal cut at two sigma
+        assert 0.02 < (w.abs() > 1.5 * std).float().mean().item() < 0.12            # and it does have tails
+
+
 def test_preprocess(nat):
     from distributedtf_b200.utils.data import cifar_preprocess_torch
     g = torch.Generator().manual_seed(0)
