@@ -41,8 +41,36 @@ class NativeMnistEngine(NativeEngineBase):
         self._build_plan()
         self._alloc_arena()
         self._alloc_buffers()
-        self.load_named_params(mnist_net.init_params(hparams.get("initializer", "None"), seed))
+        self._init_params(hparams.get("initializer", "None"), seed)
         self.set_hparams(hparams, reset_slots=True)
+
+    def _init_params(self, initializer: str, seed: int) -> None:
+        """Weights drawn on the device (``dtf_init_params``, Philox keyed by the member's seed): the two convolutions
+        and the 3136 -> 1024 layer take the member's initialiser, the logits layer the layer default, biases zero
+        (``mnist_model.py:62-126``).  ``orthogonal`` (QR) and ``DTF_HOST_INIT=1`` use the host restatement."""
+        import math
+        import os
+        if initializer == "orthogonal" or os.environ.get("DTF_HOST_INIT") == "1":
+            self.load_named_params(mnist_net.init_params(initializer, seed))
+            return
+
+        def kernel(off, count, fan_in, fan_out, init, c_pad=0, c_real=0):
+            if init == "glorot_normal":
+                kind, scale = native.INIT_TRUNC_NORMAL, math.sqrt(2.0 / (fan_in + fan_out))
+            elif init == "he_init":
+                kind, scale = native.INIT_TRUNC_NORMAL, math.sqrt(2.0 / fan_in)
+            else:
+                kind, scale = native.INIT_UNIFORM, math.sqrt(6.0 / (fan_in + fan_out))
+            return native.InitSegment(off, count, kind, scale, c_pad, c_real)
+
+        zero = lambda off, n: native.InitSegment(off, n, native.INIT_CONST, 0.0, 0, 0)
+        segs = [kernel(self.c0_w, 32 * 25 * IMG_C, 25 * 1, 25 * 32, initializer, IMG_C, 1), zero(self.c0_b, 32),
+                kernel(self.c1_w, 64 * 25 * 32, 25 * 32, 25 * 64, initializer), zero(self.c1_b, 64),
+                kernel(self.d0_w, 1024 * 3136, 3136, 1024, initializer), zero(self.d0_b, 1024),
+                kernel(self.d1_w, 10 * 1024, 1024, 10, "None"), zero(self.d1_b, 10)]
+        with torch.cuda.device(self.device):
+            native.init_params(self.params, segs, 0x9E3779B97F4A7C15 * (seed + 1))
+            self.repack()
 
     # ------------------------------------------------------------------ plan
     def _build_plan(self) -> None:

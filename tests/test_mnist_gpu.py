@@ -133,6 +133,26 @@ def _hp(opt="Momentum", lr=0.01, **extra):
             "regularizer": "None", "initializer": "glorot_normal", "batch_size": 96}
 
 
+def test_mnist_device_initialisers(nat):
+    """Weights of the MNIST member are drawn on the device: distribution per layer, zero biases, zero padding
+    channels, a function of the seed."""
+    from distributedtf_b200.models.mnist_native import NativeMnistEngine
+    a = NativeMnistEngine(_hp(), "cuda", seed=4, use_graphs=False)
+    b = NativeMnistEngine(_hp(), "cuda", seed=4, use_graphs=False)
+    c = NativeMnistEngine(_hp(), "cuda", seed=5, use_graphs=False)
+    assert torch.equal(a.params, b.params) and not torch.equal(a.params, c.params)
+    n = a.export_named()
+    assert all((n[k] == 0).all() for k in n if k.endswith("/bias"))
+    assert tuple(n["conv0/kernel"].shape) == (32, 5, 5, 1)
+    assert (a._view(a.params, a.c0_w, 32, 5, 5, 8)[..., 1:] == 0).all()
+    std0 = math.sqrt(2.0 / (3136 + 1024))                                   # glorot_normal, cut at two sigma
+    d0 = n["dense0/kernel"]
+    assert d0.abs().max().item() <= 2 * std0 * 1.0001 and abs(d0.std().item() - 0.8796 * std0) < 0.01 * std0
+    lim = math.sqrt(6.0 / (1024 + 10))                                      # logits layer: glorot_uniform
+    d1 = n["dense1/kernel"]
+    assert d1.abs().max().item() <= lim and abs(d1.std().item() - lim / math.sqrt(3)) < 0.03 * lim
+
+
 def test_native_mnist_step_matches_oracle(nat):
     from distributedtf_b200.models import mnist_net
     from distributedtf_b200.models.mnist_native import NativeMnistEngine
