@@ -88,6 +88,7 @@ bn_bwd_apply_kernel(const dtf_bf16* __restrict__ t, const dtf_bf16* __restrict__
 //   shortcut = none | sc (identity, already activated) | bn_sc(sc) (projection: conv + BN, resnet_model.py:127-168)
 // CTA 0 also updates the moving averages of the BatchNorm layers it applies (training).
 // ---------------------------------------------------------------------------------------
+template <int E>
 __global__ void __launch_bounds__(256)
 bn_act_apply_kernel(const dtf_bf16* __restrict__ x, DtfBnRef bn, const dtf_bf16* __restrict__ sc, DtfBnRef bn_sc,
                     int sc_mode, dtf_bf16* __restrict__ out, long long total_vec, int C, int update_running) {
@@ -115,20 +116,23 @@ bn_act_apply_kernel(const dtf_bf16* __restrict__ x, DtfBnRef bn, const dtf_bf16*
         }
     }
     __syncthreads();
-    const int cvec = C / 8;
+    const int cvec = C / E;
+    const uint4* xv = reinterpret_cast<const uint4*>(x);
+    const uint4* sv = reinterpret_cast<const uint4*>(sc);
+    uint4* ov = reinterpret_cast<uint4*>(out);
     for (long long v = blockIdx.x * (long long)blockDim.x + threadIdx.x; v < total_vec;
          v += (long long)gridDim.x * blockDim.x) {
-        const int cb = static_cast<int>(v % cvec) * 8;
-        float fx[8], fs[8];
-        unpack8(ldg16(x + v * 8), fx);
-        if (sc_mode != 0) unpack8(ldg16(sc + v * 8), fs);
+        const int cb = static_cast<int>(v % cvec) * E;
+        float fx[E], fs[E];
+        unpack_vec<E>(ldg16(xv + v), fx);
+        if (sc_mode != 0) unpack_vec<E>(ldg16(sv + v), fs);
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
+        for (int i = 0; i < E; ++i) {
             float y = fmaf(fx[i], a0[cb + i], a1[cb + i]);
             if (sc_mode != 0) y += fmaf(fs[i], b0[cb + i], b1[cb + i]);
             fx[i] = fmaxf(y, 0.f);
         }
-        *reinterpret_cast<uint4*>(out + v * 8) = pack8(fx);
+        ov[v] = pack_vec<E>(fx);
     }
 }
 
@@ -138,6 +142,7 @@ bn_act_apply_kernel(const dtf_bf16* __restrict__ x, DtfBnRef bn, const dtf_bf16*
 // same against the projection's BatchNorm input when there is one.  The convolutions upstream then apply the
 // BN-backward combination in their operand gather (DTF_PRO_BN_BWD), exactly as in the v2 blocks.
 // ---------------------------------------------------------------------------------------
+template <int E>
 __global__ void __launch_bounds__(256)
 relu_bwd_stats_kernel(const dtf_bf16* __restrict__ dy, const dtf_bf16* __restrict__ y, dtf_bf16* __restrict__ t_out,
                       const dtf_bf16* __restrict__ x, DtfBnRef bn, float* __restrict__ stats,
@@ -154,26 +159,31 @@ relu_bwd_stats_kernel(const dtf_bf16* __restrict__ dy, const dtf_bf16* __restric
         acc[0][c] = acc[1][c] = acc[2][c] = acc[3][c] = 0.f;
     }
     __syncthreads();
-    const int cvec = C / 8;
-    // a thread keeps the same 8 channels for all its vectors when the stride is a multiple of cvec
+    const int cvec = C / E;
+    // a thread keeps the same E channels for all its vectors when the stride is a multiple of cvec
     const long long stride = (long long)gridDim.x * blockDim.x;
     const bool fixed = (stride % cvec) == 0;
-    float s[4][8];
+    float s[4][E];
 #pragma unroll
     for (int k = 0; k < 4; ++k)
 #pragma unroll
-        for (int i = 0; i < 8; ++i) s[k][i] = 0.f;
+        for (int i = 0; i < E; ++i) s[k][i] = 0.f;
     int cb_fixed = 0;
+    const uint4* dyv = reinterpret_cast<const uint4*>(dy);
+    const uint4* yv = reinterpret_cast<const uint4*>(y);
+    const uint4* xv = reinterpret_cast<const uint4*>(x);
+    const uint4* x2v = reinterpret_cast<const uint4*>(x2);
+    uint4* tv = reinterpret_cast<uint4*>(t_out);
     for (long long v = blockIdx.x * (long long)blockDim.x + threadIdx.x; v < total_vec; v += stride) {
-        const int cb = static_cast<int>(v % cvec) * 8;
+        const int cb = static_cast<int>(v % cvec) * E;
         cb_fixed = cb;
-        float g[8], fy[8], fx[8], fx2[8];
-        unpack8(ldg16(dy + v * 8), g);
-        unpack8(ldg16(y + v * 8), fy);
-        unpack8(ldg16(x + v * 8), fx);
-        if (x2 != nullptr) unpack8(ldg16(x2 + v * 8), fx2);
+        float g[E], fy[E], fx[E], fx2[E];
+        unpack_vec<E>(ldg16(dyv + v), g);
+        unpack_vec<E>(ldg16(yv + v), fy);
+        unpack_vec<E>(ldg16(xv + v), fx);
+        if (x2 != nullptr) unpack_vec<E>(ldg16(x2v + v), fx2);
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
+        for (int i = 0; i < E; ++i) {
             const float t = fy[i] > 0.f ? g[i] : 0.f;
             g[i] = t;
             const float h1 = t * (fx[i] - m1[cb + i]) * i1[cb + i];
@@ -184,11 +194,11 @@ relu_bwd_stats_kernel(const dtf_bf16* __restrict__ dy, const dtf_bf16* __restric
                 if (x2 != nullptr) atomicAdd(&acc[2][cb + i], h2);
             }
         }
-        *reinterpret_cast<uint4*>(t_out + v * 8) = pack8(g);
+        tv[v] = pack_vec<E>(g);
     }
     if (fixed) {
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
+        for (int i = 0; i < E; ++i) {
             atomicAdd(&acc[0][cb_fixed + i], s[0][i]);
             atomicAdd(&acc[1][cb_fixed + i], s[1][i]);
             if (x2 != nullptr) atomicAdd(&acc[2][cb_fixed + i], s[2][i]);
@@ -633,34 +643,56 @@ extern "C" int dtf_bn_bwd_apply(const dtf_bf16* t, const dtf_bf16* x, const dtf_
     return dtf_bn_bwd_apply_dt(t, x, res, out, bn, bwd_stats, pixels, C, DTF_BF16, stream);
 }
 
-extern "C" int dtf_bn_act_apply(const dtf_bf16* x, const DtfBnRef* bn, const dtf_bf16* sc, const DtfBnRef* bn_sc,
-                                dtf_bf16* out, long long pixels, int C, int update_running, cudaStream_t stream) {
+extern "C" int dtf_bn_act_apply_dt(const dtf_bf16* x, const DtfBnRef* bn, const dtf_bf16* sc, const DtfBnRef* bn_sc,
+                                   dtf_bf16* out, long long pixels, int C, int update_running, int dtype,
+                                   cudaStream_t stream) {
     if (C % 8 != 0 || C > 256 || bn == nullptr) return DTF_ERR_SHAPE;
-    const long long total_vec = pixels * (C / 8);
+    if (dtype != DTF_BF16 && dtype != DTF_F32) return DTF_ERR_ARG;
+    const long long total_vec = pixels * (C / (dtype == DTF_F32 ? 4 : 8));
     long long blocks = (total_vec + 255) / 256;
     if (blocks > 148 * 8) blocks = 148 * 8;
     const int sc_mode = sc == nullptr ? 0 : (bn_sc == nullptr ? 1 : 2);
     DtfBnRef none = {};
-    dtf_launch(dtf::bn_act_apply_kernel, dim3(static_cast<int>(blocks)), dim3(256), 0, stream, x, *bn, sc,
-               bn_sc ? *bn_sc : none, sc_mode, out, total_vec, C, update_running);
+    if (dtype == DTF_F32)
+        dtf_launch(dtf::bn_act_apply_kernel<4>, dim3(static_cast<int>(blocks)), dim3(256), 0, stream, x, *bn, sc,
+                   bn_sc ? *bn_sc : none, sc_mode, out, total_vec, C, update_running);
+    else
+        dtf_launch(dtf::bn_act_apply_kernel<8>, dim3(static_cast<int>(blocks)), dim3(256), 0, stream, x, *bn, sc,
+                   bn_sc ? *bn_sc : none, sc_mode, out, total_vec, C, update_running);
+    return DTF_CHECK_LAUNCH();
+}
+
+extern "C" int dtf_bn_act_apply(const dtf_bf16* x, const DtfBnRef* bn, const dtf_bf16* sc, const DtfBnRef* bn_sc,
+                                dtf_bf16* out, long long pixels, int C, int update_running, cudaStream_t stream) {
+    return dtf_bn_act_apply_dt(x, bn, sc, bn_sc, out, pixels, C, update_running, DTF_BF16, stream);
+}
+
+extern "C" int dtf_relu_bwd_stats_dt(const dtf_bf16* dy, const dtf_bf16* y, dtf_bf16* t_out, const dtf_bf16* x,
+                                     const DtfBnRef* bn, float* stats, const dtf_bf16* x2, const DtfBnRef* bn2,
+                                     float* stats2, long long pixels, int C, int dtype, cudaStream_t stream) {
+    if (C % 8 != 0 || C > 256 || bn == nullptr || stats == nullptr) return DTF_ERR_SHAPE;
+    if (x2 != nullptr && (bn2 == nullptr || stats2 == nullptr)) return DTF_ERR_ARG;
+    if (dtype != DTF_BF16 && dtype != DTF_F32) return DTF_ERR_ARG;
+    const int cvec = C / (dtype == DTF_F32 ? 4 : 8);
+    const long long total_vec = pixels * cvec;
+    long long blocks = (total_vec + 255) / 256;
+    if (blocks > 148 * 4) blocks = 148 * 4;
+    // keep the grid stride a multiple of the channel-vector count: each thread then owns fixed channels
+    while (blocks > 1 && (blocks * 256) % cvec != 0) --blocks;
+    DtfBnRef none = {};
+    if (dtype == DTF_F32)
+        dtf_launch(dtf::relu_bwd_stats_kernel<4>, dim3(static_cast<int>(blocks)), dim3(256), 0, stream, dy, y, t_out, x,
+                   *bn, stats, x2, bn2 ? *bn2 : none, stats2, total_vec, C);
+    else
+        dtf_launch(dtf::relu_bwd_stats_kernel<8>, dim3(static_cast<int>(blocks)), dim3(256), 0, stream, dy, y, t_out, x,
+                   *bn, stats, x2, bn2 ? *bn2 : none, stats2, total_vec, C);
     return DTF_CHECK_LAUNCH();
 }
 
 extern "C" int dtf_relu_bwd_stats(const dtf_bf16* dy, const dtf_bf16* y, dtf_bf16* t_out, const dtf_bf16* x,
                                   const DtfBnRef* bn, float* stats, const dtf_bf16* x2, const DtfBnRef* bn2,
                                   float* stats2, long long pixels, int C, cudaStream_t stream) {
-    if (C % 8 != 0 || C > 256 || bn == nullptr || stats == nullptr) return DTF_ERR_SHAPE;
-    if (x2 != nullptr && (bn2 == nullptr || stats2 == nullptr)) return DTF_ERR_ARG;
-    const long long total_vec = pixels * (C / 8);
-    const int cvec = C / 8;
-    long long blocks = (total_vec + 255) / 256;
-    if (blocks > 148 * 4) blocks = 148 * 4;
-    // keep the grid stride a multiple of the channel-vector count: each thread then owns fixed channels
-    while (blocks > 1 && (blocks * 256) % cvec != 0) --blocks;
-    DtfBnRef none = {};
-    dtf_launch(dtf::relu_bwd_stats_kernel, dim3(static_cast<int>(blocks)), dim3(256), 0, stream, dy, y, t_out, x, *bn,
-               stats, x2, bn2 ? *bn2 : none, stats2, total_vec, C);
-    return DTF_CHECK_LAUNCH();
+    return dtf_relu_bwd_stats_dt(dy, y, t_out, x, bn, stats, x2, bn2, stats2, pixels, C, DTF_BF16, stream);
 }
 
 extern "C" int dtf_head(const DtfHead* p, cudaStream_t stream) {

@@ -18,7 +18,7 @@ from ..utils.data import (CIFAR_EVAL, CIFAR_TRAIN, cifar_preprocess_torch, load_
 from . import resnet
 from ._member import GpuMember
 
-_DTYPES = {"fp32": torch.float32, "bf16": torch.bfloat16, "fp16": torch.float16}
+_DTYPES = {"fp32": torch.float32, "tf32": torch.float32, "bf16": torch.bfloat16, "fp16": torch.float16}
 
 
 class Cifar10Model(GpuMember):

@@ -18,7 +18,7 @@ from ..utils.data import MNIST_EVAL, MNIST_TRAIN, load_mnist, synthetic_dataset
 from . import mnist_net
 from ._member import GpuMember
 
-_DTYPES = {"fp32": torch.float32, "bf16": torch.bfloat16, "fp16": torch.float16}
+_DTYPES = {"fp32": torch.float32, "tf32": torch.float32, "bf16": torch.bfloat16, "fp16": torch.float16}
 
 
 class MNISTModel(GpuMember):

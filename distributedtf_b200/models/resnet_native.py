@@ -78,7 +78,6 @@ class Block:
 
 class NativeResNetEngine(NativeEngineBase):
     version = 2
-    supports_f32 = True
     act_dtype = torch.bfloat16
     E = 8
 
@@ -88,8 +87,6 @@ class NativeResNetEngine(NativeEngineBase):
         self._check_config(cfg)
         if dtype not in ("bf16", "fp16", "tf32", "fp32"):
             raise NotImplementedError(f"native engine: dtype {dtype!r}")
-        if dtype in ("tf32", "fp32") and not self.supports_f32:
-            raise NotImplementedError("fp32 / tf32 tensors: v2 engines only (the v1 block-tail kernels are bf16)")
         super().__init__(device, max_batch=max_batch, use_graphs=use_graphs, arena_alloc=arena_alloc,
                          dp_group=dp_group, seed=seed, all_reduce_alg=all_reduce_alg)
         # dtype "fp16" = the reference's mixed-precision mode (fp32 master weights, static loss scale 128,

@@ -180,7 +180,6 @@ class NativeResNetBottleneckV1Engine(NativeResNetV1Engine):
     """ResNet v1 with bottleneck blocks (post-activation; the block output is written by the tail kernel)."""
     version = 1
     bottleneck = True
-    supports_f32 = False
 
     def _check_config(self, cfg) -> None:
         if cfg.resnet_version != 1:

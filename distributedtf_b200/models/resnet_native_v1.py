@@ -42,7 +42,6 @@ class BlockV1:
 
 class NativeResNetV1Engine(NativeResNetEngine):
     version = 1
-    supports_f32 = False
 
     # ------------------------------------------------------------------ plan (parameter order = models/resnet.py)
     def _build_plan(self) -> None:
@@ -183,6 +182,7 @@ class NativeResNetV1Engine(NativeResNetEngine):
         h.batch, h.HW, h.C, h.classes = nb, self.final_h ** 2, self.final_c, self.cfg.num_classes
         h.has_bn, h.training, h.update_running = 0, int(training), 0        # v1: no BN in front of the pool
         h.board_hits = 0 if training else self.board_slot_ptr
+        h.dtype = native.dtype_code(x)
         native.head(h)
         self._count += 1
 

@@ -150,6 +150,10 @@ def _declare(l: C.CDLL) -> None:
     l.dtf_bn_act_apply.restype = i
     l.dtf_relu_bwd_stats.argtypes = [vp, vp, vp, vp, C.POINTER(BnRef), vp, vp, C.POINTER(BnRef), vp, ll, i, vp]
     l.dtf_relu_bwd_stats.restype = i
+    l.dtf_bn_act_apply_dt.argtypes = [vp, C.POINTER(BnRef), vp, C.POINTER(BnRef), vp, ll, i, i, i, vp]
+    l.dtf_bn_act_apply_dt.restype = i
+    l.dtf_relu_bwd_stats_dt.argtypes = [vp, vp, vp, vp, C.POINTER(BnRef), vp, vp, C.POINTER(BnRef), vp, ll, i, i, vp]
+    l.dtf_relu_bwd_stats_dt.restype = i
     l.dtf_pack_weights.argtypes = [vp, vp, vp, vp, i, vp]
     l.dtf_optimizer_step.argtypes = [vp, vp, vp, vp, vp, vp, vp, i, vp, vp, f, vp]
     l.dtf_step_begin.argtypes = [vp, ll, vp, i, vp]
@@ -289,16 +293,17 @@ def bn_bwd_apply(t, x, res, out, bn: BnRef, bwd_stats, pixels: int, channels: in
 def bn_act_apply(x, bn: BnRef, out, pixels: int, channels: int, *, sc=None, bn_sc: Optional[BnRef] = None,
                  update_running: bool = False) -> None:
     """ResNet v1 block tail: out = relu(bn(x) + shortcut); shortcut = none | sc | bn_sc(sc)."""
-    check(lib().dtf_bn_act_apply(ptr(x), C.byref(bn), ptr(sc), C.byref(bn_sc) if bn_sc is not None else None, ptr(out),
-                                 pixels, channels, int(update_running), stream_ptr()), "dtf_bn_act_apply")
+    check(lib().dtf_bn_act_apply_dt(ptr(x), C.byref(bn), ptr(sc), C.byref(bn_sc) if bn_sc is not None else None,
+                                    ptr(out), pixels, channels, int(update_running), dtype_code(out), stream_ptr()),
+          "dtf_bn_act_apply")
 
 
 def relu_bwd_stats(dy, y, t_out, x, bn: BnRef, stats, pixels: int, channels: int, *, x2=None,
                    bn2: Optional[BnRef] = None, stats2=None) -> None:
     """Backward of the v1 block tail: t = dy * (y > 0) plus the BN-backward sums against x (and x2)."""
-    check(lib().dtf_relu_bwd_stats(ptr(dy), ptr(y), ptr(t_out), ptr(x), C.byref(bn), ptr(stats), ptr(x2),
-                                   C.byref(bn2) if bn2 is not None else None, ptr(stats2), pixels, channels,
-                                   stream_ptr()), "dtf_relu_bwd_stats")
+    check(lib().dtf_relu_bwd_stats_dt(ptr(dy), ptr(y), ptr(t_out), ptr(x), C.byref(bn), ptr(stats), ptr(x2),
+                                      C.byref(bn2) if bn2 is not None else None, ptr(stats2), pixels, channels,
+                                      dtype_code(t_out), stream_ptr()), "dtf_relu_bwd_stats")
 
 
 def head(p: Head) -> None:

@@ -178,6 +178,12 @@ int dtf_bn_act_apply(const dtf_bf16* x, const DtfBnRef* bn, const dtf_bf16* sc, 
 int dtf_relu_bwd_stats(const dtf_bf16* dy, const dtf_bf16* y, dtf_bf16* t_out, const dtf_bf16* x, const DtfBnRef* bn,
                        float* stats, const dtf_bf16* x2, const DtfBnRef* bn2, float* stats2, long long pixels, int C,
                        cudaStream_t stream);
+/* The same two for tensors of element type `dtype` (DTF_BF16 | DTF_F32). */
+int dtf_bn_act_apply_dt(const dtf_bf16* x, const DtfBnRef* bn, const dtf_bf16* sc, const DtfBnRef* bn_sc, dtf_bf16* out,
+                        long long pixels, int C, int update_running, int dtype, cudaStream_t stream);
+int dtf_relu_bwd_stats_dt(const dtf_bf16* dy, const dtf_bf16* y, dtf_bf16* t_out, const dtf_bf16* x, const DtfBnRef* bn,
+                          float* stats, const dtf_bf16* x2, const DtfBnRef* bn2, float* stats2, long long pixels, int C,
+                          int dtype, cudaStream_t stream);
 /* chunks: n_chunks x {segment index, first element} pairs; each CTA handles DTF_OPT_CHUNK elements */
 int dtf_pack_weights(const float* params, dtf_bf16* pack, const DtfOptSegment* segs, const int* chunks,
                      int n_chunks, cudaStream_t stream);

@@ -40,8 +40,9 @@ def test_cifar_population_one_gpu_p2p(tmp_path):
 
 @pytest.mark.parametrize("kw", [dict(resnet_bottleneck=True, resnet_size=11),
                                 dict(resnet_bottleneck=True, resnet_size=11, resnet_version=1),
-                                dict(dtype="tf32"), dict(dtype="fp32", resnet_bottleneck=True, resnet_size=11)],
-                         ids=["bottleneck-v2", "bottleneck-v1", "tf32", "fp32-bottleneck"])
+                                dict(dtype="tf32"), dict(dtype="fp32", resnet_bottleneck=True, resnet_size=11),
+                                dict(dtype="tf32", resnet_version=1)],
+                         ids=["bottleneck-v2", "bottleneck-v1", "tf32", "fp32-bottleneck", "tf32-v1"])
 def test_population_of_the_other_native_engines(tmp_path, kw):
     """Bottleneck blocks (v1, v2) and fp32 / tf32 compute stay on the native engines through a whole PBT run with
     exploit + explore (`engine="native"` raises if a configuration had to fall back to the torch engine)."""

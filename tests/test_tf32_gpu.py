@@ -211,8 +211,9 @@ def test_bn_bwd_apply_and_preprocess_fp32(nat):
     close(o32[..., :3], (xf - mean) / std, 1e-4, 1e-4, "per-image standardisation")
 
 
-@pytest.mark.parametrize("bottleneck,size,nb", [(False, 8, 32), (False, 14, 64), (True, 11, 32)])
-def test_native_tf32_step_matches_fp32_oracle(nat, bottleneck, size, nb):
+@pytest.mark.parametrize("version,bottleneck,size,nb", [(2, False, 8, 32), (2, False, 14, 64), (2, True, 11, 32),
+                                                        (1, False, 8, 32), (1, True, 11, 32)])
+def test_native_tf32_step_matches_fp32_oracle(nat, version, bottleneck, size, nb):
     """One full training step with fp32 tensors / tf32 MMAs against autograd on the fp32 oracle.  The gradient error
     is ReLU-mask noise, as in the bf16 test, but from tf32's 1e-3 instead of bf16's 4e-3 relative error: a
     pre-activation flips its mask when it lies that close to zero, each flip is a full-size error, so the relative
@@ -220,10 +221,13 @@ def test_native_tf32_step_matches_fp32_oracle(nat, bottleneck, size, nb):
     bf16 engine on the same networks) -- every tensor is held to 15 % and a cosine of 0.985."""
     from distributedtf_b200.models import resnet
     from distributedtf_b200.models.resnet_native import NativeResNetEngine
-    from distributedtf_b200.models.resnet_native_bottleneck import NativeResNetBottleneckEngine
+    from distributedtf_b200.models.resnet_native_bottleneck import (NativeResNetBottleneckEngine,
+                                                                    NativeResNetBottleneckV1Engine)
+    from distributedtf_b200.models.resnet_native_v1 import NativeResNetV1Engine
     from distributedtf_b200.utils.data import cifar_preprocess_torch
-    cfg = resnet.cifar10_config(size, bottleneck=bottleneck)
-    cls = NativeResNetBottleneckEngine if bottleneck else NativeResNetEngine
+    cfg = resnet.cifar10_config(size, resnet_version=version, bottleneck=bottleneck)
+    cls = {(2, False): NativeResNetEngine, (2, True): NativeResNetBottleneckEngine,
+           (1, False): NativeResNetV1Engine, (1, True): NativeResNetBottleneckV1Engine}[(version, bottleneck)]
     hp = {"opt_case": {"optimizer": "Momentum", "lr": 0.1, "momentum": 0.9}, "decay_steps": 20, "decay_rate": 0.1,
           "weight_decay": 2e-4, "regularizer": "l2_regularizer", "initializer": "he_init", "batch_size": nb}
     eng = cls(cfg, hp, "cuda", seed=5, use_graphs=False, dtype="tf32")
