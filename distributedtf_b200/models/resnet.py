@@ -206,11 +206,13 @@ def batch_norm(x: torch.Tensor, gamma, beta, mean, var, training: bool,
 
 class _ExecOps(_Ops):
     def __init__(self, cfg, params: Dict[str, torch.Tensor], x: torch.Tensor, training: bool,
-                 taps: Optional[Dict[str, torch.Tensor]] = None, emulate_bf16: bool = False):
+                 taps: Optional[Dict[str, torch.Tensor]] = None, emulate_bf16: bool = False,
+                 relu_masks: Optional[Sequence[torch.Tensor]] = None):
         self.cfg, self.p, self.x, self.training = cfg, params, x, training
-        self._bn = self._conv = self._add = 0
+        self._bn = self._conv = self._add = self._relu = 0
         self.taps = taps
         self.emulate_bf16 = emulate_bf16
+        self.relu_masks = relu_masks
 
     def _tap(self, name, t):
         if self.emulate_bf16 and name.startswith("conv") and getattr(self, "fused_add_next", False):
@@ -241,7 +243,13 @@ class _ExecOps(_Ops):
                        p[name + "/moving_variance"], self.training)
         return self._tap(name, y.to(x.dtype))
 
-    def relu(self, x): return F.relu(x)
+    def relu(self, x):
+        k = self._relu
+        self._relu += 1
+        if self.relu_masks is not None:      # masks taken from another implementation's activations (see forward)
+            return x * self.relu_masks[k].to(x.dtype)
+        return F.relu(x)
+
     def maxpool(self, x, k, s): return F.max_pool2d(x, k, s, padding=(k - 1) // 2)
     def add(self, a, b):
         name = f"add{self._add}"
@@ -256,11 +264,13 @@ class _ExecOps(_Ops):
 
 def forward(cfg: ResNetConfig, params: Dict[str, torch.Tensor], images_nchw: torch.Tensor,
             training: bool, taps: Optional[Dict[str, torch.Tensor]] = None,
-            emulate_bf16: bool = False) -> torch.Tensor:
+            emulate_bf16: bool = False, relu_masks: Optional[Sequence[torch.Tensor]] = None) -> torch.Tensor:
     """Logits ``[N, num_classes]`` (fp32).  ``params`` maps ``ParamSpec.name`` -> tensor.
     ``emulate_bf16`` rounds conv operands and stored activations to bf16 (straight-through
-    gradients), reproducing where the native engine rounds."""
-    return _walk(cfg, _ExecOps(cfg, params, images_nchw, training, taps, emulate_bf16)).float()
+    gradients), reproducing where the native engine rounds.  ``relu_masks`` (one 0/1 NCHW tensor per ReLU, in call
+    order) replaces every ``relu(x)`` by ``x * mask``: with the masks of the native engine's own activations the
+    comparison of gradients is free of mask flips and measures the arithmetic alone."""
+    return _walk(cfg, _ExecOps(cfg, params, images_nchw, training, taps, emulate_bf16, relu_masks)).float()
 
 
 def init_params(cfg: ResNetConfig, initializer: str, seed: int = 0,
