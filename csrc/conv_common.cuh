@@ -211,6 +211,21 @@ DTF_DEVINL uint4 gather16(const DtfGather& g, const int8_t* tap_dy, const int8_t
     return gather_finish<8>(g, p0, p1, p2, L);
 }
 
+// Shared-memory address of chunk jj (counted from the first chunk of the call) of one row.
+//   SW = false: chunk-major, [chunk][128 rows][16 bytes] (K-major operands, and MN-major bf16 operands);
+//                `dst` = buffer + row * 16.
+//   SW = true : the one MN-major layout kind::tf32 accepts (measured with bench/probe_umma.py: no-swizzle, 32B, 64B
+//                and plain 128B MN-major descriptors read zeros for tf32): layout type 1, "128-byte swizzle with a
+//                32-byte base".  Rows of 128 bytes = 32 channels at a 128-byte pitch, blocks of 32 channels 16 KB
+//                apart, and within a row the 32-byte unit index is XOR-ed with (row & 3).
+//                `dst` = buffer + row * 128, `sw` = (row & 3) << 1 in units of 16-byte chunks.
+constexpr uint32_t kSwBlockBytes = kTileM * 128;       // one 32-channel block of a 128-row tile
+template <bool SW>
+DTF_DEVINL uint32_t chunk_addr(uint32_t dst, int jj, uint32_t sw) {
+    if (SW) return dst + (static_cast<uint32_t>(jj >> 3) * kSwBlockBytes) + (((static_cast<uint32_t>(jj) & 7u) ^ sw) << 4);
+    return dst + jj * (kTileM * 16);
+}
+
 // ---- row gather, tap-major ---------------------------------------------------------------
 // Chunks j in [jbeg, jend) of one im2col row, written to dst + (j - jbeg) * 2 KB.  One thread owns the
 // whole row of a tile; the two gather groups (4 warps each) work on alternate tiles so that two tiles'
@@ -235,10 +250,10 @@ DTF_DEVINL RowPre row_pre(const DtfGather& g, const RowCoord& rc) {
 // One batch of TPB taps starting at t0 (taps beyond t_end are dead).  Gather warps share an issue port
 // with one other warp only, so the serial instruction stream per tile is what bounds small-K layers:
 // the caller picks TPB to match the live tap count instead of predicating a fixed-size batch.
-template <int L, bool TWO, int TPB>
+template <int L, bool TWO, int TPB, int E = 8, bool SW = false>
 DTF_DEVINL void gather_batch_t(const DtfGather& g, const int8_t* tap_dy, const int8_t* tap_dx,
                                const float* p0, const float* p1, const float* p2, const RowPre& rp,
-                               int jbeg, int jend, uint32_t dst, int t0, int t_end) {
+                               int jbeg, int jend, uint32_t dst, int t0, int t_end, uint32_t sw = 0) {
     constexpr int CPT = 1 << L;
     constexpr int PER = CPT;                                  // chunks per tap
     constexpr int TSTEP = 1;
@@ -269,8 +284,8 @@ DTF_DEVINL void gather_batch_t(const DtfGather& g, const int8_t* tap_dy, const i
             const int c8 = c;
             const int j = (t << L) + c8;
             const bool live = ok && j >= jbeg && j < jend && j < g.kchunks_real;
-            v[u * PER + c] = live ? ldg16(g.src + off + c8 * 8) : make_uint4(0, 0, 0, 0);
-            if (TWO) x[u * PER + c] = live ? ldg16(g.src2 + off + c8 * 8) : make_uint4(0, 0, 0, 0);
+            v[u * PER + c] = live ? ldg16(elem_ptr<E>(g.src, off + c8 * E)) : make_uint4(0, 0, 0, 0);
+            if (TWO) x[u * PER + c] = live ? ldg16(elem_ptr<E>(g.src2, off + c8 * E)) : make_uint4(0, 0, 0, 0);
             okmask |= (live ? 1u : 0u) << (u * PER + c);
         }
     }
@@ -283,29 +298,29 @@ DTF_DEVINL void gather_batch_t(const DtfGather& g, const int8_t* tap_dy, const i
             const int j = (t << L) + c8;
             uint4 r = v[u * PER + c];
             if (g.mode != DTF_PRO_NONE && ((okmask >> (u * PER + c)) & 1)) {
-                float f[8];
-                unpack8(r, f);
-                const int cb = c8 * 8;
+                float f[E];
+                unpack_chunk<E>(r, f);
+                const int cb = c8 * E;
                 if (!TWO) {
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) f[i] = fmaxf(fmaf(f[i], p0[cb + i], p1[cb + i]), 0.f);
+                    for (int i = 0; i < E; ++i) f[i] = fmaxf(fmaf(f[i], p0[cb + i], p1[cb + i]), 0.f);
                 } else {
-                    float xx[8];
-                    unpack8(x[u * PER + c], xx);
+                    float xx[E];
+                    unpack_chunk<E>(x[u * PER + c], xx);
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) f[i] = fmaf(f[i], p0[cb + i], fmaf(xx[i], p1[cb + i], p2[cb + i]));
+                    for (int i = 0; i < E; ++i) f[i] = fmaf(f[i], p0[cb + i], fmaf(xx[i], p1[cb + i], p2[cb + i]));
                 }
-                r = pack8(f);
+                r = pack_chunk<E>(f);
             }
-            if (t < t_end && j >= jbeg && j < jend) sts16(dst + (j - jbeg) * (kTileM * 16), r);
+            if (t < t_end && j >= jbeg && j < jend) sts16(chunk_addr<SW>(dst, j - jbeg, sw), r);
         }
     }
 }
 
-template <int L, bool TWO>
+template <int L, bool TWO, int E = 8, bool SW = false>
 DTF_DEVINL void gather_taps_t(const DtfGather& g, const int8_t* tap_dy, const int8_t* tap_dx,
                               const float* p0, const float* p1, const float* p2, const RowPre& rp,
-                              int jbeg, int jend, uint32_t dst) {
+                              int jbeg, int jend, uint32_t dst, uint32_t sw = 0) {
     constexpr int PER = 1 << L;
     constexpr int BUDGET = TWO ? 4 : 8;                       // 16-byte loads in flight per source
     constexpr int TMAX = BUDGET / PER > 0 ? BUDGET / PER : 1; // taps per full batch
@@ -314,7 +329,7 @@ DTF_DEVINL void gather_taps_t(const DtfGather& g, const int8_t* tap_dy, const in
     const int t_end = ((jend - 1) >> L) + 1;
 #define DTF_BATCH(N)                                                                                       \
     {                                                                                                      \
-        gather_batch_t<L, TWO, N>(g, tap_dy, tap_dx, p0, p1, p2, rp, jbeg, jend, dst, t, t_end);           \
+        gather_batch_t<L, TWO, N, E, SW>(g, tap_dy, tap_dx, p0, p1, p2, rp, jbeg, jend, dst, t, t_end, sw); \
         t += N * TSTEP;                                                                                    \
     }
     while (t < t_end) {
@@ -338,21 +353,6 @@ DTF_DEVINL void gather_chunks_slow(const DtfGather& g, const int8_t* tap_dy, con
 // Wide channel counts (128 / 256: the 1x1 convolutions of bottleneck blocks): the chunks of a row are taken in
 // batches whose loads are all in flight before the first one is consumed (8 x 16 bytes per source, 4 with the
 // second source of the BN-backward prologue).
-// Shared-memory address of chunk jj (counted from the first chunk of the call) of one row.
-//   SW = false: chunk-major, [chunk][128 rows][16 bytes] (K-major operands, and MN-major bf16 operands);
-//                `dst` = buffer + row * 16.
-//   SW = true : the one MN-major layout kind::tf32 accepts (measured with bench/probe_umma.py: no-swizzle, 32B, 64B
-//                and plain 128B MN-major descriptors read zeros for tf32): layout type 1, "128-byte swizzle with a
-//                32-byte base".  Rows of 128 bytes = 32 channels at a 128-byte pitch, blocks of 32 channels 16 KB
-//                apart, and within a row the 32-byte unit index is XOR-ed with (row & 3).
-//                `dst` = buffer + row * 128, `sw` = (row & 3) << 1 in units of 16-byte chunks.
-constexpr uint32_t kSwBlockBytes = kTileM * 128;       // one 32-channel block of a 128-row tile
-template <bool SW>
-DTF_DEVINL uint32_t chunk_addr(uint32_t dst, int jj, uint32_t sw) {
-    if (SW) return dst + (static_cast<uint32_t>(jj >> 3) * kSwBlockBytes) + (((static_cast<uint32_t>(jj) & 7u) ^ sw) << 4);
-    return dst + jj * (kTileM * 16);
-}
-
 template <bool TWO, int E = 8, bool SW = false>
 DTF_DEVINL void gather_chunks_wide(const DtfGather& g, const int8_t* tap_dy, const int8_t* tap_dx,
                                    const float* p0, const float* p1, const float* p2, const RowCoord& rc,
@@ -373,11 +373,25 @@ template <int E = 8, bool SW = false>
 DTF_DEVINL void gather_row(const DtfGather& g, const int8_t* tap_dy, const int8_t* tap_dx,
                            const float* p0, const float* p1, const float* p2, const RowCoord& rc,
                            int jbeg, int jend, uint32_t dst, uint32_t sw = 0) {
-    if (E != 8) {          // fp32 tensors: every layer takes the batched generic path
-        if (g.mode == DTF_PRO_BN_BWD)
-            gather_chunks_wide<true, E, SW>(g, tap_dy, tap_dx, p0, p1, p2, rc, jbeg, jend, dst, sw);
-        else
-            gather_chunks_wide<false, E, SW>(g, tap_dy, tap_dx, p0, p1, p2, rc, jbeg, jend, dst, sw);
+    if (E != 8) {          // fp32 tensors: tap-major batches up to 8 chunks (32 channels) per tap, else chunk batches
+        const bool two32 = g.mode == DTF_PRO_BN_BWD;
+        if (g.cpt_shift > 3 || g.stride > 2) {
+            if (two32) gather_chunks_wide<true, E, SW>(g, tap_dy, tap_dx, p0, p1, p2, rc, jbeg, jend, dst, sw);
+            else gather_chunks_wide<false, E, SW>(g, tap_dy, tap_dx, p0, p1, p2, rc, jbeg, jend, dst, sw);
+            return;
+        }
+        const RowPre rp32 = row_pre(g, rc);
+#define DTF_GATHER_CASE32(LL)                                                                                     \
+    case LL:                                                                                                      \
+        if (two32) gather_taps_t<LL, true, E, SW>(g, tap_dy, tap_dx, p0, p1, p2, rp32, jbeg, jend, dst, sw);       \
+        else gather_taps_t<LL, false, E, SW>(g, tap_dy, tap_dx, p0, p1, p2, rp32, jbeg, jend, dst, sw);            \
+        break;
+        switch (g.cpt_shift) {
+            DTF_GATHER_CASE32(1)
+            DTF_GATHER_CASE32(2)
+            DTF_GATHER_CASE32(3)
+        }
+#undef DTF_GATHER_CASE32
         return;
     }
     if (g.stride > 2) {
