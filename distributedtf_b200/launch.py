@@ -124,7 +124,7 @@ def run_master(cfg: RunConfig, comm, board=None) -> Dict[str, Any]:
     prof = cluster.print_profiling_info()
     cluster.kill_all_workers()
     return {"elapsed": elapsed, "best": best, "profiling": prof, "history": cluster.history,
-            "pop_size": cluster.pop_size}
+            "pop_size": cluster.pop_size, "board_fallbacks": cluster.board_fallbacks}
 
 
 def run_worker(cfg: RunConfig, comm, dp_group=None, mirror=None) -> TrainingWorker:

@@ -26,41 +26,7 @@ def _align(n: int, a: int = 256) -> int:
     return (n + a - 1) // a * a
 
 
-class _StepGate:
-    """Steps of different members (threads) run concurrently; a CUDA-graph capture runs alone."""
-
-    def __init__(self):
-        self._cv = threading.Condition()
-        self._active = 0
-        self._capturing = False
-
-    def enter_step(self) -> None:
-        with self._cv:
-            while self._capturing:
-                self._cv.wait()
-            self._active += 1
-
-    def exit_step(self) -> None:
-        with self._cv:
-            self._active -= 1
-            if self._active == 0:
-                self._cv.notify_all()
-
-    def enter_capture(self) -> None:
-        with self._cv:
-            while self._capturing:
-                self._cv.wait()
-            self._capturing = True
-            while self._active > 0:
-                self._cv.wait()
-
-    def exit_capture(self) -> None:
-        with self._cv:
-            self._capturing = False
-            self._cv.notify_all()
-
-
-_GATE = _StepGate()
+from ..utils.capture_gate import GATE as _GATE      # steps run concurrently, a CUDA-graph capture runs alone
 
 
 class NativeEngineBase:

@@ -68,9 +68,14 @@ class ScoreBoard:
 
     def snapshot(self):
         """One copy of the board to the host: (hits[int], seen[int], epochs[int]) lists."""
-        with torch.cuda.stream(self._stream):
-            self._host.copy_(self._tensor[: self._host.numel()], non_blocking=True)
-        self._stream.synchronize()
+        from ..utils.capture_gate import GATE
+        GATE.enter_step()                 # never while a thread of this process captures a CUDA graph
+        try:
+            with torch.cuda.stream(self._stream):
+                self._host.copy_(self._tensor[: self._host.numel()], non_blocking=True)
+            self._stream.synchronize()
+        finally:
+            GATE.exit_step()
         words = self._host.view(torch.int32).view(-1, 4)
         epochs = self._host.view(torch.int64).view(-1, 2)[:, 1]
         return ([int(w) & 0xFFFFFFFF for w in words[:, 0]], [int(w) & 0xFFFFFFFF for w in words[:, 1]],

@@ -55,6 +55,17 @@ def test_population_of_the_other_native_engines(tmp_path, kw):
     assert out["profiling"]["device_train"] > 0
 
 
+def test_board_polling_does_not_collide_with_graph_captures(tmp_path):
+    """In-process run (master and worker are threads): the master polls the device score board while the worker
+    captures two CUDA graphs per member and more after every explore.  Un-gated, those polls failed with
+    cudaErrorStreamCaptureUnsupported at population 50 of the reference's sweep; now they enter the capture gate."""
+    from distributedtf_b200.launch import run_local
+    out = run_local(_cfg(tmp_path, target_model="mnist", population_size=40, train_round=3, max_train_steps=2,
+                         eval_batches=1, checkpoint_every=0))
+    assert out["pop_size"] >= 38 and len(out["history"]) == 3
+    assert out["board_fallbacks"] == 0
+
+
 def test_cifar_file_exploit_restores_bit_identical_state(tmp_path):
     """Reference mechanism (checkpoint files copied by the master): loser == winner after restore."""
     from distributedtf_b200 import ckpt
