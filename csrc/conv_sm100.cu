@@ -357,6 +357,21 @@ extern "C" int dtf_sm_count() {
     }
     return (g_sm_limit > 0 && g_sm_limit < g_num_sms) ? g_sm_limit : g_num_sms;
 }
+extern "C" int dtf_stream_create(int device, cudaStream_t* out) {
+    if (out == nullptr) return DTF_ERR_ARG;
+    int prev = 0;
+    if (cudaGetDevice(&prev) != cudaSuccess || cudaSetDevice(device) != cudaSuccess) return DTF_ERR_CUDA;
+    const cudaError_t e = cudaStreamCreateWithFlags(out, cudaStreamNonBlocking);
+    cudaSetDevice(prev);
+    return e == cudaSuccess ? DTF_OK : DTF_ERR_CUDA;
+}
+extern "C" int dtf_stream_destroy(int device, cudaStream_t stream) {
+    int prev = 0;
+    if (cudaGetDevice(&prev) != cudaSuccess || cudaSetDevice(device) != cudaSuccess) return DTF_ERR_CUDA;
+    const cudaError_t e = cudaStreamDestroy(stream);
+    cudaSetDevice(prev);
+    return e == cudaSuccess ? DTF_OK : DTF_ERR_CUDA;
+}
 extern "C" int dtf_set_sm_limit(int n) {
     g_sm_limit = n > 0 ? n : 0;
     return dtf_sm_count();

@@ -70,11 +70,11 @@ def model_kwargs(cfg: RunConfig, dp_group=None, dp_rank: int = 0) -> Dict[str, A
         from .utils.logs import hooks as _hooks
         kw["hooks"] = _hooks.get_train_hooks(cfg.hooks, model_dir=cfg.save_root, batch_size=128)
     # Members that train concurrently inside one process (members_in_flight > 1: a host thread and a CUDA stream
-    # each) launch their kernels directly instead of replaying CUDA graphs.  Capturing a graph in one thread while
-    # other threads submit work and replay their own graphs was not reliable on this driver (580.159): in the full
-    # GPU test sequence four of five runs ended in an invalidated capture or an illegal memory access, none did
-    # without graphs.
-    kw["use_graphs"] = cfg.members_in_flight <= 1
+    # each) replay CUDA graphs like everybody else.  For a while they could not: captures were invalidated or ended
+    # in illegal memory accesses in four of five runs.  The cause was torch.cuda.Stream() handing out the same 32
+    # pooled streams round-robin, so one member's capture stream was another member's compute stream; every
+    # long-lived stream now comes from utils/streams.new_stream().  DTF_INFLIGHT_GRAPHS=0 restores direct launches.
+    kw["use_graphs"] = cfg.members_in_flight <= 1 or os.environ.get("DTF_INFLIGHT_GRAPHS", "1") != "0"
     kw["benchmark"] = (cfg.benchmark_logger_type, cfg.benchmark_log_dir)
     # the file-exploit path copies checkpoint files right after GET: keep those saves synchronous
     kw["checkpoint_every"] = cfg.checkpoint_every

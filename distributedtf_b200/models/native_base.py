@@ -20,6 +20,7 @@ from typing import Any, Dict, List, Optional, Tuple
 import torch
 
 from ..ops import native, reference
+from ..utils.streams import new_stream
 
 
 def _align(n: int, a: int = 256) -> int:
@@ -241,7 +242,7 @@ class NativeEngineBase:
                 # member's batch size)
                 g = torch.cuda.CUDAGraph()
                 if self._cap_stream is None:
-                    self._cap_stream = torch.cuda.Stream(device=self.device)
+                    self._cap_stream = new_stream(self.device)
                 self._cap_stream.wait_stream(cur)
                 with torch.cuda.stream(self._cap_stream):
                     g.capture_begin(capture_error_mode="thread_local")
@@ -378,3 +379,10 @@ class NativeEngineBase:
 
     def close(self) -> None:
         self._graphs.clear()
+        from ..utils import streams
+        for name in ("_side", "_cap_stream"):
+            st = getattr(self, name, None)
+            if st is not None:
+                st.synchronize()
+                streams.release(st)
+                setattr(self, name, None)

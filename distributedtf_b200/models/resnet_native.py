@@ -30,6 +30,7 @@ from typing import Any, Dict, List, Optional, Tuple
 import torch
 
 from ..ops import native, reference
+from ..utils.streams import new_stream
 from . import resnet
 from .native_base import NativeEngineBase, _align
 
@@ -323,7 +324,7 @@ class NativeResNetEngine(NativeEngineBase):
     #    flight hides a good part of it.  Inside CUDA-graph capture the fork/join become graph branches.
     def _fork(self):
         if self._side is None:
-            self._side = torch.cuda.Stream(device=self.device)
+            self._side = new_stream(self.device)
         ev = torch.cuda.Event()
         ev.record(torch.cuda.current_stream())
         self._side.wait_event(ev)

@@ -25,6 +25,7 @@ import torch
 
 from ..ops import native, native_ext
 from . import symm
+from ..utils.streams import new_stream
 
 vp, ull, i32 = C.c_void_p, C.c_ulonglong, C.c_int
 native_ext.register("dtf_score_publish", [vp, vp, i32, ull, i32, vp, vp])
@@ -53,7 +54,7 @@ class ScoreBoard:
                 self._tensor = torch.as_tensor(self._owner, device=self.device)
         self._host = torch.zeros(max_members * SLOT_BYTES, dtype=torch.uint8,
                                  pin_memory=torch.cuda.is_available())
-        self._stream = torch.cuda.Stream(device=self.device)
+        self._stream = new_stream(self.device)
 
     @classmethod
     def view(cls, ptr: int, max_members: int, device) -> "ScoreBoard":

@@ -137,7 +137,8 @@ class TrainingWorker:
             torch.cuda.set_device(dev)
             st = self._member_streams.get(g.cluster_id)
             if st is None:
-                st = self._member_streams[g.cluster_id] = torch.cuda.Stream(device=dev)
+                from .utils.streams import new_stream
+                st = self._member_streams[g.cluster_id] = new_stream(dev)
             st.wait_stream(torch.cuda.default_stream(dev))       # exploit / explore writes of the main thread
             with torch.cuda.stream(st):
                 ok = self._train_member(g, num_epoches, total_epochs)

@@ -352,6 +352,14 @@ int dtf_act_mask(const dtf_bf16* g_in, const dtf_bf16* act, dtf_bf16* g_out, flo
 int dtf_set_sm_limit(int n);
 int dtf_sm_count(void);
 
+/* A CUDA stream of its own (cudaStreamNonBlocking) on `device`.  torch.cuda.Stream() hands out streams from a pool of
+ * 32 per device round-robin, so the 33rd "new" stream of a process is the first one again: with dozens of members per
+ * worker, one member's graph-capture stream was another member's compute stream (or the master's board-polling
+ * stream), and work of the one ended up in -- or was rejected by -- the capture of the other.  Every long-lived
+ * stream of the framework comes from here instead (utils/streams.py wraps it as torch.cuda.ExternalStream). */
+int dtf_stream_create(int device, cudaStream_t* out);
+int dtf_stream_destroy(int device, cudaStream_t stream);
+
 /* ---- host runtime: background checkpoint writer (csrc/host_io.cpp) -------------------------------------
  * Replaces the synchronous `saver.save(sess, ...)` the reference runs after every train call
  * (mnist_model.py / cifar10 model, via TensorFlow's C++ Saver).  A job = wait until everything queued on
