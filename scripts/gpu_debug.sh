@@ -1,6 +1,5 @@
 #!/bin/bash
-# exit codes of the test processes with own streams; fallback configuration if they are not clean
-O=gpurun_out/r10; mkdir -p $O
-timeout 300 python -X faulthandler -m pytest tests/test_pbt_gpu.py -m gpu -q -x -k "members_in_flight or polling" > $O/own.log 2>&1; echo "own streams subset rc=$?"; tail -25 $O/own.log | cut -c1-160
-timeout 600 python -X faulthandler -m pytest tests -m gpu -q -x > $O/pytest_gpu.log 2>&1; echo "own streams suite rc=$?"; tail -2 $O/pytest_gpu.log | cut -c1-200
-DTF_POOLED_STREAMS=1 DTF_INFLIGHT_GRAPHS=0 timeout 300 python -X faulthandler -m pytest tests/test_pbt_gpu.py -m gpu -q -x -k "members_in_flight or polling" > $O/pooled.log 2>&1; echo "pooled subset rc=$?"; tail -3 $O/pooled.log | cut -c1-160
+# two GPUs: multi-GPU tests and the 2-GPU headline bench with the own-stream build
+O=gpurun_out/r11; mkdir -p $O
+timeout 400 python -m pytest tests/test_comm_kernels_gpu.py tests/test_pbt_gpu.py -m gpu -q -x > $O/pytest_2gpu.log 2>&1; echo "2-GPU tests rc=$?"; tail -2 $O/pytest_2gpu.log | cut -c1-200
+timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29551 bench.py --gpus 2 --steps 20 --warmup 5 2> $O/b2.err | grep '^{' > $O/bench_native_2gpu.json; echo "bench2 rc=$?"; cut -c1-220 $O/bench_native_2gpu.json; tail -2 $O/b2.err | cut -c1-200
