@@ -14,6 +14,7 @@ import torch
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from distributedtf_b200.hpspace import default_cifar_hparam  # noqa: E402
+from distributedtf_b200.utils.streams import new_stream  # noqa: E402
 
 
 def make_engine(model, seed, dev):
@@ -35,7 +36,7 @@ def run(model, k, steps, bs=128, share=False):
     engines, streams, data = [], [], []
     for i in range(k):
         e, shape = make_engine(model, i, dev)
-        s = torch.cuda.Stream(device=dev)
+        s = new_stream(dev)          # not torch.cuda.Stream(): its 32 pooled streams repeat (utils/streams.py)
         x = torch.randint(0, 256, (bs, *shape), dtype=torch.uint8, device=dev)
         y = torch.randint(0, 10, (bs,), dtype=torch.int32, device=dev)
         with torch.cuda.stream(s):                       # plain run + graph capture, one member at a time
