@@ -22,7 +22,15 @@
 //
 // The wgrad kernel reuses the same gathered tiles viewed MN-major (K = pixels): both UMMA
 // operands are transposed by descriptor, D[co][tap*Cin+ci] accumulates over all tiles of the
-// CTA in TMEM and is flushed with fp32 atomics into the gradient arena.
+// CTA in TMEM and is flushed with fp32 atomics into the gradient arena.  More than 128 output
+// channels (bottleneck blocks) are split over blockIdx.z.
+//
+// Both kernels are templates on E, the elements per 16-byte chunk: E = 8 for bf16 tensors
+// (kind::f16) and E = 4 for fp32 tensors multiplied as tf32 (kind::tf32; the reference's default
+// dtype).  K-major operands keep their byte layout (two chunks = 32 bytes of K per MMA either
+// way).  MN-major tf32 operands exist in one layout only -- 128-byte rows with a 32-byte swizzle
+// base, descriptor layout type 1 (bench/probe_umma.py) -- so the fp32 wgrad kernel writes its
+// tiles through chunk_addr<true> (conv_common.cuh) instead of the chunk-major form.
 #include "conv_common.cuh"
 
 namespace dtf {
