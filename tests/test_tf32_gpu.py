@@ -6,12 +6,15 @@ never pass ``--dtype``).  Tolerances here are those of tf32 products with fp32 a
 product), several times tighter than the bf16 tests in ``test_kernels_gpu.py``.
 """
 import math
+import os
+import sys
 
 import pytest
 import torch
 import torch.nn.functional as F
 
-from test_kernels_gpu import _bn_bwd_ref, bn_consts, conv_ref, rnd, stats_of
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))      # helpers of the bf16 kernel tests, any import mode
+from test_kernels_gpu import _bn_bwd_ref, bn_consts, conv_ref, rnd, stats_of  # noqa: E402
 
 pytestmark = pytest.mark.gpu
 
