@@ -239,9 +239,10 @@ def main():
     if args.impl == "reference":
         # The reference cannot be installed or run here: it has no packaging files at all and needs
         # TensorFlow 1.x + mpi4py + hyperopt (none in the image, no network).  See DESIGN.md.
-        print(json.dumps({"impl": "reference",
-                          "unavailable": "reference has no setup.py/pyproject (pip install fails) and needs "
-                                         "TensorFlow 1.x (tf.contrib), mpi4py, hyperopt, mpirun: none installable offline"}))
+        if os.environ.get("RANK", "0") == "0":           # one line per job, also under torchrun
+            print(json.dumps({"impl": "reference",
+                              "unavailable": "reference has no setup.py/pyproject (pip install fails) and needs "
+                                             "TensorFlow 1.x (tf.contrib), mpi4py, hyperopt, mpirun: none installable offline"}))
         return 0
 
     import torch
